@@ -28,6 +28,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -1402,6 +1404,8 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                     S4 Lem = Le * mis_bsdf;
                     S4 a = replay_path(sc, bb, (int) bi);
                     L = L + a * Lem;
+                    if (getenv("PLT_ORACLE_DEBUG") && std::isnan((a * Lem)[0]))
+                        fprintf(stderr, "NaN EM bi=%u a=%g Lem=%g mis=%g lnd=%g empdf=%g\n", bi, a[0], Lem[0], mis_bsdf, b.last_nd_pdf, em_pdf);
                 }
             }
         }
@@ -1457,6 +1461,10 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                 float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
                 S4 a = replay_path(sc, bb, (int) bi);
                 L = L + ((em_weight * mis_em) * bsdf_val) * a;
+                if (getenv("PLT_ORACLE_DEBUG") && std::isnan((((em_weight * mis_em) * bsdf_val) * a)[0]))
+                    fprintf(stderr, "NaN NEE bi=%u em_w=%g mis=%g bsdf=%g a=%g pdf=%g bsdf_pdf=%g wo=(%g %g %g) wi=(%g %g %g) type=%u\n", bi,
+                            em_weight[0], mis_em, bsdf_val[0], a[0], ds.pdf, bsdf_pdf, wo.x, wo.y, wo.z, si.wi.x, si.wi.y, si.wi.z,
+                            si_bsdf(sc, si)->type);
             }
         }
     }
