@@ -220,8 +220,10 @@ typedef struct pltb_stats {
 typedef struct pltb_context pltb_context;
 typedef struct pltb_scene pltb_scene;
 
-/* device < 0: use the current CUDA device. nccl_comm: an initialised ncclComm_t (as void*) or NULL. */
-int pltb_context_create(int device, int rank, int world, void *nccl_comm, pltb_context **out);
+/* device < 0: use the current CUDA device.  world > 1: nccl_unique_id points to the 128-byte ncclUniqueId that rank 0
+ * obtained from pltb_nccl_unique_id() and shared with the other ranks (e.g. through torch.distributed). */
+int pltb_nccl_unique_id(void *out128);
+int pltb_context_create(int device, int rank, int world, const void *nccl_unique_id, pltb_context **out);
 void pltb_context_destroy(pltb_context *ctx);
 
 int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *desc, pltb_scene **out);

@@ -87,7 +87,7 @@ class Stats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
-EXPORTS = ["pltb_context_create", "pltb_context_destroy", "pltb_scene_create", "pltb_scene_update_sensor",
+EXPORTS = ["pltb_nccl_unique_id", "pltb_context_create", "pltb_context_destroy", "pltb_scene_create", "pltb_scene_update_sensor",
            "pltb_scene_release", "pltb_render", "pltb_cancel", "pltb_film_device_ptr", "pltb_synchronize",
            "pltb_last_error", "pltb_abi_version"]
 
@@ -104,6 +104,7 @@ def lib():
         L = C.CDLL(LIB_PATH)
         vp = C.c_void_p
         L.pltb_context_create.argtypes = [C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp)]
+        L.pltb_nccl_unique_id.argtypes = [vp]
         L.pltb_context_destroy.argtypes = [vp]
         L.pltb_context_destroy.restype = None
         L.pltb_scene_create.argtypes = [vp, C.POINTER(SceneDesc), C.POINTER(vp)]

@@ -1,0 +1,268 @@
+// pltb_bsdf.cuh -- the wbsdf_sample / wbsdf_eval / wbsdf_pdf / wbsdf_weight family for the BSDFs on the plt path,
+// including the TwoSidedBRDF wrapper.  JIT-variant semantics (see oracle/plt_oracle.cpp header).
+#pragma once
+#include "pltb_shading.cuh"
+
+namespace pltb {
+
+struct BSDFSampleOut { V3 wo; float pdf, eta; uint32_t type; S4 weight; };
+
+PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, V2 uv, float cos_theta) {
+    S4 eta = tex_eval(sc, b.tex[0], wl, uv), k = tex_eval(sc, b.tex[1], wl, uv), F;
+    for (int i = 0; i < 4; ++i) F.v[i] = fresnel_conductor(cos_theta, eta.v[i], k.v[i]);
+    return F;
+}
+
+// wi already has the twosided flip applied.
+PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
+                                        V2 lobe_s2) {
+    BSDFSampleOut o;
+    o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f);
+    const float cos_theta_i = wi.z;
+    switch (b.type) {
+        case PLTB_BSDF_DIFFUSE: {  // src/bsdfs/diffuse.cpp:101-125
+            if (!(cos_theta_i > 0.f)) return o;
+            o.wo = square_to_cosine_hemisphere(s2);
+            o.pdf = kInvPi * o.wo.z;
+            o.eta = 1.f; o.type = F_DiffuseReflection;
+            if (o.pdf > 0.f) o.weight = tex_eval(sc, b.tex[0], wl, uv);
+            return o;
+        }
+        case PLTB_BSDF_CONDUCTOR: {  // src/bsdfs/conductor.cpp:248-308
+            if (!(cos_theta_i > 0.f)) return o;
+            o.type = F_DeltaReflection; o.wo = reflect(wi); o.eta = 1.f; o.pdf = 1.f;
+            o.weight = tex_eval(sc, b.tex[2], wl, uv) * conductor_F(sc, b, wl, uv, cos_theta_i);
+            return o;
+        }
+        case PLTB_BSDF_DIELECTRIC: {  // src/bsdfs/dielectric.cpp:265-400
+            FresnelResult f = fresnel(cos_theta_i, b.f[0]);
+            float t_i = 1.f - f.r;
+            bool selected_r = s1 <= f.r;
+            o.pdf = selected_r ? f.r : t_i;
+            o.type = selected_r ? F_DeltaReflection : F_DeltaTransmission;
+            o.wo = selected_r ? reflect(wi) : refract(wi, f.cos_theta_t, f.eta_ti);
+            o.eta = selected_r ? 1.f : f.eta_it;
+            S4 w = s4(1.f);
+            if (selected_r) { if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv); }
+            else {
+                if (b.tex[3] >= 0) w = w * tex_eval(sc, b.tex[3], wl, uv);
+                w = w * sqr(f.eta_ti);
+            }
+            o.weight = w;
+            return o;
+        }
+        case PLTB_BSDF_ROUGHCONDUCTOR: {  // src/bsdfs/roughconductor.cpp:225-311
+            if (!(cos_theta_i > 0.f)) return o;
+            Microfacet distr = make_mf(b);
+            float pdf; V3 m = distr.sample(wi, s2, pdf);
+            o.pdf = pdf; o.wo = reflect(wi, m); o.eta = 1.f; o.type = F_GlossyReflection;
+            bool active = (o.pdf != 0.f) && o.wo.z > 0.f;
+            float weight = distr.sample_visible ? distr.smith_g1(o.wo, m)
+                                                : distr.G(wi, o.wo, m) * dot(wi, m) / (cos_theta_i * m.z);
+            o.pdf /= 4.f * dot(o.wo, m);
+            S4 F = conductor_F(sc, b, wl, uv, dot(wi, m));
+            S4 w = s4(weight);
+            if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv);
+            if (active) o.weight = F * w;
+            return o;
+        }
+        case PLTB_BSDF_ROUGHGRATING: {  // src/bsdfs/roughgrating.cpp:449-595, sample_diffract :414-447
+            if (!(cos_theta_i > 0.f)) return o;
+            Microfacet distr = make_mf(b);
+            float pdf; V3 m = distr.sample(wi, s2, pdf);
+            o.pdf = pdf;
+            V3 reflection_dir = reflect(wi, m);
+            float wavelength = wl.v[0];
+            Frame nf = frame_from_normal(m);
+            V3 wi_local = nf.to_local(wi);
+            Grating g = make_grating(b, uv);
+            V2 pdf_xy; int lx, ly;
+            g.sample_lobe(sc.bessel, lobe_s2, wi_local, wavelength * 1e-3f, lx, ly, pdf_xy);
+            float intensity = g.lobe_intensity(sc.bessel, lx, ly, wi_local, wavelength);  // nm as written (N2)
+            bool valid; V3 wo_local = g.diffract(wi_local, lx, ly, wavelength * 1e-3f, valid);
+            o.wo = nf.to_world(wo_local);
+            float grating_pdf = pdf_xy.x * pdf_xy.y;
+            o.eta = 1.f; o.type = F_GlossyReflection;
+            bool active = (o.pdf != 0.f) && o.wo.z > 0.f;
+            o.pdf *= grating_pdf;
+            float weight = distr.sample_visible ? distr.smith_g1(reflection_dir, m)
+                                                : distr.G(wi, reflection_dir, m) * dot(wi, m) / (cos_theta_i * m.z);
+            o.pdf /= 4.f * dot(reflection_dir, m);
+            S4 F = conductor_F(sc, b, wl, uv, dot(wi, m));
+            S4 w = s4(weight);
+            if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv);
+            if (active) o.weight = ((F * w) * intensity) * b.f[7];
+            return o;
+        }
+        default: return o;
+    }
+}
+
+// conventional rough-conductor eval_pdf (roughconductor.cpp:432-516; RoughGrating::eval_pdf roughgrating.cpp:1036-1127)
+PLTB_HD void rough_eval_pdf(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo, bool apply_refl,
+                            S4 &value, float &pdf) {
+    value = s4(0.f); pdf = 0.f;
+    float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    V3 H = normalize(wo + wi);
+    bool active = cos_theta_i > 0.f && cos_theta_o > 0.f && dot(wi, H) > 0.f && dot(wo, H) > 0.f;
+    if (!active) return;
+    Microfacet distr = make_mf(b);
+    float D = distr.eval(H);
+    active = D != 0.f;
+    float g1 = distr.smith_g1(wi, H), G = g1 * distr.smith_g1(wo, H);
+    float val = D * G / (4.f * cos_theta_i);
+    S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
+    S4 v = s4(val);
+    if (apply_refl && b.tex[2] >= 0) v = v * tex_eval(sc, b.tex[2], wl, uv);
+    float p = distr.sample_visible ? D * g1 / (4.f * cos_theta_i) : distr.pdf(wi, H) / (4.f * dot(wo, H));
+    if (active) { value = F * v; pdf = p; }
+}
+
+// RoughGrating::wbsdf_eval, spectral branch (roughgrating.cpp:841-969).  Same arithmetic and summation order as the
+// reference's lx/ly/lambda loops; the per-order Bessel terms (4 orders x 4 wavelengths instead of 2 x lobes^2 x 4
+// evaluations), the incident sines and the coherence factor are hoisted out of the loops.
+PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    V3 H = normalize(wo + wi);
+    Grating g = make_grating(b, uv);
+    V3 reflection_dir = reflect(wi);
+    const float a_win = 2 * sqrtf(b.f[1] * b.f[2]);
+    const int half = (int) g.lobes / 2;
+    const bool one_d = g.is_1d();
+    float term[4][PLTB_MAX_LOBES / 2 + 1];
+    float coh[4], wl_um[4];
+    const float angle_offset = fabsf(unit_angle(reflection_dir, wo));
+    for (int i = 0; i < 4; ++i) {
+        wl_um[i] = wl.v[i] * 1e-3f;
+        const float a = kFourPi * g.q / (wl_um[i] * fabsf(wi.z));
+        for (int l = 0; l <= half; ++l) term[i][l] = g.axis_term(sc.bessel, a, l);
+        // Coherence(m_coherence, 1.0).inv_coherence_det(k), include/mitsuba/plt/plt.h:57-100
+        float k = kTwoPi / wl_um[i];
+        float s = k / (kTwoPi * (1.0f * 1e+3f));
+        float d00 = s * b.f[8], d01 = s * 0.f;
+        float det = fmsub(d00, d00, d01 * d01);
+        float inv_det = isnan_(det) ? 0.0f : det;
+        float ac = expf(-0.5f * angle_offset * inv_det * angle_offset);
+        coh[i] = isnan_(ac) ? 0.0f : ac;
+    }
+    const V2 sin_i = g.sin_i(wi);
+    S4 result = s4(0.f);
+    for (int lx = -half; lx <= half; ++lx) {
+        for (int ly = -half; ly <= half; ++ly) {
+            const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
+            for (int i = 0; i < 4; ++i) {
+                float ix = term[i][alx], iy = one_d ? ix : term[i][aly];
+                float lobe_intensity = g.multiplier * ix * iy;
+                bool lobe_active; V3 center_dir = g.diffract_s(sin_i, lx, ly, wl_um[i], lobe_active);
+                bool inside = lobe_active && fabsf(unit_angle(center_dir, wo)) < a_win;
+                if (lx == 0 && ly == 0) result.v[i] += inside ? lobe_intensity : 0.0f;
+                else result.v[i] += inside ? lobe_intensity * coh[i] : 0.0f;
+            }
+        }
+    }
+    S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
+    if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+    return F * result;
+}
+
+PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    switch (b.type) {
+        case PLTB_BSDF_DIFFUSE:  // diffuse.cpp:127-142
+            if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return s4(0.f);
+            return (tex_eval(sc, b.tex[0], wl, uv) * kInvPi) * cos_theta_o;
+        case PLTB_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:313-390
+            if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return s4(0.f);
+            V3 H = normalize(wo + wi);
+            Microfacet distr = make_mf(b);
+            float D = distr.eval(H);
+            float G = distr.G(wi, wo, H);
+            S4 result = s4(D * G / (4.f * cos_theta_i));
+            S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
+            if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+            return D != 0.f ? F * result : s4(0.f);
+        }
+        case PLTB_BSDF_ROUGHGRATING: return grating_eval(sc, b, wi, uv, wl, wo);
+        default: return s4(0.f);
+    }
+}
+
+PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    float cos_theta_i = wi.z, cos_theta_o = wo.z;
+    switch (b.type) {
+        case PLTB_BSDF_DIFFUSE: return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? kInvPi * wo.z : 0.f;
+        case PLTB_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:392-430
+            V3 m = normalize(wo + wi);
+            bool active = cos_theta_i > 0.f && cos_theta_o > 0.f && dot(wi, m) > 0.f && dot(wo, m) > 0.f;
+            if (!active) return 0.f;
+            Microfacet distr = make_mf(b);
+            return distr.sample_visible ? distr.eval(m) * distr.smith_g1(wi, m) / (4.f * cos_theta_i)
+                                        : distr.pdf(wi, m) / (4.f * dot(wo, m));
+        }
+        case PLTB_BSDF_ROUGHGRATING: {  // roughgrating.cpp:1009-1034
+            float k = kTwoPi / (wl.v[0] * 1e-3f);
+            return expf(-sqr(wi.z * b.f[6] * k));
+        }
+        default: return 0.f;
+    }
+}
+
+PLTB_HD S4 bsdf_weight_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    switch (b.type) {
+        case PLTB_BSDF_DIFFUSE: return tex_eval(sc, b.tex[0], wl, uv);  // diffuse.cpp:182-200
+        case PLTB_BSDF_CONDUCTOR:  // conductor.cpp:320-376
+            if (!(wi.z > 0.f)) return s4(0.f);
+            return tex_eval(sc, b.tex[2], wl, uv) * conductor_F(sc, b, wl, uv, wi.z);
+        case PLTB_BSDF_DIELECTRIC: {  // dielectric.cpp:404-590
+            S4 w = s4(1.f);
+            if (wo.z > 0.0f) { if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv); }
+            else { if (b.tex[3] >= 0) w = w * tex_eval(sc, b.tex[3], wl, uv); }
+            return w;
+        }
+        case PLTB_BSDF_ROUGHCONDUCTOR:
+        case PLTB_BSDF_ROUGHGRATING: {  // base wbsdf_weight, src/render/bsdf.cpp:85-97
+            S4 e; float p;
+            rough_eval_pdf(sc, b, wi, uv, wl, wo, b.type == PLTB_BSDF_ROUGHCONDUCTOR, e, p);
+            return p > 0.0f ? e / p : s4(0.f);
+        }
+        default: return s4(0.f);
+    }
+}
+
+// TwoSidedBRDF with a single nested BRDF (src/bsdfs/twosided.cpp:262-420)
+PLTB_HD const pltb_bsdf *si_bsdf(const DeviceScene &sc, int32_t shape) {
+    if (shape < 0) return nullptr;
+    int32_t id = sc.shapes[shape].bsdf;
+    return id < 0 ? nullptr : sc.bsdfs + id;
+}
+PLTB_HD BSDFSampleOut wbsdf_sample(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
+                                   V2 lobe_s2) {
+    if (!b) { BSDFSampleOut o; o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f); return o; }
+    if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) {
+        float wz = wi.z;
+        wi.z = fabsf(wi.z);
+        BSDFSampleOut o = bsdf_sample_inner(sc, *b, wi, uv, wl, s1, s2, lobe_s2);
+        o.wo.z = mulsign(o.wo.z, wz);
+        return o;
+    }
+    return bsdf_sample_inner(sc, *b, wi, uv, wl, s1, s2, lobe_s2);
+}
+PLTB_HD void twosided_flip(const pltb_bsdf *b, V3 &wi, V3 &wo) {
+    if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
+}
+PLTB_HD S4 wbsdf_eval(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    if (!b) return s4(0.f);
+    twosided_flip(b, wi, wo);
+    return bsdf_eval_inner(sc, *b, wi, uv, wl, wo);
+}
+PLTB_HD float wbsdf_pdf(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    if (!b) return 0.f;
+    twosided_flip(b, wi, wo);
+    return bsdf_pdf_inner(sc, *b, wi, uv, wl, wo);
+}
+PLTB_HD S4 wbsdf_weight(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    if (!b) return s4(0.f);
+    twosided_flip(b, wi, wo);
+    return bsdf_weight_inner(sc, *b, wi, uv, wl, wo);
+}
+
+}  // namespace pltb

@@ -1,0 +1,363 @@
+// pltb_capi.cu -- the C ABI of include/pltb.h: context / scene lifetime, scene upload, render orchestration,
+// NCCL film reduce.  No CPU rendering path exists in this library: every entry point that computes launches CUDA kernels.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pltb_bvh.h"
+#include "pltb_launch.h"
+
+using namespace pltb;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CU(call)                                                                                                     \
+    do {                                                                                                             \
+        cudaError_t e_ = (call);                                                                                     \
+        if (e_ != cudaSuccess)                                                                                       \
+            return fail(PLTB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                          \
+    } while (0)
+
+// ---- NCCL, resolved at run time from the libnccl the host process already loaded (torch's) -------------------------------
+typedef struct ncclComm *ncclComm_t;
+struct NcclUid { char b[128]; };   // ncclUniqueId (passed by value)
+struct NcclApi {
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, NcclUid, int) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Reduce)(const void *, void *, size_t, int, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+static NcclApi g_nccl;
+static bool load_nccl() {
+    if (g_nccl.ok) return true;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL | RTLD_NOLOAD);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = RTLD_DEFAULT;
+    *(void **) &g_nccl.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+    *(void **) &g_nccl.CommInitRank = dlsym(h, "ncclCommInitRank");
+    *(void **) &g_nccl.AllReduce = dlsym(h, "ncclAllReduce");
+    *(void **) &g_nccl.Reduce = dlsym(h, "ncclReduce");
+    *(void **) &g_nccl.CommDestroy = dlsym(h, "ncclCommDestroy");
+    *(void **) &g_nccl.GetErrorString = dlsym(h, "ncclGetErrorString");
+    g_nccl.ok = g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.Reduce && g_nccl.CommDestroy;
+    return g_nccl.ok;
+}
+
+struct pltb_context {
+    int device = 0, rank = 0, world = 1;
+    cudaStream_t stream = nullptr;
+    ncclComm_t comm = nullptr;
+    std::atomic<int> cancel{ 0 };
+    // film
+    float *accum = nullptr; uint64_t accum_floats = 0;
+    float *rgb = nullptr; uint64_t rgb_floats = 0;
+    // pass state
+    PassState st{};
+    uint32_t st_chunk = 0, st_depth = 0;
+    std::vector<void *> st_allocs;
+    unsigned long long *counters = nullptr;
+    float *dump_wl = nullptr, *dump_L = nullptr; uint64_t dump_cap = 0;
+    int sm_count = 148;
+    cudaEvent_t ev[2] = { nullptr, nullptr };
+};
+
+struct pltb_scene {
+    pltb_context *ctx = nullptr;
+    DeviceScene dev{};
+    std::vector<void *> allocs;
+    std::vector<pltb_sensor> sensors;
+    pltb_sensor *d_sensors = nullptr;
+    uint32_t film_w = 0, film_h = 0;
+};
+
+template <class T> static int upload(std::vector<void *> &allocs, const T *host, size_t n, const T **dev) {
+    void *p = nullptr;
+    size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    CU(cudaMalloc(&p, bytes));
+    allocs.push_back(p);
+    if (n) CU(cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice));
+    *dev = (const T *) p;
+    return 0;
+}
+
+extern "C" {
+
+const char *pltb_last_error(void) { return g_err.c_str(); }
+int pltb_abi_version(void) { return PLTB_ABI_VERSION; }
+
+int pltb_nccl_unique_id(void *out128) {
+    if (!load_nccl()) return fail(PLTB_ERR_UNSUPPORTED, "NCCL is not loaded in this process (import torch first)");
+    int r = g_nccl.GetUniqueId(out128);
+    return r == 0 ? 0 : fail(PLTB_ERR_CUDA, "ncclGetUniqueId failed");
+}
+
+int pltb_context_create(int device, int rank, int world, const void *nccl_unique_id, pltb_context **out) {
+    if (!out || world < 1 || rank < 0 || rank >= world) return fail(PLTB_ERR_INVALID, "pltb_context_create: bad arguments");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(PLTB_ERR_CUDA, std::string("no CUDA device available (the plt path has no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0) CU(cudaGetDevice(&device));
+    CU(cudaSetDevice(device));
+    pltb_context *c = new pltb_context();
+    c->device = device; c->rank = rank; c->world = world;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev[0])); CU(cudaEventCreate(&c->ev[1]));
+    CU(cudaMalloc(&c->counters, 8 * sizeof(unsigned long long)));
+    if (world > 1) {
+        if (!nccl_unique_id) { delete c; return fail(PLTB_ERR_INVALID, "world > 1 needs an NCCL unique id"); }
+        if (!load_nccl()) { delete c; return fail(PLTB_ERR_UNSUPPORTED, "NCCL is not loaded in this process"); }
+        NcclUid uid; memcpy(uid.b, nccl_unique_id, 128);
+        int r = g_nccl.CommInitRank(&c->comm, world, uid, rank);
+        if (r != 0) { delete c; return fail(PLTB_ERR_CUDA, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error")); }
+    }
+    *out = c;
+    return 0;
+}
+
+static void free_state(pltb_context *c) {
+    for (void *p : c->st_allocs) cudaFree(p);
+    c->st_allocs.clear(); c->st_chunk = 0; c->st_depth = 0;
+}
+
+void pltb_context_destroy(pltb_context *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    free_state(c);
+    cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
+    cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **out) {
+    if (!ctx || !d || !out) return fail(PLTB_ERR_INVALID, "pltb_scene_create: null argument");
+    if (d->abi_version != PLTB_ABI_VERSION) return fail(PLTB_ERR_INVALID, "pltb_scene_create: ABI version mismatch");
+    if (d->n_sensors < 1) return fail(PLTB_ERR_INVALID, "pltb_scene_create: scene has no sensor");
+    for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
+        if (d->bsdfs[i].type > PLTB_BSDF_ROUGHGRATING) return fail(PLTB_ERR_UNSUPPORTED, "unsupported BSDF type");
+        if (d->bsdfs[i].type == PLTB_BSDF_ROUGHGRATING && (d->bsdfs[i].u[2] < 1 || d->bsdfs[i].u[2] > PLTB_MAX_LOBES))
+            return fail(PLTB_ERR_INVALID, "roughgrating: lobes must be in [1, 9]");
+    }
+    for (uint32_t i = 0; i < d->n_faces * 3; ++i)
+        if (d->faces[i] >= d->n_vertices) return fail(PLTB_ERR_INVALID, "face index out of range");
+    CU(cudaSetDevice(ctx->device));
+    pltb_scene *s = new pltb_scene();
+    s->ctx = ctx;
+    HostBVH bvh;
+    build_bvh(d, bvh);
+    DeviceScene &ds = s->dev;
+    int rc = 0;
+    const float *nodes = nullptr, *tris = nullptr;
+    rc |= upload(s->allocs, bvh.nodes.data(), bvh.nodes.size(), &nodes);
+    rc |= upload(s->allocs, bvh.tri_data.data(), bvh.tri_data.size(), &tris);
+    ds.bvh_nodes = (const float4 *) nodes; ds.tri_data = (const float4 *) tris;
+    ds.n_nodes = bvh.n_nodes; ds.n_prims = bvh.n_prims;
+    rc |= upload(s->allocs, d->positions, 3 * (size_t) d->n_vertices, &ds.positions);
+    rc |= upload(s->allocs, d->normals, 3 * (size_t) d->n_vertices, &ds.normals);
+    rc |= upload(s->allocs, d->texcoords, 2 * (size_t) d->n_vertices, &ds.texcoords);
+    rc |= upload(s->allocs, d->faces, 3 * (size_t) d->n_faces, &ds.faces);
+    rc |= upload(s->allocs, d->face_shape, (size_t) d->n_faces, &ds.face_shape);
+    rc |= upload(s->allocs, d->shapes, d->n_shapes, &ds.shapes);
+    rc |= upload(s->allocs, d->bsdfs, d->n_bsdfs, &ds.bsdfs);
+    rc |= upload(s->allocs, d->textures, d->n_textures, &ds.textures);
+    rc |= upload(s->allocs, d->tex_data, d->n_tex_data, &ds.tex_data);
+    rc |= upload(s->allocs, d->emitters, d->n_emitters, &ds.emitters);
+    rc |= upload(s->allocs, d->area_cdf, d->n_area_cdf, &ds.area_cdf);
+    rc |= upload(s->allocs, d->sensors, d->n_sensors, &ds.sensors);
+    rc |= upload(s->allocs, d->cie_srgb, 3 * 95, &ds.cie_srgb);
+    if (rc) { pltb_scene_release(s); return PLTB_ERR_CUDA; }
+    s->d_sensors = (pltb_sensor *) ds.sensors;
+    s->sensors.assign(d->sensors, d->sensors + d->n_sensors);
+    ds.film = d->film;
+    ds.n_faces = d->n_faces; ds.n_shapes = d->n_shapes; ds.n_emitters = d->n_emitters; ds.n_sensors = d->n_sensors;
+    ds.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
+    // Simpson nodes of math::bessel_j_small (include/mitsuba/core/math.h:204-223, 316-322), float ops as the reference
+    {
+        const float a = 0.f, b = kPi, h = (b - a) / (float) (20 - 1);
+        for (int i = 0; i < 20; ++i) { float t = a + h * (float) i; ds.bessel.t[i] = t; ds.bessel.sin_t[i] = sinf(t); }
+        ds.bessel.t[0] = a; ds.bessel.sin_t[0] = sinf(a); ds.bessel.t[19] = b; ds.bessel.sin_t[19] = sinf(b);
+        ds.bessel.h_over_3 = h / 3.0f;
+    }
+    s->film_w = d->film.width * d->n_sensors; s->film_h = d->film.height;
+    *out = s;
+    return 0;
+}
+
+int pltb_scene_update_sensor(pltb_scene *s, uint32_t sensor_index, const float to_world[16]) {
+    if (!s || sensor_index >= s->sensors.size()) return fail(PLTB_ERR_INVALID, "pltb_scene_update_sensor: bad sensor index");
+    CU(cudaSetDevice(s->ctx->device));
+    memcpy(s->sensors[sensor_index].to_world, to_world, 16 * sizeof(float));
+    CU(cudaMemcpyAsync(s->d_sensors + sensor_index, &s->sensors[sensor_index], sizeof(pltb_sensor), cudaMemcpyHostToDevice,
+                       s->ctx->stream));
+    CU(cudaStreamSynchronize(s->ctx->stream));
+    return 0;
+}
+
+void pltb_scene_release(pltb_scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    for (void *p : s->allocs) cudaFree(p);
+    delete s;
+}
+
+int pltb_cancel(pltb_context *c) { if (c) c->cancel.store(1); return 0; }
+int pltb_synchronize(pltb_context *c) { if (!c) return fail(PLTB_ERR_INVALID, "null context"); CU(cudaStreamSynchronize(c->stream)); return 0; }
+int pltb_film_device_ptr(pltb_context *c, float **accum, uint64_t *n) {
+    if (!c) return fail(PLTB_ERR_INVALID, "null context");
+    if (accum) *accum = c->accum;
+    if (n) *n = c->accum_floats;
+    return 0;
+}
+
+static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
+    if (c->st_chunk >= chunk && c->st_depth >= depth) return 0;
+    free_state(c);
+    auto alloc = [&](void **p, size_t bytes) -> int {
+        CU(cudaMalloc(p, bytes));
+        c->st_allocs.push_back(*p);
+        return 0;
+    };
+    PassState &st = c->st;
+    size_t nv = (size_t) chunk * depth;
+    int rc = 0;
+    rc |= alloc((void **) &st.wl, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.sensor_w, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.film_pos, chunk * sizeof(float2));
+    rc |= alloc((void **) &st.rng_state, chunk * sizeof(uint64_t));
+    rc |= alloc((void **) &st.rng_inc, chunk * sizeof(uint64_t));
+    rc |= alloc((void **) &st.n_vertices, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.v_p_u, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_n_v, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_s_wix, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_shn_wiy, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_alpha, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_em, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_nee, nv * sizeof(float4));
+    rc |= alloc((void **) &st.v_wiz_shape, nv * sizeof(float2));
+    rc |= alloc((void **) &st.queue[0], nv * sizeof(uint32_t));
+    rc |= alloc((void **) &st.queue[1], nv * sizeof(uint32_t));
+    rc |= alloc((void **) &st.queue_count, 2 * sizeof(uint32_t));
+    if (rc) { free_state(c); return rc; }
+    st.chunk = chunk;
+    st.counters = c->counters;
+    c->st_chunk = chunk; c->st_depth = depth;
+    return 0;
+}
+
+int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_params *prm, float *film_out, pltb_sample_dump *dump,
+                pltb_stats *stats) {
+    if (!c || !scene || !prm) return fail(PLTB_ERR_INVALID, "pltb_render: null argument");
+    if (scene->ctx != c) return fail(PLTB_ERR_INVALID, "pltb_render: scene belongs to another context");
+    if (prm->max_depth < 1 || prm->max_depth > PLTB_MAX_DEPTH) return fail(PLTB_ERR_INVALID, "max_depth must be in [1, 16]");
+    if (prm->rr_depth < 1) return fail(PLTB_ERR_INVALID, "\"rr_depth\" must be set to a value greater than zero!");
+    if (prm->spp == 0 || prm->spp_begin + prm->spp_count > prm->spp) return fail(PLTB_ERR_INVALID, "bad spp window");
+    const uint32_t W = scene->film_w, H = scene->film_h;
+    if ((uint64_t) W * H * prm->spp > (1ull << 32))
+        return fail(PLTB_ERR_INVALID, "The total number of Monte Carlo samples required by this rendering task exceeds 2^32 = "
+                                      "4294967296. Please use fewer samples per pixel or render using multiple passes.");
+    CU(cudaSetDevice(c->device));
+    c->cancel.store(0);
+    cudaStream_t s = c->stream;
+    const uint32_t cw = prm->crop_w ? prm->crop_w : W, ch = prm->crop_h ? prm->crop_h : H;
+    if (prm->crop_x + cw > W || prm->crop_y + ch > H) return fail(PLTB_ERR_INVALID, "crop window outside the film");
+    const uint64_t total = (uint64_t) cw * ch * prm->spp_count;
+    const uint64_t n_acc = (uint64_t) W * H * 4;
+    if (c->accum_floats != n_acc) {
+        cudaFree(c->accum); c->accum = nullptr;
+        CU(cudaMalloc(&c->accum, n_acc * sizeof(float)));
+        CU(cudaMemsetAsync(c->accum, 0, n_acc * sizeof(float), s));
+        c->accum_floats = n_acc;
+    }
+    uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(total, 1), 1u << 21);
+    if (int rc = ensure_state(c, chunk, prm->max_depth)) return rc;
+    PassState st = c->st;
+    st.chunk = c->st_chunk; st.max_depth = prm->max_depth; st.rr_depth = prm->rr_depth;
+    float *d_wl = nullptr, *d_L = nullptr; uint64_t dcap = 0;
+    if (dump && (dump->wavelengths || dump->radiance)) {
+        dcap = std::min<uint64_t>(dump->capacity, total);
+        if (c->dump_cap < dcap) {
+            cudaFree(c->dump_wl); cudaFree(c->dump_L); c->dump_wl = c->dump_L = nullptr; c->dump_cap = 0;
+            CU(cudaMalloc(&c->dump_wl, dcap * 4 * sizeof(float)));
+            CU(cudaMalloc(&c->dump_L, dcap * 4 * sizeof(float)));
+            c->dump_cap = dcap;
+        }
+        d_wl = c->dump_wl; d_L = c->dump_L;
+    }
+    uint64_t launches = 0;
+    CU(cudaEventRecord(c->ev[0], s));
+    CU(cudaMemsetAsync(c->counters, 0, 8 * sizeof(unsigned long long), s));
+    if (!(prm->flags & PLTB_RENDER_ACCUMULATE)) CU(cudaMemsetAsync(c->accum, 0, n_acc * sizeof(float), s));
+    PassParams pp{};
+    pp.seed = prm->seed; pp.spp = prm->spp; pp.spp_begin = prm->spp_begin; pp.spp_count = prm->spp_count;
+    pp.crop_x = prm->crop_x; pp.crop_y = prm->crop_y; pp.crop_w = cw; pp.crop_h = ch;
+    pp.film_w = W; pp.film_h = H;
+    const int nee_grid = c->sm_count * 8;
+    const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
+    for (uint64_t first = 0; first < total; first += st.chunk) {
+        if (c->cancel.load()) { cudaStreamSynchronize(s); return fail(PLTB_ERR_CANCELLED, "render cancelled"); }
+        pp.first = first;
+        pp.count = (uint32_t) std::min<uint64_t>(st.chunk, total - first);
+        CU(cudaMemsetAsync(st.queue_count, 0, 2 * sizeof(uint32_t), s));
+        launch_sample(scene->dev, st, pp, s);
+        launch_nee(scene->dev, st, 1, nee_grid, s);
+        launch_nee(scene->dev, st, 0, nee_grid, s);
+        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
+        launches += 4;
+    }
+    CU(cudaGetLastError());
+    if ((prm->flags & PLTB_RENDER_REDUCE) && c->world > 1) {
+        // one sum-reduce of the raw RGBW accumulator to rank 0 per render over NVLink
+        int r = g_nccl.Reduce(c->accum, c->accum, n_acc, /* ncclFloat32 */ 7, /* ncclSum */ 0, 0, c->comm, s);
+        if (r != 0) return fail(PLTB_ERR_CUDA, std::string("ncclReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error"));
+    }
+    const bool root = !(prm->flags & PLTB_RENDER_REDUCE) || c->rank == 0;
+    if (film_out && root) {
+        const float *src = c->accum; uint64_t n_out = n_acc;
+        if (prm->flags & PLTB_RENDER_DEVELOP) {
+            const uint64_t n_rgb = (uint64_t) W * H * 3;
+            if (c->rgb_floats != n_rgb) {
+                cudaFree(c->rgb); c->rgb = nullptr;
+                CU(cudaMalloc(&c->rgb, n_rgb * sizeof(float)));
+                c->rgb_floats = n_rgb;
+            }
+            launch_develop(c->accum, c->rgb, (uint64_t) W * H, s);
+            launches++;
+            src = c->rgb; n_out = n_rgb;
+        }
+        CU(cudaMemcpyAsync(film_out, src, n_out * sizeof(float),
+                           (prm->flags & PLTB_RENDER_DEVICE_OUT) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    }
+    if (dcap) {
+        if (dump->wavelengths) CU(cudaMemcpyAsync(dump->wavelengths, d_wl, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+        if (dump->radiance) CU(cudaMemcpyAsync(dump->radiance, d_L, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    CU(cudaEventRecord(c->ev[1], s));
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        unsigned long long h[8];
+        CU(cudaMemcpy(h, c->counters, sizeof(h), cudaMemcpyDeviceToHost));
+        stats->samples = total; stats->closest_rays = h[0]; stats->shadow_rays = h[1];
+        stats->vertices = h[2]; stats->grating_vertices = h[3];
+        stats->kernel_launches = launches;
+        CU(cudaEventElapsedTime(&stats->ms_total, c->ev[0], c->ev[1]));
+    }
+    return 0;
+}
+
+}  // extern "C"

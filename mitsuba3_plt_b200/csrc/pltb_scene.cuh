@@ -1,0 +1,240 @@
+// pltb_scene.cuh -- device-resident flattened scene: geometry SoA, 2-wide BVH, plugin tables, texture evaluation.
+// Layout in HBM (all tables are small and stay L1/L2-resident for the config scenes):
+//   bvh_nodes : float4[4] per node  {lo0.xyz,hi0.x}{hi0.yz,lo1.xy}{lo1.z,hi1.xyz}{child0,child1 as int bits}
+//   tri_data  : float4[3] per leaf-ordered primitive {p0.xyz,e1.x}{e1.yz,e2.xy}{e2.z, prim id, shape id, -}
+//   vertex arrays / faces as uploaded from pltb_scene_desc; plugin tables as arrays of the ABI structs.
+#pragma once
+#include "../../include/pltb.h"
+#include "pltb_math.cuh"
+
+#if defined(__CUDA_ARCH__)
+#  define PLTB_LDG(p) __ldg(p)
+#else
+#  define PLTB_LDG(p) (*(p))
+#endif
+#if !defined(__CUDACC__)
+struct float4 { float x, y, z, w; };
+struct float2 { float x, y; };
+#endif
+
+namespace pltb {
+
+struct DeviceScene {
+    const float4 *bvh_nodes;
+    const float4 *tri_data;
+    uint32_t n_nodes, n_prims;
+    const float *positions, *normals, *texcoords;
+    const uint32_t *faces, *face_shape;
+    const pltb_shape *shapes;
+    const pltb_bsdf *bsdfs;
+    const pltb_texture *textures;
+    const float *tex_data;
+    const pltb_emitter *emitters;
+    const float *area_cdf;
+    const pltb_sensor *sensors;
+    const float *cie_srgb;
+    pltb_film film;
+    uint32_t n_faces, n_shapes, n_emitters, n_sensors;
+    float emitter_pmf;
+    BesselTables bessel;
+};
+
+struct Ray { V3 o, d; float maxt; };
+struct Hit { float t, u, v; uint32_t prim; int32_t shape; };
+
+PLTB_HD V3 ld3(const float *p, uint32_t i) { return mk3(PLTB_LDG(p + 3 * i), PLTB_LDG(p + 3 * i + 1), PLTB_LDG(p + 3 * i + 2)); }
+PLTB_HD V2 ld2(const float *p, uint32_t i) { return mk2(PLTB_LDG(p + 2 * i), PLTB_LDG(p + 2 * i + 1)); }
+
+// Sphere / rectangle intersection (src/shapes/sphere.cpp:393-436 -- double precision as in the reference;
+// src/shapes/rectangle.cpp:262-283)
+PLTB_HD bool sphere_intersect(const pltb_shape &sh, const Ray &ray, float &t_out) {
+    double ox = (double) ray.o.x - (double) sh.center[0], oy = (double) ray.o.y - (double) sh.center[1],
+           oz = (double) ray.o.z - (double) sh.center[2];
+    double dx = ray.d.x, dy = ray.d.y, dz = ray.d.z, radius = sh.radius, maxt = ray.maxt;
+    double A = dx * dx + dy * dy + dz * dz, B = 2.0 * (ox * dx + oy * dy + oz * dz),
+           Cc = ox * ox + oy * oy + oz * oz - radius * radius;
+    if (A == 0.0) return false;
+    double discrim = B * B - 4.0 * A * Cc;
+    if (discrim < 0) return false;
+    double temp = -0.5 * (B + copysign(sqrt(discrim), B));
+    double x0p = temp / A, x1p = Cc / temp;
+    double near_t = fmin(x0p, x1p), far_t = fmax(x0p, x1p);
+    bool out_bounds = !(near_t <= maxt && far_t >= 0.0), in_bounds = near_t < 0.0 && far_t > maxt;
+    if (out_bounds || in_bounds) return false;
+    t_out = (float) (near_t < 0.0 ? far_t : near_t);
+    return true;
+}
+PLTB_HD bool rectangle_intersect(const pltb_shape &sh, const Ray &ray, float &t_out, float &u, float &v) {
+    V3 o = xf_point(sh.to_object, ray.o), d = xf_vector(sh.to_object, ray.d);
+    float t = -o.z / d.z;
+    V3 local = fmadd3(d, t, o);
+    bool active = t >= 0.f && t <= ray.maxt && fabsf(local.x) <= 1.f && fabsf(local.y) <= 1.f;
+    if (!active) return false;
+    t_out = t; u = local.x; v = local.y;
+    return true;
+}
+
+// Scene::ray_intersect / ray_test (src/render/scene.cpp:176-205) over our own BVH: short-stack traversal, ordered
+// descent, Moeller-Trumbore exactly as Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:460-481).
+template <bool AnyHit> PLTB_HD Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
+    Hit best; best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
+    if (sc.n_nodes == 0) return best;
+    const float ix = 1.f / ray.d.x, iy = 1.f / ray.d.y, iz = 1.f / ray.d.z;
+    int32_t stack[32];
+    int sp = 0;
+    int32_t node = 0;  // >= 0: inner node index; < 0: leaf ~(first | count << 24)
+    for (;;) {
+        if (node >= 0) {
+            const float4 *n = sc.bvh_nodes + 4 * (size_t) node;
+            float4 a = PLTB_LDG(n), b = PLTB_LDG(n + 1), c = PLTB_LDG(n + 2), d = PLTB_LDG(n + 3);
+            // child 0: lo (a.x a.y a.z) hi (a.w b.x b.y); child 1: lo (b.z b.w c.x) hi (c.y c.z c.w)
+            float t0x = (a.x - ray.o.x) * ix, t1x = (a.w - ray.o.x) * ix;
+            float t0y = (a.y - ray.o.y) * iy, t1y = (b.x - ray.o.y) * iy;
+            float t0z = (a.z - ray.o.z) * iz, t1z = (b.y - ray.o.z) * iz;
+            float n0 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+            float f0 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
+            t0x = (b.z - ray.o.x) * ix; t1x = (c.y - ray.o.x) * ix;
+            t0y = (b.w - ray.o.y) * iy; t1y = (c.z - ray.o.y) * iy;
+            t0z = (c.x - ray.o.z) * iz; t1z = (c.w - ray.o.z) * iz;
+            float n1 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+            float f1 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
+            // boxes are padded at build time; the 1 + 4 ulp factor keeps the slab test conservative
+            bool h0 = n0 <= f0 * 1.0000005f, h1 = n1 <= f1 * 1.0000005f;
+            int32_t c0 = (int32_t) f2u(d.x), c1 = (int32_t) f2u(d.y);
+            if (h0 && h1) {
+                if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
+                stack[sp++] = c1;
+                node = c0;
+                continue;
+            } else if (h0) { node = c0; continue; }
+            else if (h1) { node = c1; continue; }
+        } else {
+            uint32_t leaf = ~(uint32_t) node, first = leaf & 0xFFFFFFu, count = leaf >> 24;
+            for (uint32_t i = first; i < first + count; ++i) {
+                const float4 *tp = sc.tri_data + 3 * (size_t) i;
+                float4 q0 = PLTB_LDG(tp), q1 = PLTB_LDG(tp + 1), q2 = PLTB_LDG(tp + 2);
+                uint32_t prim = f2u(q2.y);
+                int32_t shape = (int32_t) f2u(q2.z);
+                float t, u = 0.f, v = 0.f;
+                bool hit;
+                if (prim < sc.n_faces) {
+                    V3 p0 = mk3(q0.x, q0.y, q0.z), e1 = mk3(q0.w, q1.x, q1.y), e2 = mk3(q1.z, q1.w, q2.x);
+                    V3 pvec = cross(ray.d, e2);
+                    float inv_det = rcp(dot(e1, pvec));
+                    V3 tvec = ray.o - p0;
+                    u = dot(tvec, pvec) * inv_det;
+                    hit = u >= 0.f && u <= 1.f;
+                    V3 qvec = cross(tvec, e1);
+                    v = dot(ray.d, qvec) * inv_det;
+                    hit &= v >= 0.f && u + v <= 1.f;
+                    t = dot(e2, qvec) * inv_det;
+                    hit &= t >= 0.f && t <= ray.maxt;
+                } else {
+                    const pltb_shape &sh = sc.shapes[shape];
+                    if (sh.type == PLTB_SHAPE_SPHERE) hit = sphere_intersect(sh, ray, t);
+                    else hit = rectangle_intersect(sh, ray, t, u, v);
+                }
+                if (hit && t < best.t) {
+                    best.t = t; best.u = u; best.v = v; best.prim = prim; best.shape = shape;
+                    if (AnyHit) return best;
+                    ray.maxt = t;
+                }
+            }
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+    return best;
+}
+
+// ---- textures / spectra -------------------------------------------------------------------------------------------------
+PLTB_HD float srgb_model_eval(const float *c, float wl) {  // include/mitsuba/render/srgb.h:9-23
+    float c0 = PLTB_LDG(c), c1 = PLTB_LDG(c + 1), c2 = PLTB_LDG(c + 2);
+    float v = fmadd(fmadd(c0, wl, c1), wl, c2);
+    if (isinf_(c2)) return fmadd(sign1(c2), .5f, .5f);
+    return fmaxf(0.f, fmadd(.5f * v, rsqrt_(fmadd(v, v, 1.f)), .5f));
+}
+PLTB_HD float regular_eval(const float *vals, uint32_t count, float lo, float hi, float x) {  // distr_1d.h:364-379
+    if (!(x >= lo && x <= hi)) return 0.f;
+    float inv_interval = rcp((hi - lo) / (float) (count - 1));
+    x = (x - lo) * inv_interval;
+    uint32_t index = (uint32_t) fmaxf(x, 0.f);
+    if (index > count - 2) index = count - 2;
+    float y0 = PLTB_LDG(vals + index), y1 = PLTB_LDG(vals + index + 1), w1 = x - (float) index, w0 = 1.f - w1;
+    return fmadd(w0, y0, w1 * y1);
+}
+PLTB_HD float irregular_eval(const float *nodes, const float *vals, uint32_t count, float x) {  // distr_1d.h:705-730
+    if (!(x >= nodes[0] && x <= nodes[count - 1])) return 0.f;
+    uint32_t a = 0, b = count;
+    while (a < b) { uint32_t m = (a + b) / 2; if (nodes[m] < x) a = m + 1; else b = m; }
+    uint32_t i0 = (a > 1u ? a : 1u) - 1u;
+    if (i0 > count - 2) i0 = count - 2;
+    float x0 = nodes[i0], x1 = nodes[i0 + 1], y0 = vals[i0], y1 = vals[i0 + 1];
+    float t = (x - x0) / (x1 - x0);
+    return fmadd(y1 - y0, t, y0);
+}
+PLTB_HD float blackbody_eval(float temperature, float wl) {  // src/spectra/blackbody.cpp:128-150
+    const float c = 2.99792458e+8f, h = 6.62607004e-34f, k = 1.38064852e-23f;
+    const float c0 = 2 * h * c * c, c1 = h * c / k;
+    float lambda = wl * 1e-9f, lambda2 = lambda * lambda, lambda5 = lambda2 * lambda2 * lambda;
+    return 1e-9f * c0 / (lambda5 * (expf(c1 / (lambda * temperature)) - 1.f));
+}
+PLTB_HD int wrap_coord(int pos, int shape, uint32_t mode) {  // ext/drjit/include/drjit/texture.h:1222-1250
+    if (mode == PLTB_WRAP_CLAMP) return pos < 0 ? 0 : (pos > shape - 1 ? shape - 1 : pos);
+    int shift_neg = pos < 0 ? pos + 1 : pos;
+    int div = shift_neg / shape;
+    int mod = pos - div * shape;
+    if (mod < 0) mod += shape;
+    if (mode == PLTB_WRAP_MIRROR && !(((div & 1) == 0) ^ (pos < 0))) mod = shape - 1 - mod;
+    return mod;
+}
+
+PLTB_HD S4 tex_eval(const DeviceScene &sc, int32_t id, const S4 &wl, V2 uv) {
+    if (id < 0) return s4(1.f);
+    const pltb_texture &t = sc.textures[id];
+    const float *data = sc.tex_data + t.offset;
+    S4 r = s4(0.f);
+    switch (t.type) {
+        case PLTB_TEX_UNIFORM: return s4(t.p[0]);
+        case PLTB_TEX_SRGB:
+            for (int i = 0; i < 4; ++i) r.v[i] = srgb_model_eval(t.p, wl.v[i]);
+            return r;
+        case PLTB_TEX_D65:
+            for (int i = 0; i < 4; ++i) {
+                float dv = regular_eval(data, t.count, t.p[3], t.p[4], wl.v[i]);
+                r.v[i] = (t.flags & 1u) ? dv * srgb_model_eval(t.p, wl.v[i]) : dv;
+            }
+            return r;
+        case PLTB_TEX_REGULAR:
+            for (int i = 0; i < 4; ++i) r.v[i] = regular_eval(data, t.count, t.p[3], t.p[4], wl.v[i]);
+            return r;
+        case PLTB_TEX_IRREGULAR:
+            for (int i = 0; i < 4; ++i) r.v[i] = irregular_eval(data, data + t.count, t.count, wl.v[i]);
+            return r;
+        case PLTB_TEX_BLACKBODY:
+            for (int i = 0; i < 4; ++i)
+                r.v[i] = (wl.v[i] >= t.p[3] && wl.v[i] <= t.p[4]) ? blackbody_eval(t.p[0], wl.v[i]) : 0.f;
+            return r;
+        case PLTB_TEX_BITMAP: {  // src/textures/bitmap.cpp:700-737
+            float u = fmadd(t.to_uv[1], uv.y, fmadd(t.to_uv[0], uv.x, t.to_uv[2])),
+                  v = fmadd(t.to_uv[4], uv.y, fmadd(t.to_uv[3], uv.x, t.to_uv[5]));
+            float pu = fmadd(u, (float) t.width, -.5f), pv = fmadd(v, (float) t.height, -.5f);
+            int iu = (int) floorf(pu), iv = (int) floorf(pv);
+            int x0 = wrap_coord(iu, (int) t.width, t.wrap), x1 = wrap_coord(iu + 1, (int) t.width, t.wrap),
+                y0 = wrap_coord(iv, (int) t.height, t.wrap), y1 = wrap_coord(iv + 1, (int) t.height, t.wrap);
+            const float *v00 = data + 3 * ((size_t) y0 * t.width + x0), *v10 = data + 3 * ((size_t) y0 * t.width + x1),
+                        *v01 = data + 3 * ((size_t) y1 * t.width + x0), *v11 = data + 3 * ((size_t) y1 * t.width + x1);
+            float w1x = pu - (float) iu, w0x = 1.f - w1x, w1y = pv - (float) iv, w0y = 1.f - w1y;
+            for (int i = 0; i < 4; ++i) {
+                float c00 = srgb_model_eval(v00, wl.v[i]), c10 = srgb_model_eval(v10, wl.v[i]),
+                      c01 = srgb_model_eval(v01, wl.v[i]), c11 = srgb_model_eval(v11, wl.v[i]);
+                float c0 = fmadd(w0x, c00, w1x * c10), c1 = fmadd(w0x, c01, w1x * c11);
+                r.v[i] = fmadd(w0y, c0, w1y * c1);
+            }
+            return r;
+        }
+        default: return r;
+    }
+}
+
+}  // namespace pltb

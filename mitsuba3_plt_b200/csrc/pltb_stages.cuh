@@ -1,0 +1,235 @@
+// pltb_stages.cuh -- bodies of the three wavefront stages (see pltb_integrator.cuh).  Written as host/device templates over
+// a queue-append policy so that tests can run the identical code on the host (tests/host_emul.cpp) -- the product only
+// instantiates them inside the CUDA kernels of pltb_kernels.cu.
+#pragma once
+#include "pltb_integrator.cuh"
+
+namespace pltb {
+
+PLTB_HD float4 mkf4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
+PLTB_HD float4 s4_to_f4(const S4 &s) { return mkf4(s.v[0], s.v[1], s.v[2], s.v[3]); }
+PLTB_HD S4 f4_to_s4(const float4 &f) { S4 s; s.v[0] = f.x; s.v[1] = f.y; s.v[2] = f.z; s.v[3] = f.w; return s; }
+
+// window-order sample index -> pixel / sample-in-pixel / reference lane index (common.py:256-266)
+PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32_t &y, uint32_t &s, uint32_t &idx) {
+    uint64_t pix = w / pp.spp_count;
+    s = (uint32_t) (w - pix * pp.spp_count) + pp.spp_begin;
+    uint32_t row = (uint32_t) (pix / pp.crop_w);
+    x = pp.crop_x + (uint32_t) (pix - (uint64_t) row * pp.crop_w);
+    y = pp.crop_y + row;
+    idx = (y * pp.film_w + x) * pp.spp + s;
+}
+
+template <class Queue>
+PLTB_HD void stage_sample(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Queue &queue,
+                          uint32_t cnt[4]) {
+    uint32_t x, y, s, idx;
+    decode_sample(pp, pp.first + local, x, y, s, idx);
+    // PCG32Sampler::seed (src/render/sampler.cpp:125-145)
+    uint32_t v0, v1;
+    sample_tea_32(pp.seed, idx, v0, v1);
+    PCG32 rng; rng.seed(v0, v1);
+    // ADIntegrator.sample_rays (common.py:231-309)
+    float jx = rng.next_float32(), jy = rng.next_float32();
+    V2 pos_f = mk2((float) x + jx, (float) y + jy);
+    float wav_sample = rng.next_float32();
+    const uint32_t fw = sc.film.width;
+    uint32_t sidx = x / fw;   // BatchSensor: film split in x (src/sensors/batch.cpp:131-190)
+    const pltb_sensor &sn = sc.sensors[sidx];
+    V2 pos_adj = mk2((pos_f.x - (float) (sidx * fw)) * rcp((float) fw), pos_f.y * rcp((float) pp.film_h));
+    S4 wl, wgt;
+    sample_wavelengths(sc, sn, wav_sample, wl, wgt);
+    Ray ray = sensor_ray(sn, pos_adj);
+    st.wl[local] = s4_to_f4(wl);
+    st.sensor_w[local] = s4_to_f4(wgt);
+    float2 fp; fp.x = pos_f.x; fp.y = pos_f.y;
+    st.film_pos[local] = fp;
+
+    // ---- plt_sample_phase (plt.py:50-171) ----
+    for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1)
+    S4 alpha = s4(1.f);
+    float eta = 1.f, last_nd_pdf = 1.f;
+    uint32_t depth = 0, i = 0;
+    bool active = true, prev_bsdf_delta = true;
+    V3 prev_p = mk3(0.f, 0.f, 0.f);
+    S4 w[PLTB_MAX_DEPTH];
+    while (active) {
+        Hit h = bvh_intersect<false>(sc, ray);
+        cnt[0]++;
+        SI si = make_si(sc, ray, h);
+        const bool valid = si.valid();
+        bool active_next = (depth + 1 < st.max_depth) && valid;
+        float sample_1 = rng.next_float32();
+        V2 sample_2, lobe_sample_2;
+        sample_2.x = rng.next_float32(); sample_2.y = rng.next_float32();
+        lobe_sample_2.x = rng.next_float32(); lobe_sample_2.y = rng.next_float32();
+        const pltb_bsdf *b = si_bsdf(sc, si.shape);
+        BSDFSampleOut so = wbsdf_sample(sc, b, si.wi, si.uv, wl, sample_1, sample_2, lobe_sample_2);
+
+        // replay_path for this vertex (plt.py:408-472): alpha_i = w_0 * (w_1 * (... * (w_{i-1} * 1)))
+        S4 ai = s4(1.f);
+        for (int j = (int) i - 1; j >= 0; --j) ai = w[j] * ai;
+        // solve_replay_emissive (plt.py:315-405)
+        S4 em = s4(0.f);
+        if (valid) {
+            int32_t em_id = sc.shapes[si.shape].emitter;
+            if (em_id >= 0) {
+                const pltb_emitter &e = sc.emitters[em_id];
+                float em_pdf = 0.f;
+                if (!prev_bsdf_delta) {   // Scene::pdf_emitter_direction -> AreaLight::pdf_direction (area.cpp:170-196)
+                    V3 rel = si.p - prev_p;
+                    float dist = norm(rel);
+                    V3 d = rel / dist;
+                    if (dot(d, si.sh.n) < 0.f) em_pdf = shape_pdf_direction(sc.shapes[e.shape], prev_p, d, si.sh.n, dist);
+                    em_pdf *= sc.emitter_pmf;
+                }
+                float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
+                S4 Le = si.wi.z > 0.f ? tex_eval(sc, e.radiance, wl, si.uv) : s4(0.f);   // AreaLight::eval (area.cpp:82-89)
+                em = ai * (Le * mis_bsdf);
+            }
+            w[i] = wbsdf_weight(sc, b, si.wi, si.uv, wl, so.wo);
+            cnt[2]++;
+            if (b && b->type == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
+        } else {
+            w[i] = s4(0.f);
+        }
+
+        ray = si.spawn_ray(si.sh.to_world(so.wo));
+        if (active_next) { alpha = so.weight * alpha; eta = so.eta; }
+        if (valid) depth += 1;
+        float alpha_max = smax(alpha);
+        active_next = active_next && alpha_max != 0.f;
+        float rr_prob = fminf(alpha_max * sqr(eta), 0.95f);
+        bool rr_active = depth >= st.rr_depth;
+        if (rr_active) alpha = alpha * rcp(rr_prob);
+        bool rr_continue = rng.next_float32() < rr_prob;
+        active_next = active_next && (!rr_active || rr_continue);
+
+        // bounce record
+        const size_t r = (size_t) i * st.chunk + local;
+        const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
+        st.v_em[r] = s4_to_f4(em);
+        if (nee) {
+            st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
+            st.v_n_v[r] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
+            st.v_s_wix[r] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
+            st.v_shn_wiy[r] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
+            st.v_alpha[r] = s4_to_f4(ai);
+            float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
+            st.v_wiz_shape[r] = ws;
+            queue.push((b->type == PLTB_BSDF_ROUGHGRATING) ? 1 : 0, local | (i << 27));
+        } else {
+            st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
+        }
+
+        last_nd_pdf = ((so.type & F_Delta) != 0) ? last_nd_pdf : so.pdf;
+        prev_bsdf_delta = (so.type & F_Delta) != 0;
+        prev_p = si.p;
+        active = active_next;
+        i += 1;
+    }
+    st.rng_state[local] = rng.state;
+    st.rng_inc[local] = rng.inc;
+    st.n_vertices[local] = i;
+}
+
+// solve_replay_NEE (plt.py:221-300) for one queued vertex
+PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entry, uint32_t cnt[4]) {
+    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = (size_t) depth * st.chunk + local;
+    float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r];
+    float2 ws = st.v_wiz_shape[r];
+    SI si;
+    si.t = 0.f;
+    si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z); si.uv = mk2(a0.w, a1.w);
+    si.sh.s = mk3(a2.x, a2.y, a2.z); si.sh.n = mk3(a3.x, a3.y, a3.z); si.sh.t = cross(si.sh.n, si.sh.s);
+    si.wi = mk3(a2.w, a3.w, ws.x);
+    si.shape = (int32_t) f2u(ws.y);
+    const S4 wl = f4_to_s4(st.wl[local]);
+    PCG32 rng; rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local];
+    for (uint32_t k = 0; k < 2 * depth; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
+    V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
+
+    // Scene::sample_emitter_direction (src/render/scene.cpp:294-348) + sample_emitter (:222-245)
+    uint32_t index = 0;
+    if (sc.n_emitters > 1) {
+        float cf = (float) sc.n_emitters, scaled = sample.x * cf;
+        index = (uint32_t) scaled;
+        if (index > sc.n_emitters - 1u) index = sc.n_emitters - 1u;
+        sample.x = scaled - (float) index;
+    }
+    const pltb_emitter &em = sc.emitters[index];
+    DirectionSample ds;
+    if (em.type == PLTB_EMITTER_AREA) {
+        ds = shape_sample_direction(sc, sc.shapes[em.shape], si.p, sample);   // AreaLight::sample_direction (area.cpp:116-168)
+    } else {   // DirectionalEmitter::sample_direction (src/emitters/directional.cpp:149-176)
+        V3 dirn = mk3(em.direction[0], em.direction[1], em.direction[2]);
+        ds.d = -dirn;
+        float dist = 2.f * em.bsphere_radius;
+        ds.p = fmadd3(ds.d, dist, si.p);
+        ds.n = dirn; ds.pdf = 1.f; ds.delta = true; ds.dist = dist; ds.uv = mk2(0.f, 0.f);
+    }
+    ds.pdf *= sc.emitter_pmf;
+    if (ds.pdf != 0.f) {
+        cnt[1]++;
+        Hit sh = bvh_intersect<true>(sc, si.spawn_ray_to(ds.p));
+        if (sh.shape >= 0) ds.pdf = 0.f;
+    }
+    ds.d = normalize(ds.p - si.p);   // plt.py:264-269
+    S4 em_val = s4(0.f);
+    if (em.type == PLTB_EMITTER_AREA) { if (dot(ds.d, ds.n) < 0.f) em_val = tex_eval(sc, em.radiance, wl, ds.uv); }
+    else em_val = tex_eval(sc, em.radiance, wl, ds.uv);
+    S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
+    V3 wo = si.sh.to_local(ds.d);
+    const pltb_bsdf *b = si_bsdf(sc, si.shape);
+    S4 bsdf_val = wbsdf_eval(sc, b, si.wi, si.uv, wl, wo);
+    float bsdf_pdf = wbsdf_pdf(sc, b, si.wi, si.uv, wl, wo);
+    float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
+    S4 a = f4_to_s4(st.v_alpha[r]);
+    st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
+}
+
+// plt_solve_phase accumulation order (plt.py:191-216) + _splat_to_block (common.py:370-397); returns L
+template <class Film>
+PLTB_HD S4 stage_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Film &film, bool do_splat) {
+    S4 L = s4(0.f);
+    const uint32_t n = st.n_vertices[local];
+    for (uint32_t i = 0; i < n; ++i) {
+        const size_t r = (size_t) i * st.chunk + local;
+        L = L + f4_to_s4(st.v_em[r]);
+        L = L + f4_to_s4(st.v_nee[r]);
+    }
+    if (!do_splat) return L;
+    const S4 wl = f4_to_s4(st.wl[local]);
+    float values[4];
+    spectrum_to_srgb(sc.cie_srgb, L * f4_to_s4(st.sensor_w[local]), wl, values);
+    values[3] = 1.f;
+    const float2 pos = st.film_pos[local];
+    const int W = (int) pp.film_w, H = (int) pp.film_h;
+    if (sc.film.rfilter == PLTB_RFILTER_BOX) {
+        int px = (int) floorf(pos.x), py = (int) floorf(pos.y);
+        if (px >= 0 && py >= 0 && px < W && py < H) film.add((size_t) py * W + px, values, 1.f);
+        return L;
+    }
+    // ImageBlock::put, coalesced path (src/render/imageblock.cpp:429-500)
+    const int nr = (int) ceilf(sc.film.radius - .5f), count = 2 * nr + 1;
+    const int px = (int) floorf(pos.x) - nr, py = (int) floorf(pos.y) - nr;
+    float relx = ((float) px + .5f) - pos.x, rely = ((float) py + .5f) - pos.y;
+    float wx[9], wy[9];
+    for (int k = 0; k < count && k < 9; ++k) {
+        wx[k] = rfilter_eval(sc.film, relx); wy[k] = rfilter_eval(sc.film, rely);
+        relx += 1; rely += 1;
+    }
+    for (int ys = 0; ys < count && ys < 9; ++ys) {
+        int yy = py + ys;
+        if (yy < 0 || yy >= H) continue;
+        for (int xs = 0; xs < count && xs < 9; ++xs) {
+            int xx = px + xs;
+            if (xx < 0 || xx >= W) continue;
+            film.add((size_t) yy * W + xx, values, wy[ys] * wx[xs]);
+        }
+    }
+    return L;
+}
+
+}  // namespace pltb
