@@ -1,0 +1,28 @@
+"""Shared parity metrics (north star): per-sample spectral radiance within 1e-4 relative error on >= 99.9 % of samples;
+converged-image relative MSE <= 1 %."""
+import numpy as np
+
+REL_TOL = 1e-4          # north_star: "per-sample spectral radiance must agree to within 1e-4 relative error"
+MIN_FRACTION = 0.999    # "... on >= 99.9 % of samples"
+MAX_RMSE = 0.01         # "converged image at equal spp must have relative MSE <= 1 %"
+
+
+def sample_agreement(a, b):
+    """fraction of samples whose 4 spectral radiance values all agree (NaN == NaN: the reference propagates NaNs of
+    invalid diffraction lobes, DESIGN.md "Reference quirks kept")"""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    both_nan = np.isnan(a) & np.isnan(b)
+    with np.errstate(invalid="ignore"):
+        err = np.abs(a - b) / np.maximum(np.abs(b), 1e-6)
+        ok = (err <= REL_TOL) | both_nan
+    return ok.all(axis=1).mean()
+
+
+def relative_mse(img, ref):
+    """mean((img - ref)^2 / (ref^2 + 1e-2)) over the pixels finite in both images; also returns the fraction of pixels
+    whose finiteness differs"""
+    img, ref = np.asarray(img, np.float64), np.asarray(ref, np.float64)
+    fin = np.isfinite(img).all(-1) & np.isfinite(ref).all(-1)
+    mism = (np.isfinite(img).all(-1) != np.isfinite(ref).all(-1)).mean()
+    d = img[fin] - ref[fin]
+    return float(np.mean(d * d / (ref[fin] ** 2 + 1e-2))), float(mism)
