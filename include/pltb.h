@@ -182,7 +182,8 @@ enum {
     PLTB_RENDER_REDUCE = 2,       /* sum the accumulator over all ranks of the context before develop */
     PLTB_RENDER_DEVICE_OUT = 4,   /* film_out is a device pointer */
     PLTB_RENDER_ACCUMULATE = 8,   /* do not clear the accumulator first (multi-pass renders) */
-    PLTB_RENDER_NO_SPLAT = 16     /* skip the film (per-sample dump only) */
+    PLTB_RENDER_NO_SPLAT = 16,    /* skip the film (per-sample dump only) */
+    PLTB_RENDER_PROFILE = 32      /* bracket every kernel with CUDA events and fill the per-kernel ms_* fields of pltb_stats */
 };
 
 typedef struct pltb_render_params {
@@ -213,8 +214,10 @@ typedef struct pltb_stats {
     uint64_t kernel_launches;
     uint64_t vertices;          /* recorded bounce vertices (sum of path depths) */
     uint64_t grating_vertices;  /* of which on a roughgrating BSDF */
+    uint64_t nee_other, nee_grating; /* NEE work items processed by the two k_nee launches (queue sizes) */
     float ms_total;             /* device time of the whole call (CUDA events) */
-    float ms_raygen, ms_trace, ms_shade, ms_solve, ms_splat, ms_develop, ms_reduce;
+    /* per-kernel device time, summed over passes; filled only with PLTB_RENDER_PROFILE */
+    float ms_sample, ms_nee_grating, ms_nee_other, ms_splat, ms_develop, ms_reduce, ms_copy;
 } pltb_stats;
 
 typedef struct pltb_context pltb_context;

@@ -247,7 +247,7 @@ class PLTIntegrator:
             capi.lib().pltb_cancel(self._cancel_ctx._h)
 
     def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, *, ctx=None, dump=None, crop=None,
-               reduce=True):
+               reduce=True, profile=False, download=True, out=None):
         """Returns the developed image (H, W, 3) float32, or the raw RGBW accumulator (H, W, 4) if develop=False.
         `dump`: optional dict that receives per-sample 'wavelengths' and 'radiance' arrays (parity mode).
         Multi-GPU: the spp range is sharded over the ranks of `ctx`; rank 0 returns the image, the others None."""
@@ -272,7 +272,12 @@ class PLTIntegrator:
             raise RuntimeError(f"render(): spp={spp} exceeds the 2^32 wavefront limit and is not divisible into "
                                f"{n_sub} equal sub-renders")
         sub_spp = spp // n_sub
-        out = np.empty((H, W, 3 if develop else 4), np.float32) if (ctx.rank == 0 or not reduce) else None
+        shape = (H, W, 3 if develop else 4)
+        if out is not None:
+            if out.shape != shape or out.dtype != np.float32 or not out.flags.c_contiguous:
+                raise RuntimeError(f"render(): `out` must be a C-contiguous float32 array of shape {shape}")
+        elif ctx.rank == 0 or not reduce:
+            out = np.empty(shape, np.float32)
         total = capi.Stats()
         self._cancel_ctx = ctx
         try:
@@ -295,6 +300,8 @@ class PLTIntegrator:
                     flags |= capi.RENDER_REDUCE
                 if last and develop:
                     flags |= capi.RENDER_DEVELOP
+                if profile:
+                    flags |= capi.RENDER_PROFILE
                 prm.flags = flags
                 dmp = None
                 if dump is not None and last:
@@ -304,14 +311,14 @@ class PLTIntegrator:
                     dump["radiance"] = np.zeros((n, 4), np.float32)
                     dmp = capi.SampleDump(capi.fptr(dump["wavelengths"]), capi.fptr(dump["radiance"]), None, n)
                 st = capi.Stats()
-                dst = out.ctypes.data if (last and out is not None) else None
+                dst = out.ctypes.data if (last and out is not None and download) else None
                 capi.check(L.pltb_render(ctx._h, dev, C.byref(prm), dst, C.byref(dmp) if dmp else None, C.byref(st)))
                 for f, _ in capi.Stats._fields_:
                     setattr(total, f, getattr(total, f) + getattr(st, f))
         finally:
             self._cancel_ctx = None
         self.last_stats = total.as_dict()
-        return out
+        return out if download else None
 
     def sample(self, *a, **kw):
         raise RuntimeError("PLTIntegrator.sample() is inlined into the CUDA wavefront kernels; use render()")

@@ -25,7 +25,7 @@ SHAPE_HAS_NORMALS, SHAPE_HAS_UV, SHAPE_FLIP_NORMALS = 1, 2, 4
 EMITTER_AREA, EMITTER_DIRECTIONAL = 0, 1
 SENSOR_PERSPECTIVE, SENSOR_ORTHOGRAPHIC = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = range(3)
-RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT = 1, 2, 4, 8, 16
+RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT, RENDER_PROFILE = 1, 2, 4, 8, 16, 32
 
 f32, u32, i32, u64 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64
 PF, PU = C.POINTER(f32), C.POINTER(u32)
@@ -80,8 +80,9 @@ class SampleDump(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("samples", u64), ("closest_rays", u64), ("shadow_rays", u64), ("kernel_launches", u64),
-                ("vertices", u64), ("grating_vertices", u64), ("ms_total", f32), ("ms_raygen", f32), ("ms_trace", f32),
-                ("ms_shade", f32), ("ms_solve", f32), ("ms_splat", f32), ("ms_develop", f32), ("ms_reduce", f32)]
+                ("vertices", u64), ("grating_vertices", u64), ("nee_other", u64), ("nee_grating", u64),
+                ("ms_total", f32), ("ms_sample", f32), ("ms_nee_grating", f32),
+                ("ms_nee_other", f32), ("ms_splat", f32), ("ms_develop", f32), ("ms_reduce", f32), ("ms_copy", f32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -67,6 +67,7 @@ struct pltb_context {
     float *dump_wl = nullptr, *dump_L = nullptr; uint64_t dump_cap = 0;
     int sm_count = 148;
     cudaEvent_t ev[2] = { nullptr, nullptr };
+    std::vector<cudaEvent_t> prof;   // PLTB_RENDER_PROFILE: 5 events per pass + 4 for the tail
 };
 
 struct pltb_scene {
@@ -139,6 +140,7 @@ void pltb_context_destroy(pltb_context *c) {
     free_state(c);
     cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
     cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
+    for (cudaEvent_t e : c->prof) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -298,6 +300,13 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         d_wl = c->dump_wl; d_L = c->dump_L;
     }
     uint64_t launches = 0;
+    const bool profile = (prm->flags & PLTB_RENDER_PROFILE) != 0;
+    const uint64_t n_pass = (total + st.chunk - 1) / st.chunk;
+    if (profile) {
+        while (c->prof.size() < 5 * n_pass + 4) { cudaEvent_t e; CU(cudaEventCreate(&e)); c->prof.push_back(e); }
+    }
+    size_t pe = 0;
+#define PROF() do { if (profile) CU(cudaEventRecord(c->prof[pe++], s)); } while (0)
     CU(cudaEventRecord(c->ev[0], s));
     CU(cudaMemsetAsync(c->counters, 0, 8 * sizeof(unsigned long long), s));
     if (!(prm->flags & PLTB_RENDER_ACCUMULATE)) CU(cudaMemsetAsync(c->accum, 0, n_acc * sizeof(float), s));
@@ -312,18 +321,25 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         pp.first = first;
         pp.count = (uint32_t) std::min<uint64_t>(st.chunk, total - first);
         CU(cudaMemsetAsync(st.queue_count, 0, 2 * sizeof(uint32_t), s));
+        PROF();
         launch_sample(scene->dev, st, pp, s);
+        PROF();
         launch_nee(scene->dev, st, 1, nee_grid, s);
+        PROF();
         launch_nee(scene->dev, st, 0, nee_grid, s);
+        PROF();
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
+        PROF();
         launches += 4;
     }
     CU(cudaGetLastError());
+    PROF();   // tail event 0
     if ((prm->flags & PLTB_RENDER_REDUCE) && c->world > 1) {
         // one sum-reduce of the raw RGBW accumulator to rank 0 per render over NVLink
         int r = g_nccl.Reduce(c->accum, c->accum, n_acc, /* ncclFloat32 */ 7, /* ncclSum */ 0, 0, c->comm, s);
         if (r != 0) return fail(PLTB_ERR_CUDA, std::string("ncclReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error"));
     }
+    PROF();   // tail event 1: after the reduce
     const bool root = !(prm->flags & PLTB_RENDER_REDUCE) || c->rank == 0;
     if (film_out && root) {
         const float *src = c->accum; uint64_t n_out = n_acc;
@@ -338,6 +354,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
             launches++;
             src = c->rgb; n_out = n_rgb;
         }
+        PROF();   // tail event 2: after develop
         CU(cudaMemcpyAsync(film_out, src, n_out * sizeof(float),
                            (prm->flags & PLTB_RENDER_DEVICE_OUT) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
     }
@@ -345,6 +362,8 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         if (dump->wavelengths) CU(cudaMemcpyAsync(dump->wavelengths, d_wl, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
         if (dump->radiance) CU(cudaMemcpyAsync(dump->radiance, d_L, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
     }
+    if (!(film_out && root)) PROF();
+    PROF();   // tail event 3: after the copies
     CU(cudaEventRecord(c->ev[1], s));
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
@@ -354,8 +373,23 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         CU(cudaMemcpy(h, c->counters, sizeof(h), cudaMemcpyDeviceToHost));
         stats->samples = total; stats->closest_rays = h[0]; stats->shadow_rays = h[1];
         stats->vertices = h[2]; stats->grating_vertices = h[3];
+        stats->nee_other = h[4]; stats->nee_grating = h[5];
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, c->ev[0], c->ev[1]));
+        if (profile) {
+            float ms;
+            for (uint64_t p = 0; p < n_pass; ++p) {
+                cudaEvent_t *e = &c->prof[5 * p];
+                CU(cudaEventElapsedTime(&ms, e[0], e[1])); stats->ms_sample += ms;
+                CU(cudaEventElapsedTime(&ms, e[1], e[2])); stats->ms_nee_grating += ms;
+                CU(cudaEventElapsedTime(&ms, e[2], e[3])); stats->ms_nee_other += ms;
+                CU(cudaEventElapsedTime(&ms, e[3], e[4])); stats->ms_splat += ms;
+            }
+            cudaEvent_t *t = &c->prof[5 * n_pass];
+            CU(cudaEventElapsedTime(&stats->ms_reduce, t[0], t[1]));
+            CU(cudaEventElapsedTime(&stats->ms_develop, t[1], t[2]));
+            CU(cudaEventElapsedTime(&stats->ms_copy, t[2], t[3]));
+        }
     }
     return 0;
 }

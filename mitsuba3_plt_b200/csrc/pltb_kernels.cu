@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(128) k_nee(const __grid_constant__ DeviceScene
     const uint32_t n = st.queue_count[which];
     const uint32_t *queue = st.queue[which];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + which, (unsigned long long) n);   // queue sizes
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_nee(sc, st, queue[e], cnt);
     flush_counters(cnt, st.counters);
