@@ -14,12 +14,12 @@ PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, 
 }
 
 // wi already has the twosided flip applied.
-PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
-                                        V2 lobe_s2) {
+PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl,
+                                        float s1, V2 s2, V2 lobe_s2) {
     BSDFSampleOut o;
     o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f);
     const float cos_theta_i = wi.z;
-    switch (b.type) {
+    switch (type) {
         case PLTB_BSDF_DIFFUSE: {  // src/bsdfs/diffuse.cpp:101-125
             if (!(cos_theta_i > 0.f)) return o;
             o.wo = square_to_cosine_hemisphere(s2);
@@ -164,9 +164,9 @@ PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv,
     return F * result;
 }
 
-PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
-    switch (b.type) {
+    switch (type) {
         case PLTB_BSDF_DIFFUSE:  // diffuse.cpp:127-142
             if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return s4(0.f);
             return (tex_eval(sc, b.tex[0], wl, uv) * kInvPi) * cos_theta_o;
@@ -186,9 +186,9 @@ PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 
     }
 }
 
-PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
-    switch (b.type) {
+    switch (type) {
         case PLTB_BSDF_DIFFUSE: return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? kInvPi * wo.z : 0.f;
         case PLTB_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:392-430
             V3 m = normalize(wo + wi);
@@ -206,8 +206,8 @@ PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V
     }
 }
 
-PLTB_HD S4 bsdf_weight_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
-    switch (b.type) {
+PLTB_HD S4 bsdf_weight_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    switch (type) {
         case PLTB_BSDF_DIFFUSE: return tex_eval(sc, b.tex[0], wl, uv);  // diffuse.cpp:182-200
         case PLTB_BSDF_CONDUCTOR:  // conductor.cpp:320-376
             if (!(wi.z > 0.f)) return s4(0.f);
@@ -221,7 +221,7 @@ PLTB_HD S4 bsdf_weight_inner(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V
         case PLTB_BSDF_ROUGHCONDUCTOR:
         case PLTB_BSDF_ROUGHGRATING: {  // base wbsdf_weight, src/render/bsdf.cpp:85-97
             S4 e; float p;
-            rough_eval_pdf(sc, b, wi, uv, wl, wo, b.type == PLTB_BSDF_ROUGHCONDUCTOR, e, p);
+            rough_eval_pdf(sc, b, wi, uv, wl, wo, type == PLTB_BSDF_ROUGHCONDUCTOR, e, p);
             return p > 0.0f ? e / p : s4(0.f);
         }
         default: return s4(0.f);
@@ -234,35 +234,48 @@ PLTB_HD const pltb_bsdf *si_bsdf(const DeviceScene &sc, int32_t shape) {
     int32_t id = sc.shapes[shape].bsdf;
     return id < 0 ? nullptr : sc.bsdfs + id;
 }
+template <int Class> PLTB_HD uint32_t class_type(const pltb_bsdf *b) {
+    if (Class == 1) return PLTB_BSDF_ROUGHGRATING;
+    uint32_t t = b->type;
+#if defined(__CUDA_ARCH__)
+    if (Class == 0 && t == PLTB_BSDF_ROUGHGRATING) __builtin_unreachable();
+#endif
+    return t;
+}
+template <int Class = -1>
 PLTB_HD BSDFSampleOut wbsdf_sample(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
                                    V2 lobe_s2) {
     if (!b) { BSDFSampleOut o; o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f); return o; }
+    const uint32_t type = class_type<Class>(b);
     if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) {
         float wz = wi.z;
         wi.z = fabsf(wi.z);
-        BSDFSampleOut o = bsdf_sample_inner(sc, *b, wi, uv, wl, s1, s2, lobe_s2);
+        BSDFSampleOut o = bsdf_sample_inner(sc, *b, type, wi, uv, wl, s1, s2, lobe_s2);
         o.wo.z = mulsign(o.wo.z, wz);
         return o;
     }
-    return bsdf_sample_inner(sc, *b, wi, uv, wl, s1, s2, lobe_s2);
+    return bsdf_sample_inner(sc, *b, type, wi, uv, wl, s1, s2, lobe_s2);
 }
 PLTB_HD void twosided_flip(const pltb_bsdf *b, V3 &wi, V3 &wo) {
     if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
 }
+template <int Class = -1>
 PLTB_HD S4 wbsdf_eval(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     if (!b) return s4(0.f);
     twosided_flip(b, wi, wo);
-    return bsdf_eval_inner(sc, *b, wi, uv, wl, wo);
+    return bsdf_eval_inner(sc, *b, class_type<Class>(b), wi, uv, wl, wo);
 }
+template <int Class = -1>
 PLTB_HD float wbsdf_pdf(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     if (!b) return 0.f;
     twosided_flip(b, wi, wo);
-    return bsdf_pdf_inner(sc, *b, wi, uv, wl, wo);
+    return bsdf_pdf_inner(sc, *b, class_type<Class>(b), wi, uv, wl, wo);
 }
+template <int Class = -1>
 PLTB_HD S4 wbsdf_weight(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     if (!b) return s4(0.f);
     twosided_flip(b, wi, wo);
-    return bsdf_weight_inner(sc, *b, wi, uv, wl, wo);
+    return bsdf_weight_inner(sc, *b, class_type<Class>(b), wi, uv, wl, wo);
 }
 
 }  // namespace pltb

@@ -242,6 +242,16 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
     rc |= alloc((void **) &st.rng_state, chunk * sizeof(uint64_t));
     rc |= alloc((void **) &st.rng_inc, chunk * sizeof(uint64_t));
     rc |= alloc((void **) &st.n_vertices, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.p_ray_o, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.p_ray_d, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.p_hit, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.p_alpha, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.p_prev, chunk * sizeof(float4));
+    rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.v_w, nv * sizeof(float4));
+    rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.shade_q[0], chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.shade_q[1], chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.v_p_u, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_n_v, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_s_wix, nv * sizeof(float4));
@@ -252,7 +262,7 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
     rc |= alloc((void **) &st.v_wiz_shape, nv * sizeof(float2));
     rc |= alloc((void **) &st.queue[0], nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.queue[1], nv * sizeof(uint32_t));
-    rc |= alloc((void **) &st.queue_count, 2 * sizeof(uint32_t));
+    rc |= alloc((void **) &st.counts, kCountsTotal * sizeof(uint32_t));
     if (rc) { free_state(c); return rc; }
     st.chunk = chunk;
     st.counters = c->counters;
@@ -314,15 +324,22 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     pp.seed = prm->seed; pp.spp = prm->spp; pp.spp_begin = prm->spp_begin; pp.spp_count = prm->spp_count;
     pp.crop_x = prm->crop_x; pp.crop_y = prm->crop_y; pp.crop_w = cw; pp.crop_h = ch;
     pp.film_w = W; pp.film_h = H;
-    const int nee_grid = c->sm_count * 8;
+    const int nee_grid = c->sm_count * 8, wf_grid = c->sm_count * 8;
     const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
     for (uint64_t first = 0; first < total; first += st.chunk) {
         if (c->cancel.load()) { cudaStreamSynchronize(s); return fail(PLTB_ERR_CANCELLED, "render cancelled"); }
         pp.first = first;
         pp.count = (uint32_t) std::min<uint64_t>(st.chunk, total - first);
-        CU(cudaMemsetAsync(st.queue_count, 0, 2 * sizeof(uint32_t), s));
+        CU(cudaMemsetAsync(st.counts, 0, kCountsTotal * sizeof(uint32_t), s));
         PROF();
-        launch_sample(scene->dev, st, pp, s);
+        // sample phase as dense per-bounce wavefronts: raygen + trace(0), then shade(i) / trace(i + 1)
+        launch_raygen(scene->dev, st, pp, s);
+        for (uint32_t b = 0; b < prm->max_depth; ++b) {
+            launch_shade(scene->dev, st, b, 1, wf_grid, s);
+            launch_shade(scene->dev, st, b, 0, wf_grid, s);
+            launches += 2;
+            if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches++; }
+        }
         PROF();
         launch_nee(scene->dev, st, 1, nee_grid, s);
         PROF();

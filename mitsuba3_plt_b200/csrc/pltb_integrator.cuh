@@ -1,12 +1,13 @@
-// pltb_integrator.cuh -- the three wavefront stages of one render pass (DESIGN.md "Kernels"):
-//   stage 1  k_sample : one thread per Monte-Carlo sample.  Ray generation (PCG32/TEA seeding, pixel jitter, wavelength
-//                       sampling, sensor ray), then PLTIntegrator.plt_sample_phase: BVH closest hit, surface interaction,
-//                       wbsdf_sample, RR, and -- because every replay weight depends only on the vertex itself --
-//                       the per-vertex replay weight w_i, the replayed throughput alpha_i and the MIS-weighted emissive
-//                       term.  Writes one vertex record per bounce (SoA by depth) and appends NEE work items to two queues
-//                       (grating / other) with warp-aggregated atomics.
-//   stage 2  k_nee    : one thread per queued vertex.  solve_replay_NEE: emitter sampling, shadow ray, wbsdf_eval, wbsdf_pdf.
-//   stage 3  k_splat  : one thread per sample.  Sums the contributions in the reference's order, spectrum -> sRGB, film splat.
+// pltb_integrator.cuh -- emitter / sensor / film helpers and the wavefront state of one render pass (DESIGN.md "Kernels"):
+//   k_raygen          one thread per Monte-Carlo sample: PCG32/TEA seeding, pixel jitter, wavelength sampling, sensor ray,
+//                     then the bounce-0 closest-hit traversal; hits are appended to the shade queue of their material class.
+//   k_shade<class>(i) one thread per hit of bounce i (dense, one material class per launch): surface interaction,
+//                     wbsdf_sample, and -- because every replay weight depends only on the vertex itself -- the
+//                     replay weight w_i, the replayed throughput alpha_i and the MIS-weighted emissive term; RR; bounce
+//                     record; NEE work item; continuing paths are appended to the live list.
+//   k_trace(i)        one thread per live path: BVH closest hit for bounce i >= 1; misses are finalised in place.
+//   k_nee<class>      one thread per queued vertex.  solve_replay_NEE: emitter sampling, shadow ray, wbsdf_eval, wbsdf_pdf.
+//   k_splat           one thread per sample.  Sums the contributions in the reference's order, spectrum -> sRGB, film splat.
 // Reference: scripts/rendering/integrators/plt.py:50-529, src/python/python/ad/integrators/common.py:231-397.
 #pragma once
 #include "pltb_bsdf.cuh"
@@ -213,8 +214,8 @@ PLTB_HD float rfilter_eval(const pltb_film &f, float x) {  // gaussian.cpp:94-10
 }
 
 // ---- wavefront state ------------------------------------------------------------------------------------------------------------
-// Vertex records are SoA by depth: index = depth * chunk + sample_local, so that stage-1 writes and stage-2/3 reads of a
-// warp are coalesced float4 accesses.
+// All arrays are SoA.  Per-sample and per-path arrays are indexed by the sample's local id in the pass; vertex records are
+// depth-major (index = depth * chunk + sample_local) so that accesses of a warp are coalesced float4s.
 struct PassState {
     uint32_t chunk;            // samples per pass (capacity of every per-sample array)
     uint32_t max_depth, rr_depth;
@@ -222,20 +223,34 @@ struct PassState {
     float4 *wl;                // sampled wavelengths
     float4 *sensor_w;          // sensor spectral weight
     float2 *film_pos;          // splat position
-    uint64_t *rng_state, *rng_inc;   // PCG32 after the sample phase (NEE draws continue from here)
+    uint64_t *rng_state, *rng_inc;   // PCG32 state (advanced bounce by bounce; NEE draws continue from the final state)
     uint32_t *n_vertices;      // bounce records written
+    // per path, carried from bounce to bounce
+    float4 *p_ray_o;           // {ray.o, ray.maxt}
+    float4 *p_ray_d;           // {ray.d, eta}
+    float4 *p_hit;             // {t, u, v, prim id bits} of the closest hit found by k_trace
+    float4 *p_alpha;           // sample-phase throughput alpha
+    float4 *p_prev;            // {prev_si.p, last_nd_pdf}
+    uint32_t *p_flags;         // bit 0: prev_bsdf_delta
     // per vertex (depth-major)
+    float4 *v_w;               // replay weight w_i = wbsdf_weight(si_i, wo_i)
     float4 *v_p_u, *v_n_v, *v_s_wix, *v_shn_wiy;   // {p, uv.x} {n, uv.y} {sh.s, wi.x} {sh.n, wi.y}
     float4 *v_alpha;           // replayed throughput alpha_i
     float4 *v_em;              // MIS-weighted emissive contribution alpha_i * Lem_i
-    float4 *v_nee;             // NEE contribution (stage 2)
+    float4 *v_nee;             // NEE contribution (k_nee)
     float2 *v_wiz_shape;       // {wi.z, shape id bits}
-    // NEE work queues: entry = sample_local | depth << 27
-    uint32_t *queue[2];        // 0: non-grating, 1: roughgrating
-    uint32_t *queue_count;     // [2]
+    // work lists (path ids), filled with warp-aggregated atomics
+    uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
+    uint32_t *shade_q[2];      // hits of the current bounce by material class: 0 everything else, 1 roughgrating
+    uint32_t *queue[2];        // NEE work items of the whole pass: entry = sample_local | depth << 27
+    // counters, zeroed once per pass: [4 * i + 0] live count of bounce i, [4 * i + 1 + c] shade_q[c] count of bounce i;
+    // the NEE queue counts sit at [4 * PLTB_MAX_DEPTH + 4 + c]
+    uint32_t *counts;
     // statistics
-    unsigned long long *counters;  // closest, shadow, vertices, grating vertices
+    unsigned long long *counters;  // closest, shadow, vertices, grating vertices, nee_other, nee_grating
 };
+constexpr int kCountsNee = 4 * PLTB_MAX_DEPTH + 4;
+constexpr int kCountsTotal = kCountsNee + 2;
 
 struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;
@@ -243,10 +258,6 @@ struct PassParams {
     uint32_t film_w, film_h;       // whole film (n_sensors * film.width, film.height)
     uint64_t first;                // first sample (in window order) of this pass
     uint32_t count;                // samples in this pass
-};
-
-struct PathVertexOut {   // what stage 1 hands to the record writer
-    SI si; uint32_t flags; S4 alpha, em; bool nee; bool grating;
 };
 
 }  // namespace pltb

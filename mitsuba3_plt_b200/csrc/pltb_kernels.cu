@@ -1,6 +1,8 @@
 // pltb_kernels.cu -- sm_100a kernels of the plt render path and their launchers.
-//   k_sample : stage 1 (ray generation + sample phase), one thread per Monte-Carlo sample
-//   k_nee    : stage 2 (next-event estimation), persistent grid over a work queue filled by k_sample
+//   k_raygen : ray generation + bounce-0 closest hit, one thread per Monte-Carlo sample
+//   k_shade<c>(i) / k_trace(i) : the sample-phase loop unrolled over bounces as dense wavefronts (grid-stride over device-side
+//              work lists; one material class per k_shade launch)
+//   k_nee<c> : next-event estimation, grid-stride over the NEE work queues filled by k_shade
 //   k_splat  : stage 3 (ordered accumulation, spectrum -> sRGB, film splat with vector atomics)
 //   k_develop: HDRFilm::develop weight division
 // Path state lives in SoA arrays indexed depth-major (pltb_integrator.cuh) so warp accesses are coalesced float4s; queue
@@ -12,17 +14,16 @@
 
 namespace pltb {
 
-struct DevQueue {
-    uint32_t *q0, *q1;
-    uint32_t *count;
-    __device__ __forceinline__ void push(int which, uint32_t entry) {
+// Warp-aggregated list append: lanes appending to the same list elect a leader that reserves the slots with one atomicAdd.
+struct DevPush {
+    __device__ __forceinline__ void operator()(uint32_t *list, uint32_t *count, uint32_t entry) const {
         const unsigned active = __activemask();
-        const unsigned peers = __match_any_sync(active, which);
+        const unsigned peers = __match_any_sync(active, (unsigned long long) count);
         const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
         uint32_t base = 0;
-        if (lane == leader) base = atomicAdd(count + which, (uint32_t) __popc(peers));
+        if (lane == leader) base = atomicAdd(count, (uint32_t) __popc(peers));
         base = __shfl_sync(peers, base, leader);
-        (which ? q1 : q0)[base + __popc(peers & ((1u << lane) - 1u))] = entry;
+        list[base + __popc(peers & ((1u << lane) - 1u))] = entry;
     }
 };
 
@@ -44,25 +45,48 @@ __device__ __forceinline__ void flush_counters(const uint32_t cnt[4], unsigned l
     }
 }
 
-__global__ void __launch_bounds__(128) k_sample(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+__global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                 const __grid_constant__ PassParams pp) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     if (local < pp.count) {
-        DevQueue q{ st.queue[0], st.queue[1], st.queue_count };
-        stage_sample(sc, st, pp, local, q, cnt);
+        DevPush push;
+        stage_raygen(sc, st, pp, local, push, cnt);
     }
     flush_counters(cnt, st.counters);
 }
 
-__global__ void __launch_bounds__(128) k_nee(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
-                                             int which) {
-    const uint32_t n = st.queue_count[which];
-    const uint32_t *queue = st.queue[which];
+// grid-stride over a device-side work list whose length is only known on the device
+__global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                               uint32_t bounce) {
+    const uint32_t n = st.counts[4 * bounce];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + which, (unsigned long long) n);   // queue sizes
+    DevPush push;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee(sc, st, queue[e], cnt);
+        stage_trace(sc, st, st.live[e], bounce, push, cnt);
+    flush_counters(cnt, st.counters);
+}
+
+template <int Class>
+__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                               uint32_t bounce) {
+    const uint32_t n = st.counts[4 * bounce + 1 + Class];
+    const uint32_t *list = st.shade_q[Class];
+    uint32_t cnt[4] = { 0, 0, 0, 0 };
+    DevPush push;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_shade<Class>(sc, st, list[e], bounce, push, cnt);
+    flush_counters(cnt, st.counters);
+}
+
+template <int Class>
+__global__ void __launch_bounds__(128) k_nee(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+    const uint32_t n = st.counts[kCountsNee + Class];
+    const uint32_t *queue = st.queue[Class];
+    uint32_t cnt[4] = { 0, 0, 0, 0 };
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + Class, (unsigned long long) n);   // queue sizes
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_nee<Class>(sc, st, queue[e], cnt);
     flush_counters(cnt, st.counters);
 }
 
@@ -89,11 +113,19 @@ __global__ void k_develop(const float4 *accum, float *rgb, uint64_t n_pixels) {
     rgb[3 * i] = a.x / d; rgb[3 * i + 1] = a.y / d; rgb[3 * i + 2] = a.z / d;
 }
 
-void launch_sample(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s) {
-    k_sample<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp);
+void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s) {
+    k_raygen<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp);
 }
-void launch_nee(const DeviceScene &sc, const PassState &st, int which, int grid, cudaStream_t s) {
-    k_nee<<<grid, 128, 0, s>>>(sc, st, which);
+void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
+    k_trace<<<grid, 128, 0, s>>>(sc, st, bounce);
+}
+void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
+    if (cls) k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce);
+    else k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce);
+}
+void launch_nee(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
+    if (cls) k_nee<1><<<grid, 128, 0, s>>>(sc, st);
+    else k_nee<0><<<grid, 128, 0, s>>>(sc, st);
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint64_t dump_cap, cudaStream_t s) {

@@ -9,9 +9,11 @@
 #if defined(__CUDACC__)
 #  define PLTB_HD __host__ __device__ __forceinline__
 #  define PLTB_D __device__ __forceinline__
+#  define PLTB_NI inline __host__ __device__ __noinline__   /* big, multiply-used bodies: one copy per kernel keeps the I-cache footprint down */
 #else
 #  define PLTB_HD inline
 #  define PLTB_D inline
+#  define PLTB_NI inline
 #endif
 
 namespace pltb {
@@ -165,9 +167,9 @@ struct BesselTables { float t[20]; float sin_t[20]; float h_over_3; };
 PLTB_HD float bessel_j_small(const BesselTables &bt, float x, int nu) {
     float fnu = (float) nu;
     float I_odd = 0.f, I_even = 0.f;
-#pragma unroll
+#pragma unroll 1
     for (int i = 1; i < 19; i += 2) I_odd += cosf(fnu * bt.t[i] - x * bt.sin_t[i]);
-#pragma unroll
+#pragma unroll 1
     for (int i = 2; i < 19; i += 2) I_even += cosf(fnu * bt.t[i] - x * bt.sin_t[i]);
     float fa = cosf(fnu * bt.t[0] - x * bt.sin_t[0]), fb = cosf(fnu * bt.t[19] - x * bt.sin_t[19]);
     return kInvPi * (bt.h_over_3 * (fa + 4.0f * I_odd + 2.0f * I_even + fb));
@@ -179,7 +181,7 @@ PLTB_HD float bessel_j_asymp(float x, int nu) {
         return sign * sqrtf(2.0f / (kPi * x_abs)) * cosf(x_abs - kPi * (float) nu / 2.0f - kPi / 4.0f);
     return nu == 0 ? 1.0f : 0.0f;
 }
-PLTB_HD float bessel_j(const BesselTables &bt, float x, int nu) {
+PLTB_NI float bessel_j(const BesselTables &bt, float x, int nu) {
     int nua = nu < 0 ? -nu : nu;
     const float nu_abs = (float) nua, nsign = nu < 0 ? -1.f : 1.f;
     float center = 45.f + nu_abs;

@@ -76,7 +76,7 @@ PLTB_HD bool rectangle_intersect(const pltb_shape &sh, const Ray &ray, float &t_
 
 // Scene::ray_intersect / ray_test (src/render/scene.cpp:176-205) over our own BVH: short-stack traversal, ordered
 // descent, Moeller-Trumbore exactly as Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:460-481).
-template <bool AnyHit> PLTB_HD Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
+template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
     Hit best; best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
     if (sc.n_nodes == 0) return best;
     const float ix = 1.f / ray.d.x, iy = 1.f / ray.d.y, iz = 1.f / ray.d.z;
@@ -189,7 +189,7 @@ PLTB_HD int wrap_coord(int pos, int shape, uint32_t mode) {  // ext/drjit/includ
     return mod;
 }
 
-PLTB_HD S4 tex_eval(const DeviceScene &sc, int32_t id, const S4 &wl, V2 uv) {
+PLTB_NI S4 tex_eval(const DeviceScene &sc, int32_t id, const S4 &wl, V2 uv) {
     if (id < 0) return s4(1.f);
     const pltb_texture &t = sc.textures[id];
     const float *data = sc.tex_data + t.offset;

@@ -38,7 +38,7 @@ struct SI {
     }
 };
 
-PLTB_HD SI make_si(const DeviceScene &sc, const Ray &ray, const Hit &h) {
+PLTB_NI SI make_si(const DeviceScene &sc, const Ray &ray, const Hit &h) {
     SI si;
     si.t = inf_f(); si.shape = -1;
     si.p = si.n = mk3(0, 0, 0); si.uv = mk2(0, 0);
@@ -161,7 +161,7 @@ struct Microfacet {
             return mk2(fmsub(cos_theta_i, y, sin_theta_i * z) * nrm, x * nrm);
         }
     }
-    PLTB_HD V3 sample(V3 wi, V2 sample, float &pdf_out) const {
+    PLTB_NI V3 sample(V3 wi, V2 sample, float &pdf_out) const {
         if (!sample_visible) {
             float sin_phi, cos_phi, cos_theta, cos_theta_2, alpha_2;
             if (au == av) {

@@ -1,6 +1,5 @@
-// pltb_stages.cuh -- bodies of the three wavefront stages (see pltb_integrator.cuh).  Written as host/device templates over
-// a queue-append policy so that tests can run the identical code on the host (tests/host_emul.cpp) -- the product only
-// instantiates them inside the CUDA kernels of pltb_kernels.cu.
+// pltb_stages.cuh -- bodies of the wavefront stages (see pltb_integrator.cuh), templated over the list-append policy and the
+// material class; instantiated by the CUDA kernels of pltb_kernels.cu.
 #pragma once
 #include "pltb_integrator.cuh"
 
@@ -20,8 +19,31 @@ PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32
     idx = (y * pp.film_w + x) * pp.spp + s;
 }
 
-template <class Queue>
-PLTB_HD void stage_sample(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Queue &queue,
+// Closest-hit bookkeeping shared by k_raygen (bounce 0) and k_trace (bounce >= 1): a hit is routed to the shade queue of
+// its material class; a miss finalises the path in place (plt.py:93-168 with si invalid: the five BSDF draws and the RR
+// draw are still consumed, the bounce record contributes nothing, the loop ends).
+template <class Push>
+PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, const Hit &h, PCG32 &rng,
+                       bool rng_dirty, Push &push) {
+    if (h.shape >= 0) {
+        st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim));
+        if (rng_dirty) { st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc; }
+        const int32_t bid = sc.shapes[h.shape].bsdf;
+        const int cls = (bid >= 0 && sc.bsdfs[bid].type == PLTB_BSDF_ROUGHGRATING) ? 1 : 0;
+        push(st.shade_q[cls], st.counts + 4 * i + 1 + cls, local);
+    } else {
+        for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
+        st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
+        const size_t r = (size_t) i * st.chunk + local;
+        st.v_em[r] = mkf4(0.f, 0.f, 0.f, 0.f);
+        st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
+        st.n_vertices[local] = i + 1;
+    }
+}
+
+// ADIntegrator.sample_rays (common.py:231-309) + the first iteration's scene.ray_intersect (plt.py:96)
+template <class Push>
+PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Push &push,
                           uint32_t cnt[4]) {
     uint32_t x, y, s, idx;
     decode_sample(pp, pp.first + local, x, y, s, idx);
@@ -29,7 +51,6 @@ PLTB_HD void stage_sample(const DeviceScene &sc, const PassState &st, const Pass
     uint32_t v0, v1;
     sample_tea_32(pp.seed, idx, v0, v1);
     PCG32 rng; rng.seed(v0, v1);
-    // ADIntegrator.sample_rays (common.py:231-309)
     float jx = rng.next_float32(), jy = rng.next_float32();
     V2 pos_f = mk2((float) x + jx, (float) y + jy);
     float wav_sample = rng.next_float32();
@@ -44,96 +65,122 @@ PLTB_HD void stage_sample(const DeviceScene &sc, const PassState &st, const Pass
     st.sensor_w[local] = s4_to_f4(wgt);
     float2 fp; fp.x = pos_f.x; fp.y = pos_f.y;
     st.film_pos[local] = fp;
+    for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1, plt.py:65-70)
+    st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+    st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
+    Hit h = bvh_intersect<false>(sc, ray);
+    cnt[0]++;
+    route_hit(sc, st, local, 0, h, rng, true, push);
+}
 
-    // ---- plt_sample_phase (plt.py:50-171) ----
-    for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1)
+// scene.ray_intersect of loop iteration i >= 1 (plt.py:96)
+template <class Push>
+PLTB_HD void stage_trace(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
+    float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
+    Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
+    Hit h = bvh_intersect<false>(sc, ray);
+    cnt[0]++;
+    PCG32 rng;
+    if (h.shape < 0) { rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local]; }
+    route_hit(sc, st, local, i, h, rng, false, push);
+}
+
+// One iteration of the sample-phase loop (plt.py:93-168) for a path that hit a surface of material class `Class`, fused with
+// the parts of the solve phase that only depend on vertices 0..i (replay_path :408-472, solve_replay_emissive :315-405).
+template <int Class, class Push>
+PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
+    const float4 o4 = st.p_ray_o[local], d4 = st.p_ray_d[local], h4 = st.p_hit[local];
+    Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
+    Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w);
+    h.shape = h.prim < sc.n_faces ? (int32_t) PLTB_LDG(sc.face_shape + h.prim) : (int32_t) (h.prim - sc.n_faces);
+    const S4 wl = f4_to_s4(st.wl[local]);
+    PCG32 rng; rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local];
     S4 alpha = s4(1.f);
     float eta = 1.f, last_nd_pdf = 1.f;
-    uint32_t depth = 0, i = 0;
-    bool active = true, prev_bsdf_delta = true;
+    bool prev_bsdf_delta = true;
     V3 prev_p = mk3(0.f, 0.f, 0.f);
-    S4 w[PLTB_MAX_DEPTH];
-    while (active) {
-        Hit h = bvh_intersect<false>(sc, ray);
-        cnt[0]++;
-        SI si = make_si(sc, ray, h);
-        const bool valid = si.valid();
-        bool active_next = (depth + 1 < st.max_depth) && valid;
-        float sample_1 = rng.next_float32();
-        V2 sample_2, lobe_sample_2;
-        sample_2.x = rng.next_float32(); sample_2.y = rng.next_float32();
-        lobe_sample_2.x = rng.next_float32(); lobe_sample_2.y = rng.next_float32();
-        const pltb_bsdf *b = si_bsdf(sc, si.shape);
-        BSDFSampleOut so = wbsdf_sample(sc, b, si.wi, si.uv, wl, sample_1, sample_2, lobe_sample_2);
+    if (i > 0) {
+        alpha = f4_to_s4(st.p_alpha[local]);
+        float4 pv = st.p_prev[local];
+        prev_p = mk3(pv.x, pv.y, pv.z); last_nd_pdf = pv.w;
+        eta = d4.w;
+        prev_bsdf_delta = (st.p_flags[local] & 1u) != 0;
+    }
+    SI si = make_si(sc, ray, h);
+    bool active_next = (i + 1 < st.max_depth);   // si is valid here; depth == i on entry
+    float sample_1 = rng.next_float32();
+    V2 sample_2, lobe_sample_2;
+    sample_2.x = rng.next_float32(); sample_2.y = rng.next_float32();
+    lobe_sample_2.x = rng.next_float32(); lobe_sample_2.y = rng.next_float32();
+    const pltb_bsdf *b = si_bsdf(sc, si.shape);
+    BSDFSampleOut so = wbsdf_sample<Class>(sc, b, si.wi, si.uv, wl, sample_1, sample_2, lobe_sample_2);
 
-        // replay_path for this vertex (plt.py:408-472): alpha_i = w_0 * (w_1 * (... * (w_{i-1} * 1)))
-        S4 ai = s4(1.f);
-        for (int j = (int) i - 1; j >= 0; --j) ai = w[j] * ai;
-        // solve_replay_emissive (plt.py:315-405)
-        S4 em = s4(0.f);
-        if (valid) {
-            int32_t em_id = sc.shapes[si.shape].emitter;
-            if (em_id >= 0) {
-                const pltb_emitter &e = sc.emitters[em_id];
-                float em_pdf = 0.f;
-                if (!prev_bsdf_delta) {   // Scene::pdf_emitter_direction -> AreaLight::pdf_direction (area.cpp:170-196)
-                    V3 rel = si.p - prev_p;
-                    float dist = norm(rel);
-                    V3 d = rel / dist;
-                    if (dot(d, si.sh.n) < 0.f) em_pdf = shape_pdf_direction(sc.shapes[e.shape], prev_p, d, si.sh.n, dist);
-                    em_pdf *= sc.emitter_pmf;
-                }
-                float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
-                S4 Le = si.wi.z > 0.f ? tex_eval(sc, e.radiance, wl, si.uv) : s4(0.f);   // AreaLight::eval (area.cpp:82-89)
-                em = ai * (Le * mis_bsdf);
-            }
-            w[i] = wbsdf_weight(sc, b, si.wi, si.uv, wl, so.wo);
-            cnt[2]++;
-            if (b && b->type == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
-        } else {
-            w[i] = s4(0.f);
+    // replay_path for this vertex: alpha_i = w_0 * (w_1 * (... * (w_{i-1} * 1)))
+    S4 ai = s4(1.f);
+    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
+    // solve_replay_emissive
+    S4 em = s4(0.f);
+    const int32_t em_id = sc.shapes[si.shape].emitter;
+    if (em_id >= 0) {
+        const pltb_emitter &e = sc.emitters[em_id];
+        float em_pdf = 0.f;
+        if (!prev_bsdf_delta) {   // Scene::pdf_emitter_direction -> AreaLight::pdf_direction (area.cpp:170-196)
+            V3 rel = si.p - prev_p;
+            float dist = norm(rel);
+            V3 d = rel / dist;
+            if (dot(d, si.sh.n) < 0.f) em_pdf = shape_pdf_direction(sc.shapes[e.shape], prev_p, d, si.sh.n, dist);
+            em_pdf *= sc.emitter_pmf;
         }
+        float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
+        S4 Le = si.wi.z > 0.f ? tex_eval(sc, e.radiance, wl, si.uv) : s4(0.f);   // AreaLight::eval (area.cpp:82-89)
+        em = ai * (Le * mis_bsdf);
+    }
+    const size_t r = (size_t) i * st.chunk + local;
+    if (active_next) st.v_w[r] = s4_to_f4(wbsdf_weight<Class>(sc, b, si.wi, si.uv, wl, so.wo));
+    cnt[2]++;
+    if (Class == 1) cnt[3]++;
 
-        ray = si.spawn_ray(si.sh.to_world(so.wo));
-        if (active_next) { alpha = so.weight * alpha; eta = so.eta; }
-        if (valid) depth += 1;
-        float alpha_max = smax(alpha);
-        active_next = active_next && alpha_max != 0.f;
-        float rr_prob = fminf(alpha_max * sqr(eta), 0.95f);
-        bool rr_active = depth >= st.rr_depth;
-        if (rr_active) alpha = alpha * rcp(rr_prob);
-        bool rr_continue = rng.next_float32() < rr_prob;
-        active_next = active_next && (!rr_active || rr_continue);
+    Ray next = si.spawn_ray(si.sh.to_world(so.wo));
+    if (active_next) { alpha = so.weight * alpha; eta = so.eta; }
+    float alpha_max = smax(alpha);
+    active_next = active_next && alpha_max != 0.f;
+    float rr_prob = fminf(alpha_max * sqr(eta), 0.95f);
+    bool rr_active = (i + 1) >= st.rr_depth;
+    if (rr_active) alpha = alpha * rcp(rr_prob);
+    bool rr_continue = rng.next_float32() < rr_prob;
+    active_next = active_next && (!rr_active || rr_continue);
 
-        // bounce record
-        const size_t r = (size_t) i * st.chunk + local;
-        const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
-        st.v_em[r] = s4_to_f4(em);
-        if (nee) {
-            st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
-            st.v_n_v[r] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
-            st.v_s_wix[r] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
-            st.v_shn_wiy[r] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
-            st.v_alpha[r] = s4_to_f4(ai);
-            float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
-            st.v_wiz_shape[r] = ws;
-            queue.push((b->type == PLTB_BSDF_ROUGHGRATING) ? 1 : 0, local | (i << 27));
-        } else {
-            st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
-        }
-
-        last_nd_pdf = ((so.type & F_Delta) != 0) ? last_nd_pdf : so.pdf;
-        prev_bsdf_delta = (so.type & F_Delta) != 0;
-        prev_p = si.p;
-        active = active_next;
-        i += 1;
+    // bounce record
+    const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
+    st.v_em[r] = s4_to_f4(em);
+    if (nee) {
+        st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
+        st.v_n_v[r] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
+        st.v_s_wix[r] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
+        st.v_shn_wiy[r] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
+        st.v_alpha[r] = s4_to_f4(ai);
+        float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
+        st.v_wiz_shape[r] = ws;
+        push(st.queue[Class], st.counts + kCountsNee + Class, local | (i << 27));
+    } else {
+        st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
     st.rng_state[local] = rng.state;
-    st.rng_inc[local] = rng.inc;
-    st.n_vertices[local] = i;
+    if (active_next) {
+        const bool delta = (so.type & F_Delta) != 0;
+        st.p_ray_o[local] = mkf4(next.o.x, next.o.y, next.o.z, next.maxt);
+        st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
+        st.p_alpha[local] = s4_to_f4(alpha);
+        st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
+        st.p_flags[local] = delta ? 1u : 0u;
+        push(st.live, st.counts + 4 * (i + 1), local);
+    } else {
+        st.n_vertices[local] = i + 1;
+    }
 }
 
 // solve_replay_NEE (plt.py:221-300) for one queued vertex
+template <int Class>
 PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entry, uint32_t cnt[4]) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
@@ -182,8 +229,8 @@ PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entr
     S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
     V3 wo = si.sh.to_local(ds.d);
     const pltb_bsdf *b = si_bsdf(sc, si.shape);
-    S4 bsdf_val = wbsdf_eval(sc, b, si.wi, si.uv, wl, wo);
-    float bsdf_pdf = wbsdf_pdf(sc, b, si.wi, si.uv, wl, wo);
+    S4 bsdf_val = wbsdf_eval<Class>(sc, b, si.wi, si.uv, wl, wo);
+    float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
     S4 a = f4_to_s4(st.v_alpha[r]);
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
