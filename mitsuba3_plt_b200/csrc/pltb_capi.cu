@@ -323,7 +323,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     PassParams pp{};
     pp.seed = prm->seed; pp.spp = prm->spp; pp.spp_begin = prm->spp_begin; pp.spp_count = prm->spp_count;
     pp.crop_x = prm->crop_x; pp.crop_y = prm->crop_y; pp.crop_w = cw; pp.crop_h = ch;
-    pp.film_w = W; pp.film_h = H;
+    pp.film_w = W; pp.film_h = H; pp.n_pix = cw * ch;
     const int nee_grid = c->sm_count * 8, wf_grid = c->sm_count * 8;
     const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
     for (uint64_t first = 0; first < total; first += st.chunk) {

@@ -256,6 +256,7 @@ struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;
     uint32_t crop_x, crop_y, crop_w, crop_h;
     uint32_t film_w, film_h;       // whole film (n_sensors * film.width, film.height)
+    uint32_t n_pix;                // crop_w * crop_h
     uint64_t first;                // first sample (in window order) of this pass
     uint32_t count;                // samples in this pass
 };

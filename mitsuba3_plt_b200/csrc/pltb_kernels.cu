@@ -97,7 +97,9 @@ __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceSce
     if (local >= pp.count) return;
     DevFilm film{ accum };
     S4 L = stage_splat(sc, st, pp, local, film, do_splat != 0);
-    const uint64_t di = pp.first + local;
+    uint32_t pix, s_rel;
+    split_work(pp, pp.first + local, pix, s_rel);
+    const uint64_t di = (uint64_t) pix * pp.spp_count + s_rel;   // dump order: pixel-major, then sample (include/pltb.h)
     if (di < dump_cap) {
         if (dump_L) reinterpret_cast<float4 *>(dump_L)[di] = s4_to_f4(L);
         if (dump_wl) reinterpret_cast<float4 *>(dump_wl)[di] = st.wl[local];

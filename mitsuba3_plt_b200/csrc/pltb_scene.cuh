@@ -79,6 +79,10 @@ PLTB_HD bool rectangle_intersect(const pltb_shape &sh, const Ray &ray, float &t_
 template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
     Hit best; best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
     if (sc.n_nodes == 0) return best;
+    // A ray with a NaN component (the reference lets paths continue with alpha = inf * 0, SURVEY/DESIGN "quirks") fails every
+    // triangle / shape test (NaN comparisons are false) but would pass every slab test and walk the whole tree: report the
+    // miss right away.
+    if (isnan_(ray.o.x + ray.o.y + ray.o.z + ray.d.x + ray.d.y + ray.d.z)) return best;
     const float ix = 1.f / ray.d.x, iy = 1.f / ray.d.y, iz = 1.f / ray.d.z;
     int32_t stack[32];
     int sp = 0;

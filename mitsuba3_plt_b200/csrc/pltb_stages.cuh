@@ -9,12 +9,21 @@ PLTB_HD float4 mkf4(float x, float y, float z, float w) { float4 r; r.x = x; r.y
 PLTB_HD float4 s4_to_f4(const S4 &s) { return mkf4(s.v[0], s.v[1], s.v[2], s.v[3]); }
 PLTB_HD S4 f4_to_s4(const float4 &f) { S4 s; s.v[0] = f.x; s.v[1] = f.y; s.v[2] = f.z; s.v[3] = f.w; return s; }
 
-// window-order sample index -> pixel / sample-in-pixel / reference lane index (common.py:256-266)
+// Work order of a render: sample-major, w = s_rel * n_pix + pixel (pixel fastest).  Adjacent threads work on adjacent pixels
+// of the same sample index, so primary rays stay coherent and the 5x5 film splats of a warp go to 32 neighbouring pixels
+// (coalesced vector atomics to distinct addresses) instead of 32 times to the same 25 pixels.
+// work index -> window pixel index / sample-in-window
+PLTB_HD void split_work(const PassParams &pp, uint64_t w, uint32_t &pix, uint32_t &s_rel) {
+    s_rel = (uint32_t) (w / pp.n_pix);
+    pix = (uint32_t) (w - (uint64_t) s_rel * pp.n_pix);
+}
+// -> pixel / sample-in-pixel / reference lane index (common.py:256-266)
 PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32_t &y, uint32_t &s, uint32_t &idx) {
-    uint64_t pix = w / pp.spp_count;
-    s = (uint32_t) (w - pix * pp.spp_count) + pp.spp_begin;
-    uint32_t row = (uint32_t) (pix / pp.crop_w);
-    x = pp.crop_x + (uint32_t) (pix - (uint64_t) row * pp.crop_w);
+    uint32_t pix, s_rel;
+    split_work(pp, w, pix, s_rel);
+    s = s_rel + pp.spp_begin;
+    uint32_t row = pix / pp.crop_w;
+    x = pp.crop_x + (pix - row * pp.crop_w);
     y = pp.crop_y + row;
     idx = (y * pp.film_w + x) * pp.spp + s;
 }
