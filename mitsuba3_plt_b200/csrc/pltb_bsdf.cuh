@@ -145,17 +145,42 @@ PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv,
         coh[i] = isnan_(ac) ? 0.0f : ac;
     }
     const V2 sin_i = g.sin_i(wi);
+    // Window test |unit_angle(center_dir, wo)| < a_win (drjit sphere.h:53-60) without the asin / sqrt per lobe: for
+    // dot >= 0 the angle is 2 asin(|wo - c| / 2), monotone in the squared chord, so the test is chord^2 < (2 sin(a_win/2))^2;
+    // dot < 0 means angle >= pi/2, which can only pass for a_win > pi/2 (alpha > 0.6): those BSDFs take the exact path.  Lobes that fail the validity test
+    // |sin_o| <= 1 add exactly 0 and are skipped before the direction is reconstructed.
+    const float half_win = fminf(0.5f * a_win, 0.5f * kPi), chord = 2.f * sinf(half_win), chord_sq = chord * chord;
+    // Conservative pre-filter on the lobe's "sines" (da, db) before its direction is reconstructed.  For a valid lobe the
+    // direction c is a unit vector with c.x / |c.xz| == da and c.y / |c.yz| == db (diffractiongrating.h:211-225).  The map
+    // v -> v.x / |v.xz| has gradient <= 1 / |v.xz|, so |c - wo| < chord implies |da - wo.x / |wo.xz|| <= chord / (|wo.xz| -
+    // chord) (likewise for y); lobes outside that box (with a 1.5x margin for rounding) cannot pass the window test.
+    const bool small_win = a_win <= 0.5f * kPi;
+    const float pwx = sqrtf(sqr(wo.x) + sqr(wo.z)), pwy = sqrtf(sqr(wo.y) + sqr(wo.z));
+    const bool fx = small_win && pwx > 2.f * chord, fy = small_win && pwy > 2.f * chord;
+    const float awo = fx ? wo.x / pwx : 0.f, bwo = fy ? wo.y / pwy : 0.f;
+    const float tolx = fx ? 1.5f * chord / (pwx - chord) + 1e-5f : inf_f(), toly = fy ? 1.5f * chord / (pwy - chord) + 1e-5f : inf_f();
+    const float cos_g = g.dir.x, sin_g = g.dir.y;
     S4 result = s4(0.f);
     for (int lx = -half; lx <= half; ++lx) {
+#pragma unroll 1
         for (int ly = -half; ly <= half; ++ly) {
-            const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
+            const float lrx = cos_g * (float) lx - sin_g * (float) ly, lry = sin_g * (float) lx + cos_g * (float) ly;
+#pragma unroll
             for (int i = 0; i < 4; ++i) {
+                const float da = wl_um[i] * lrx * g.inv_period.x - sin_i.x, db = wl_um[i] * lry * g.inv_period.y - sin_i.y;
+                if (!(fabsf(da) <= 1.0f && fabsf(db) <= 1.0f)) continue;   // lobe_active == false: adds 0
+                if (fabsf(da - awo) > tolx || fabsf(db - bwo) > toly) continue;   // cannot be inside the window
+                const float m = (sqr(da) - 1) / (sqr(da * db) - 1), qq = 1 - sqr(db) * m;
+                const V3 c = mk3(da * sqrtf(fmaxf(0.0f, qq)), db * sqrtf(m), sqrtf(fmaxf(0.0f, 1 - sqr(da) * qq - sqr(db) * m)));
+                bool inside;
+                if (small_win) inside = dot(c, wo) >= 0.f && sqnorm(wo - c) < chord_sq;
+                else inside = fabsf(unit_angle(c, wo)) < a_win;
+                if (!inside) continue;
+                const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
                 float ix = term[i][alx], iy = one_d ? ix : term[i][aly];
                 float lobe_intensity = g.multiplier * ix * iy;
-                bool lobe_active; V3 center_dir = g.diffract_s(sin_i, lx, ly, wl_um[i], lobe_active);
-                bool inside = lobe_active && fabsf(unit_angle(center_dir, wo)) < a_win;
-                if (lx == 0 && ly == 0) result.v[i] += inside ? lobe_intensity : 0.0f;
-                else result.v[i] += inside ? lobe_intensity * coh[i] : 0.0f;
+                if (lx == 0 && ly == 0) result.v[i] += lobe_intensity;
+                else result.v[i] += lobe_intensity * coh[i];
             }
         }
     }
