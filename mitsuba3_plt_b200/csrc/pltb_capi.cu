@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -294,7 +295,11 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         CU(cudaMemsetAsync(c->accum, 0, n_acc * sizeof(float), s));
         c->accum_floats = n_acc;
     }
-    uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(total, 1), 1u << 21);
+    // samples per wavefront pass: large enough that the nearly empty late-bounce launches are amortised (their cost is the
+    // latency of one thread's work, not throughput); ~1.1 KB of state per sample -> 9 GB at 2^23
+    uint32_t chunk_log2 = 23;
+    if (const char *e = getenv("PLTB_CHUNK_LOG2")) chunk_log2 = (uint32_t) std::min(26, std::max(10, atoi(e)));
+    uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(total, 1), 1ull << chunk_log2);
     if (int rc = ensure_state(c, chunk, prm->max_depth)) return rc;
     PassState st = c->st;
     st.chunk = c->st_chunk; st.max_depth = prm->max_depth; st.rr_depth = prm->rr_depth;
@@ -391,6 +396,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         stats->samples = total; stats->closest_rays = h[0]; stats->shadow_rays = h[1];
         stats->vertices = h[2]; stats->grating_vertices = h[3];
         stats->nee_other = h[4]; stats->nee_grating = h[5];
+        stats->passes = n_pass;
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, c->ev[0], c->ev[1]));
         if (profile) {
