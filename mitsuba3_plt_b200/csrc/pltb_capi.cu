@@ -343,7 +343,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
             launch_shade(scene->dev, st, b, 1, wf_grid, s);
             launch_shade(scene->dev, st, b, 0, wf_grid, s);
             launches += 2;
-            if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches++; }
+            if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches += 2; }
         }
         PROF();
         launch_nee(scene->dev, st, 1, nee_grid, s);

@@ -56,15 +56,72 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
     flush_counters(cnt, st.counters);
 }
 
-// grid-stride over a device-side work list whose length is only known on the device
+// Closest hit for the live paths of bounce >= 1.  Secondary rays are incoherent and their traversal lengths differ by orders
+// of magnitude (most leave the open box after a few nodes, some walk a 960-triangle sphere), so a ray-per-thread loop leaves
+// two thirds of the lanes idle.  Persistent warps instead: every lane owns a resumable Traversal; whenever lanes finish, the
+// warp reserves new rays for them with one atomicAdd on the bounce's cursor, then all lanes advance by a bounded number of
+// inner-node steps followed by one leaf step (while-while order).
 __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
     const uint32_t n = st.counts[4 * bounce];
+    uint32_t *cursor = st.counts + 4 * bounce + 3;
+    const unsigned lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    DevPush push;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_trace(sc, st, st.live[e], bounce, push, cnt);
+    Traversal tr;
+    tr.done = true;
+    bool active = false, exhausted = false;
+    uint32_t local = 0;
+    for (;;) {
+        __syncwarp();
+        const unsigned need = __ballot_sync(0xffffffffu, !active);
+        if (need && !exhausted) {
+            uint32_t base = 0;
+            const int leader = __ffs(need) - 1;
+            if ((int) lane == leader) base = atomicAdd(cursor, (uint32_t) __popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active) {
+                const uint32_t e = base + __popc(need & lt_mask);
+                if (e < n) {
+                    local = st.live[e];
+                    float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
+                    Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
+                    tr.begin(sc, ray);
+                    active = true;
+                    cnt[0]++;
+                }
+            }
+            exhausted = base + __popc(need) >= n;   // warp-uniform
+        }
+        if (__ballot_sync(0xffffffffu, active) == 0) break;
+#pragma unroll 1
+        for (int k = 0; k < 6; ++k)
+            if (active && !tr.done && tr.node >= 0) tr.inner_step(sc);
+        if (active && !tr.done && tr.node < 0) tr.leaf_step<false>(sc);
+        if (active && tr.done) {
+            // results are written in place; k_classify walks the live list in order afterwards so that the shade / NEE work
+            // lists stay (nearly) sorted by sample id and the per-sample state accesses of later kernels stay coalesced
+            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? 0xFFFFFFFFu : tr.best.prim));
+            active = false;
+        }
+    }
     flush_counters(cnt, st.counters);
+}
+
+// Routes the results of k_trace: hits to the shade queue of their material class, misses finalised in place.
+__global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                                  uint32_t bounce) {
+    const uint32_t n = st.counts[4 * bounce];
+    DevPush push;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t local = st.live[e];
+        const float4 h4 = st.p_hit[local];
+        Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w); h.shape = -1;
+        PCG32 rng; rng.state = 0; rng.inc = 0;
+        if (h.prim != 0xFFFFFFFFu)
+            h.shape = h.prim < sc.n_faces ? (int32_t) __ldg(sc.face_shape + h.prim) : (int32_t) (h.prim - sc.n_faces);
+        else { rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local]; }
+        route_hit(sc, st, local, bounce, h, rng, false, push);
+    }
 }
 
 template <int Class>
@@ -120,6 +177,7 @@ void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams 
 }
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
     k_trace<<<grid, 128, 0, s>>>(sc, st, bounce);
+    k_classify<<<grid, 256, 0, s>>>(sc, st, bounce);
 }
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
     if (cls) k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce);

@@ -76,6 +76,97 @@ PLTB_HD bool rectangle_intersect(const pltb_shape &sh, const Ray &ray, float &t_
 
 // Scene::ray_intersect / ray_test (src/render/scene.cpp:176-205) over our own BVH: short-stack traversal, ordered
 // descent, Moeller-Trumbore exactly as Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:460-481).
+// The traversal is a resumable state machine (one inner node or one leaf per step) so that k_trace can keep the lanes of
+// a warp busy by handing finished lanes a new ray while the others are still walking the tree.
+struct Traversal {
+    Ray ray;
+    float ix, iy, iz;
+    int32_t node;   // >= 0: inner node index; < 0: leaf ~(first | count << 24)
+    int sp;
+    bool done;
+    Hit best;
+    int32_t stack[32];
+
+    PLTB_HD void begin(const DeviceScene &sc, const Ray &r) {
+        ray = r;
+        best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
+        sp = 0; node = 0;
+        // A ray with a NaN component (the reference lets paths continue with alpha = inf * 0, DESIGN.md "quirks") fails every
+        // triangle / shape test (NaN comparisons are false) but would pass every slab test and walk the whole tree: report
+        // the miss right away.
+        done = sc.n_nodes == 0 || isnan_(r.o.x + r.o.y + r.o.z + r.d.x + r.d.y + r.d.z);
+        ix = 1.f / r.d.x; iy = 1.f / r.d.y; iz = 1.f / r.d.z;
+    }
+    PLTB_HD void pop() {
+        if (sp == 0) done = true;
+        else node = stack[--sp];
+    }
+    PLTB_HD void inner_step(const DeviceScene &sc) {
+        const float4 *n = sc.bvh_nodes + 4 * (size_t) node;
+        float4 a = PLTB_LDG(n), b = PLTB_LDG(n + 1), c = PLTB_LDG(n + 2), d = PLTB_LDG(n + 3);
+        // child 0: lo (a.x a.y a.z) hi (a.w b.x b.y); child 1: lo (b.z b.w c.x) hi (c.y c.z c.w)
+        float t0x = (a.x - ray.o.x) * ix, t1x = (a.w - ray.o.x) * ix;
+        float t0y = (a.y - ray.o.y) * iy, t1y = (b.x - ray.o.y) * iy;
+        float t0z = (a.z - ray.o.z) * iz, t1z = (b.y - ray.o.z) * iz;
+        float n0 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+        float f0 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
+        t0x = (b.z - ray.o.x) * ix; t1x = (c.y - ray.o.x) * ix;
+        t0y = (b.w - ray.o.y) * iy; t1y = (c.z - ray.o.y) * iy;
+        t0z = (c.x - ray.o.z) * iz; t1z = (c.w - ray.o.z) * iz;
+        float n1 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+        float f1 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
+        // boxes are padded at build time; the 1 + 4 ulp factor keeps the slab test conservative
+        bool h0 = n0 <= f0 * 1.0000005f, h1 = n1 <= f1 * 1.0000005f;
+        int32_t c0 = (int32_t) f2u(d.x), c1 = (int32_t) f2u(d.y);
+        if (h0 && h1) {
+            if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
+            stack[sp++] = c1;
+            node = c0;
+        } else if (h0) node = c0;
+        else if (h1) node = c1;
+        else pop();
+    }
+    template <bool AnyHit> PLTB_HD void leaf_step(const DeviceScene &sc) {
+        uint32_t leaf = ~(uint32_t) node, first = leaf & 0xFFFFFFu, count = leaf >> 24;
+        for (uint32_t i = first; i < first + count; ++i) {
+            const float4 *tp = sc.tri_data + 3 * (size_t) i;
+            float4 q0 = PLTB_LDG(tp), q1 = PLTB_LDG(tp + 1), q2 = PLTB_LDG(tp + 2);
+            uint32_t prim = f2u(q2.y);
+            int32_t shape = (int32_t) f2u(q2.z);
+            float t, u = 0.f, v = 0.f;
+            bool hit;
+            if (prim < sc.n_faces) {
+                V3 p0 = mk3(q0.x, q0.y, q0.z), e1 = mk3(q0.w, q1.x, q1.y), e2 = mk3(q1.z, q1.w, q2.x);
+                V3 pvec = cross(ray.d, e2);
+                float inv_det = rcp(dot(e1, pvec));
+                V3 tvec = ray.o - p0;
+                u = dot(tvec, pvec) * inv_det;
+                hit = u >= 0.f && u <= 1.f;
+                V3 qvec = cross(tvec, e1);
+                v = dot(ray.d, qvec) * inv_det;
+                hit &= v >= 0.f && u + v <= 1.f;
+                t = dot(e2, qvec) * inv_det;
+                hit &= t >= 0.f && t <= ray.maxt;
+            } else {
+                const pltb_shape &sh = sc.shapes[shape];
+                if (sh.type == PLTB_SHAPE_SPHERE) hit = sphere_intersect(sh, ray, t);
+                else hit = rectangle_intersect(sh, ray, t, u, v);
+            }
+            if (hit && t < best.t) {
+                best.t = t; best.u = u; best.v = v; best.prim = prim; best.shape = shape;
+                if (AnyHit) { done = true; return; }
+                ray.maxt = t;
+            }
+        }
+        pop();
+    }
+    template <bool AnyHit> PLTB_HD void step(const DeviceScene &sc) {
+        if (node >= 0) inner_step(sc);
+        else leaf_step<AnyHit>(sc);
+    }
+};
+
+// one-ray-per-thread form (coherent primary rays in k_raygen, shadow rays in k_nee): same steps as Traversal, state in registers
 template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
     Hit best; best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
     if (sc.n_nodes == 0) return best;

@@ -82,18 +82,6 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
     route_hit(sc, st, local, 0, h, rng, true, push);
 }
 
-// scene.ray_intersect of loop iteration i >= 1 (plt.py:96)
-template <class Push>
-PLTB_HD void stage_trace(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
-    float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
-    Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
-    Hit h = bvh_intersect<false>(sc, ray);
-    cnt[0]++;
-    PCG32 rng;
-    if (h.shape < 0) { rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local]; }
-    route_hit(sc, st, local, i, h, rng, false, push);
-}
-
 // One iteration of the sample-phase loop (plt.py:93-168) for a path that hit a surface of material class `Class`, fused with
 // the parts of the solve phase that only depend on vertices 0..i (replay_path :408-472, solve_replay_emissive :315-405).
 template <int Class, class Push>
