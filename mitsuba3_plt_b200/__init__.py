@@ -210,6 +210,23 @@ def traverse(scene):
 # ---------------------------------------------------------------------------------------------------------------------
 # Integrators
 # ---------------------------------------------------------------------------------------------------------------------
+def split_subrenders(W, H, spp):
+    """The reference raises above 2^32 samples per wavefront (common.py:358-363); larger renders become n equal sub-renders
+    with seeds seed, seed+1, ... whose raw accumulators are summed.  Returns (n, spp per sub-render)."""
+    n_sub = 1
+    while W * H * (-(-spp // n_sub)) > (1 << 32):
+        n_sub += 1
+    if spp % n_sub:
+        raise RuntimeError(f"render(): spp={spp} exceeds the 2^32 wavefront limit and is not divisible into "
+                           f"{n_sub} equal sub-renders")
+    return n_sub, spp // n_sub
+
+
+def shard_spp(spp, rank, world):
+    """Sample-index range [lo, hi) of every pixel rendered by `rank`: contiguous, disjoint, covering."""
+    return (rank * spp) // world, ((rank + 1) * spp) // world
+
+
 _integrator_registry = {}
 
 
@@ -265,13 +282,7 @@ class PLTIntegrator:
         L = capi.lib()
         # wavefront limit of the reference (common.py:358-363); larger renders are split into sub-renders with
         # consecutive seeds whose raw accumulators are summed (SURVEY.md 8b "Seed/pass convention")
-        n_sub = 1
-        while W * H * (-(-spp // n_sub)) > (1 << 32):
-            n_sub += 1
-        if spp % n_sub:
-            raise RuntimeError(f"render(): spp={spp} exceeds the 2^32 wavefront limit and is not divisible into "
-                               f"{n_sub} equal sub-renders")
-        sub_spp = spp // n_sub
+        n_sub, sub_spp = split_subrenders(W, H, spp)
         shape = (H, W, 3 if develop else 4)
         if out is not None:
             if out.shape != shape or out.dtype != np.float32 or not out.flags.c_contiguous:
@@ -285,9 +296,7 @@ class PLTIntegrator:
                 prm = capi.RenderParams()
                 prm.seed = (int(seed) + k + flat.base_seed) & 0xFFFFFFFF
                 prm.spp = sub_spp
-                lo, hi = (ctx.rank * sub_spp) // ctx.world, ((ctx.rank + 1) * sub_spp) // ctx.world
-                if not reduce:
-                    lo, hi = 0, sub_spp
+                lo, hi = shard_spp(sub_spp, ctx.rank, ctx.world) if reduce else (0, sub_spp)
                 prm.spp_begin, prm.spp_count = lo, hi - lo
                 prm.max_depth, prm.rr_depth = self.max_depth, self.rr_depth
                 if crop:

@@ -184,7 +184,7 @@ class FlatScene:
             if np.any(rgb < 0) or np.any(rgb > 1):
                 raise RuntimeError(f"Invalid RGB reflectance value {list(rgb)}, must be in the range [0, 1]!")
             coeff = spectra.srgb_model_fetch(rgb)
-            return self._add_tex(type=capi.TEX_SRGB, p=list(coeff), mean=float(spectra.srgb_model_mean(coeff)))
+            return self._add_tex(type=capi.TEX_SRGB, p=list(coeff), mean=float(np.asarray(spectra.srgb_model_mean(coeff)).reshape(-1)[0]))
         if isinstance(v, SpectrumValue):
             if v.const is not None:
                 if within_emitter:

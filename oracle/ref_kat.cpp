@@ -10,6 +10,7 @@
 #include <mitsuba/render/fresnel.h>
 #include <mitsuba/render/microfacet.h>
 #include <drjit/random.h>
+#include <cstdarg>
 #include <cstdio>
 
 using namespace mitsuba;
@@ -96,3 +97,51 @@ int main() {
         printf("%s[%.9g, %.9g, %.9g, %.9g, %u, %u, %d, %.9g, %.9g, %.9g]", i ? ", " : "", gs[i].angle, gs[i].ipx, gs[i].ipy, gs[i].q,
                gs[i].lobes, gs[i].type, (int) gs[i].radial, gs[i].mult, gs[i].u, gs[i].v);
     printf("]");
+    // ---- Fresnel (include/mitsuba/render/fresnel.h) ----
+    open_arr("fresnel");
+    for (float c : { 1.f, 0.7f, 0.2f, 0.f, -0.3f, -1.f }) for (float eta : { 1.5f, 1.4f, 1.f / 1.4f }) {
+        auto [r, ct, eit, eti] = fresnel<float>(c, eta);
+        item("[%.9g, %.9g, %.9g, %.9g, %.9g, %.9g]", c, eta, r, ct, eit, eti);
+    }
+    close_arr();
+    open_arr("fresnel_conductor");
+    for (float c : { 1.f, 0.7f, 0.2f, 0.01f }) for (auto ek : { std::pair<float, float>{ 0.f, 1.f }, { 0.2f, 3.9f }, { 1.657f, 9.224f } })
+        item("[%.9g, %.9g, %.9g, %.9g]", c, ek.first, ek.second, fresnel_conductor<float>(c, dr::Complex<float>(ek.first, ek.second)));
+    close_arr();
+    // ---- MicrofacetDistribution (include/mitsuba/render/microfacet.h) ----
+    open_arr("microfacet");
+    for (int type = 0; type < 2; ++type) for (auto al : { std::pair<float, float>{ 0.02f, 0.02f }, { 0.1f, 0.1f }, { 0.3f, 0.05f } }) for (int vis = 0; vis < 2; ++vis) {
+        MicrofacetDistribution<float, Spec> distr(type == 0 ? MicrofacetType::Beckmann : MicrofacetType::GGX, al.first, al.second, vis != 0);
+        for (const V3 &wi : wis) for (auto u : { std::pair<float, float>{ 0.3f, 0.8f }, { 0.95f, 0.05f }, { 0.5f, 0.5f } }) {
+            auto [m, pdf] = distr.sample(wi, P2(u.first, u.second));
+            float D = distr.eval(m), g1 = distr.smith_g1(wi, m);
+            item("{\"type\": %d, \"au\": %.9g, \"av\": %.9g, \"vis\": %d, \"wi\": [%.9g, %.9g, %.9g], \"u\": [%.9g, %.9g], "
+                 "\"m\": [%.9g, %.9g, %.9g], \"pdf\": %.9g, \"D\": %.9g, \"G1\": %.9g}", type, al.first, al.second, vis, wi.x(), wi.y(),
+                 wi.z(), u.first, u.second, m.x(), m.y(), m.z(), pdf, D, g1);
+        }
+    }
+    close_arr();
+    // ---- RNG (include/mitsuba/core/random.h, drjit/random.h) ----
+    open_arr("tea32");
+    for (uint32_t v0 : { 0u, 1u, 12345u }) for (uint32_t v1 : { 0u, 1u, 4294967295u }) {
+        auto [a, b] = sample_tea_32<uint32_t>(v0, v1, 4);
+        item("[%u, %u, %u, %u]", v0, v1, a, b);
+    }
+    close_arr();
+    open_arr("pcg32");
+    for (auto ss : { std::pair<uint64_t, uint64_t>{ 0x853c49e6748fea9bULL, 0xda3e39cb94b95bdbULL }, { 42, 54 }, { 0, 1 } }) {
+        dr::PCG32<uint32_t> rng(1, ss.first, ss.second);
+        float f0 = rng.next_float32(), f1 = rng.next_float32(), f2 = rng.next_float32(), f3 = rng.next_float32();
+        item("[%llu, %llu, %.9g, %.9g, %.9g, %.9g]", (unsigned long long) ss.first, (unsigned long long) ss.second, f0, f1, f2, f3);
+    }
+    close_arr();
+    // ---- wavelength sampling (include/mitsuba/core/spectrum.h) ----
+    open_arr("sample_rgb_spectrum");
+    for (float u : { 0.f, 0.1f, 0.37f, 0.5f, 0.9f, 0.999f }) {
+        auto [wl, w] = sample_rgb_spectrum<float>(u);
+        item("[%.9g, %.9g, %.9g]", u, wl, w);
+    }
+    close_arr();
+    printf("\n}\n");
+    return 0;
+}

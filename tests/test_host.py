@@ -1,0 +1,150 @@
+"""Host-side logic on CPU: scene front end, plugin parameters, sample sharding (incl. a 2-process gloo run), oracle invariants."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+REF = "/root/reference"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_builtin_scenes_load(mi):
+    from mitsuba3_plt_b200 import scenes
+    a = scenes.load("cbox", resx=40, resy=30, spp=5)
+    assert a.film_size() == (40, 30) and a.flat.spp == 5
+    assert a.flat.desc.n_faces == 3 * 960 + 6 * 2 and a.flat.desc.n_emitters == 1
+    b = scenes.load("cbox-grating", resx=16, resy=16)
+    d = b.flat.desc
+    assert d.n_faces == 3 * 960 + 3 * 2
+    types = sorted(x.type for x in b.flat.bsdfs)
+    from mitsuba3_plt_b200 import capi
+    assert capi.BSDF_ROUGHGRATING in types and capi.BSDF_DIELECTRIC in types
+    g = [x for x in b.flat.bsdfs if x.type == capi.BSDF_ROUGHGRATING][0]
+    assert g.u[2] == 7 and g.u[3] == 0x10 and abs(g.f[3] - 1.509) < 1e-6 and abs(g.f[7] - 10) < 1e-6
+    assert abs(g.f[4] - 0.7) < 1e-6 and abs(g.f[5] - 0.4) < 1e-6 and abs(g.f[1] - 0.02) < 1e-7
+    assert b.integrator().max_depth == 7 and b.integrator().rr_depth == 50
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree only exists in the build container")
+def test_reference_scene_files_load(mi):
+    """the reference's own XML / PLY / PNG files go through the loaders unchanged"""
+    s = mi.load_file(f"{REF}/scenes/cbox-grating/cbox.xml", resx=32, resy=32, spp=2)
+    assert s.flat.desc.n_faces == 2886 and s.flat.desc.n_shapes == 6 and s.flat.spp == 2
+    with pytest.raises(RuntimeError, match='Plugin "path" not found'):
+        s.integrator()
+    s = mi.load_file(f"{REF}/scenes/cbox/cbox.xml")
+    assert s.film_size() == (500, 500) and s.flat.spp == 64 and s.flat.desc.n_faces == 2892
+
+
+def test_plugin_parameters_and_errors(mi):
+    it = mi.load_dict({"type": "plt"})
+    assert (it.max_depth, it.rr_depth) == (16, 4)          # plt.py:37-38
+    assert it.emissive_sourcing_area == 1e-4 and it.distant_sourcing_area == 1e-7 and it.max_angular_spread == 1e-7
+    with pytest.raises(RuntimeError, match="rr_depth"):
+        mi.load_dict({"type": "plt", "rr_depth": 0})
+    with pytest.raises(RuntimeError, match="polarized"):   # src/integrators/stokes.cpp:73-74
+        mi.load_dict({"type": "stokes", "nested": {"type": "plt"}})
+    with pytest.raises(RuntimeError):
+        mi.load_dict({"type": "volpath"})
+    with pytest.raises(ImportError):
+        mi.set_variant("cuda_ad_spectral_polarized")
+    mi.set_variant("cuda_ad_spectral_polarized", "llvm_spectral")
+    assert mi.variant() == "llvm_spectral"
+    mi.register_integrator("myplt", lambda p: mi.PLTIntegrator(p))
+    assert mi.load_dict({"type": "myplt", "max_depth": 3}).max_depth == 3
+
+
+def test_xml_defaults_refs_transforms(mi, tmp_path):
+    xml = tmp_path / "s.xml"
+    xml.write_text('''<scene version="2.1.0"><default name="w" value="8"/>
+      <sensor type="perspective"><float name="fov" value="45"/>
+        <transform name="to_world"><lookat origin="0 0 5" target="0 0 0" up="0 1 0"/></transform>
+        <film type="hdrfilm"><integer name="width" value="$w"/><integer name="height" value="$w"/>
+          <rfilter type="tent"/></film></sensor>
+      <bsdf type="roughconductor" id="m"><float name="alpha" value="0.05"/><string name="distribution" value="ggx"/></bsdf>
+      <shape type="rectangle"><ref id="m"/><transform name="to_world"><scale value="2"/><translate z="-1"/></transform></shape>
+      <shape type="sphere"><float name="radius" value="0.5"/><emitter type="area"><rgb name="radiance" value="3"/></emitter></shape>
+      <emitter type="directional"><vector name="direction" value="0 0 -1"/><spectrum name="irradiance" value="2"/></emitter>
+    </scene>''')
+    s = mi.load_file(str(xml), w=12)
+    from mitsuba3_plt_b200 import capi
+    assert s.film_size() == (12, 12) and s.flat.film.rfilter == capi.RFILTER_TENT
+    assert [x.type for x in s.flat.shapes] == [capi.SHAPE_RECTANGLE, capi.SHAPE_SPHERE]
+    assert [e.type for e in s.flat.emitters] == [capi.EMITTER_AREA, capi.EMITTER_DIRECTIONAL]
+    m = np.array(list(s.flat.sensors[0].to_world)).reshape(4, 4)
+    assert np.allclose(m[:3, 3], [0, 0, 5]) and np.allclose(m[:3, 2], [0, 0, -1])
+    p = mi.traverse(s)
+    key = next(iter(p))
+    p[key] = mi.Transform().translate([1, 2, 3])
+    p.update()
+    assert np.allclose(np.array(list(s.flat.sensors[0].to_world)).reshape(4, 4)[:3, 3], [1, 2, 3])
+    with pytest.raises(RuntimeError, match="Undefined parameter"):
+        (tmp_path / "bad.xml").write_text('<scene version="2.1.0"><integrator type="plt"><integer name="max_depth" value="$nope"/></integrator></scene>')
+        mi.load_file(str(tmp_path / "bad.xml"))
+
+
+def test_ply_round_trip(tmp_path):
+    from mitsuba3_plt_b200 import scenes
+    from mitsuba3_plt_b200.scene import load_ply
+    p, n, t, f = scenes.uv_sphere((0.1, 0.2, 0.3), 0.5)
+    scenes.write_ply(str(tmp_path / "s.ply"), p, f, n, t)
+    p2, n2, t2, f2 = load_ply(str(tmp_path / "s.ply"))
+    assert len(f2) == 960 and np.array_equal(p, p2) and np.array_equal(n, n2) and np.array_equal(t, t2) and np.array_equal(f, f2)
+
+
+def test_split_and_shard():
+    from mitsuba3_plt_b200 import shard_spp, split_subrenders
+    assert split_subrenders(1024, 1024, 1024) == (1, 1024)
+    assert split_subrenders(1920, 1080, 4096) == (2, 2048)        # C4: 8.49e9 samples > 2^32
+    with pytest.raises(RuntimeError):
+        split_subrenders(1920, 1080, 4097)
+    for spp, world in ((1024, 8), (7, 3), (1, 4), (16, 16)):
+        r = [shard_spp(spp, k, world) for k in range(world)]
+        assert r[0][0] == 0 and r[-1][1] == spp and all(r[i][1] == r[i + 1][0] for i in range(world - 1))
+
+
+def test_oracle_shards_union_and_thread_independence(oracle):
+    """per-sample results depend only on (seed, pixel, sample index): shards and thread counts do not change them"""
+    from mitsuba3_plt_b200 import scenes
+    sc = scenes.load("cbox-grating", resx=24, resy=24)
+    full = oracle.render(sc.flat, 6, seed=3, dump=True, n_threads=1)
+    par = oracle.render(sc.flat, 6, seed=3, dump=True, n_threads=4)
+    assert np.array_equal(full["radiance"].view(np.uint32), par["radiance"].view(np.uint32))
+    parts = [oracle.render(sc.flat, 6, seed=3, spp_begin=lo, spp_count=hi - lo, dump=True)["radiance"].reshape(24 * 24, hi - lo, 4)
+             for lo, hi in ((0, 2), (2, 6))]
+    union = np.concatenate(parts, axis=1).reshape(-1, 4)
+    assert np.array_equal(union.view(np.uint32), full["radiance"].view(np.uint32))
+    films = sum(oracle.render(sc.flat, 6, seed=3, spp_begin=lo, spp_count=hi - lo)["film_rgbw"] for lo, hi in ((0, 2), (2, 6)))
+    ok = np.isfinite(films) & np.isfinite(full["film_rgbw"])
+    assert np.allclose(films[ok], full["film_rgbw"][ok], rtol=1e-4, atol=1e-5)
+
+
+def test_two_rank_gloo_film_reduce():
+    """world_size-2 on CPU (gloo): each rank renders its spp shard (oracle standing in for the kernels), one SUM reduce
+    of the RGBW accumulator to rank 0 == the single-rank film"""
+    code = r'''
+import os, sys, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+import oracle_lib
+from mitsuba3_plt_b200 import scenes, shard_spp
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+sc = scenes.load("cbox", resx=16, resy=16)
+lo, hi = shard_spp(8, rank, world)
+film = torch.from_numpy(oracle_lib.render(sc.flat, 8, seed=1, spp_begin=lo, spp_count=hi - lo, n_threads=2)["film_rgbw"].copy())
+dist.reduce(film, 0, op=dist.ReduceOp.SUM)
+if rank == 0:
+    ref = oracle_lib.render(sc.flat, 8, seed=1, n_threads=2)["film_rgbw"]
+    assert np.allclose(film.numpy(), ref, rtol=1e-4, atol=1e-5), float(np.abs(film.numpy() - ref).max())
+    print("REDUCE_OK")
+dist.destroy_process_group()
+''' % (ROOT, ROOT)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29617", "-c", code] if False else
+                         [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29617", "--no-python", sys.executable, "-c", code],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert "REDUCE_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
