@@ -118,75 +118,129 @@ PLTB_HD void rough_eval_pdf(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2
     if (active) { value = F * v; pdf = p; }
 }
 
-// RoughGrating::wbsdf_eval, spectral branch (roughgrating.cpp:841-969).  Same arithmetic and summation order as the
-// reference's lx/ly/lambda loops; the per-order Bessel terms (4 orders x 4 wavelengths instead of 2 x lobes^2 x 4
-// evaluations), the incident sines and the coherence factor are hoisted out of the loops.
-PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
-    V3 H = normalize(wo + wi);
-    Grating g = make_grating(b, uv);
-    V3 reflection_dir = reflect(wi);
-    const float a_win = 2 * sqrtf(b.f[1] * b.f[2]);
-    const int half = (int) g.lobes / 2;
-    const bool one_d = g.is_1d();
-    float term[4][PLTB_MAX_LOBES / 2 + 1];
-    float coh[4], wl_um[4];
-    const float angle_offset = fabsf(unit_angle(reflection_dir, wo));
-    for (int i = 0; i < 4; ++i) {
-        wl_um[i] = wl.v[i] * 1e-3f;
-        const float a = kFourPi * g.q / (wl_um[i] * fabsf(wi.z));
-        for (int l = 0; l <= half; ++l) term[i][l] = g.axis_term(sc.bessel, a, l);
-        // Coherence(m_coherence, 1.0).inv_coherence_det(k), include/mitsuba/plt/plt.h:57-100
-        float k = kTwoPi / wl_um[i];
-        float s = k / (kTwoPi * (1.0f * 1e+3f));
-        float d00 = s * b.f[8], d01 = s * 0.f;
-        float det = fmsub(d00, d00, d01 * d01);
-        float inv_det = isnan_(det) ? 0.0f : det;
-        float ac = expf(-0.5f * angle_offset * inv_det * angle_offset);
-        coh[i] = isnan_(ac) ? 0.0f : ac;
+// RoughGrating::wbsdf_eval, spectral branch (roughgrating.cpp:841-969), in two steps with the reference's arithmetic and
+// summation order:
+//   grating_scan   walks the (lx, ly, lambda) loops and lists the lobes whose window contains wo.  Invalid lobes (|sin_o| > 1)
+//                  add exactly 0 and are skipped; the window test |unit_angle(c, wo)| < a_win (drjit sphere.h:53-60) is done on
+//                  the squared chord (for dot >= 0 the angle is 2 asin(|wo - c| / 2), monotone in |wo - c|^2; dot < 0 means an
+//                  angle >= pi/2, which only passes for a_win > pi/2, i.e. alpha > 0.6: those BSDFs take the exact test); and a
+//                  conservative pre-filter in the grating's sine space rejects lobes before their direction is reconstructed.
+//   grating_finish evaluates the per-order terms J_l(a)^2 the listed lobes need -- in one uniform (lambda, order) loop, so the
+//                  lanes of a warp that need the same term evaluate it together -- and accumulates the listed lobes in loop
+//                  order.  On cbox-grating 9 % of the NEE directions hit any window, so 12 Bessel evaluations per item (392 as
+//                  written in the reference) become ~0.4.
+struct GratingHits {
+    static constexpr int kMax = 12;
+    uint32_t need;             // bit (8 * i + l): term of order l at wavelength i is needed
+    int n;                     // lobes inside their window (may exceed kMax: then `hit` is incomplete and finish() rescans)
+    uint16_t hit[kMax];        // (lx + 4) | (ly + 4) << 4 | i << 8, in loop order
+};
+
+struct GratingLoop {
+    Grating g;
+    V2 sin_i;
+    float wl_um[4];
+    float a_win, chord_sq, awo, bwo, tolx, toly;
+    int half;
+    bool small_win;
+
+    PLTB_HD void init(const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+        g = make_grating(b, uv);
+        a_win = 2 * sqrtf(b.f[1] * b.f[2]);   // Texture::eval_1 of alpha_u / alpha_v: unclamped (roughgrating.cpp:871-874)
+        half = (int) g.lobes / 2;
+        for (int i = 0; i < 4; ++i) wl_um[i] = wl.v[i] * 1e-3f;
+        sin_i = g.sin_i(wi);
+        const float half_win = fminf(0.5f * a_win, 0.5f * kPi), chord = 2.f * sinf(half_win);
+        chord_sq = chord * chord;
+        // Pre-filter: for a valid lobe the direction c is a unit vector with c.x / |c.xz| == da and c.y / |c.yz| == db
+        // (diffractiongrating.h:211-225).  v -> v.x / |v.xz| has gradient <= 1 / |v.xz|, so |c - wo| < chord implies
+        // |da - wo.x / |wo.xz|| <= chord / (|wo.xz| - chord) (likewise in y); a 1.5x margin covers rounding.
+        small_win = a_win <= 0.5f * kPi;
+        const float pwx = sqrtf(sqr(wo.x) + sqr(wo.z)), pwy = sqrtf(sqr(wo.y) + sqr(wo.z));
+        const bool fx = small_win && pwx > 2.f * chord, fy = small_win && pwy > 2.f * chord;
+        awo = fx ? wo.x / pwx : 0.f; bwo = fy ? wo.y / pwy : 0.f;
+        tolx = fx ? 1.5f * chord / (pwx - chord) + 1e-5f : inf_f();
+        toly = fy ? 1.5f * chord / (pwy - chord) + 1e-5f : inf_f();
     }
-    const V2 sin_i = g.sin_i(wi);
-    // Window test |unit_angle(center_dir, wo)| < a_win (drjit sphere.h:53-60) without the asin / sqrt per lobe: for
-    // dot >= 0 the angle is 2 asin(|wo - c| / 2), monotone in the squared chord, so the test is chord^2 < (2 sin(a_win/2))^2;
-    // dot < 0 means angle >= pi/2, which can only pass for a_win > pi/2 (alpha > 0.6): those BSDFs take the exact path.  Lobes that fail the validity test
-    // |sin_o| <= 1 add exactly 0 and are skipped before the direction is reconstructed.
-    const float half_win = fminf(0.5f * a_win, 0.5f * kPi), chord = 2.f * sinf(half_win), chord_sq = chord * chord;
-    // Conservative pre-filter on the lobe's "sines" (da, db) before its direction is reconstructed.  For a valid lobe the
-    // direction c is a unit vector with c.x / |c.xz| == da and c.y / |c.yz| == db (diffractiongrating.h:211-225).  The map
-    // v -> v.x / |v.xz| has gradient <= 1 / |v.xz|, so |c - wo| < chord implies |da - wo.x / |wo.xz|| <= chord / (|wo.xz| -
-    // chord) (likewise for y); lobes outside that box (with a 1.5x margin for rounding) cannot pass the window test.
-    const bool small_win = a_win <= 0.5f * kPi;
-    const float pwx = sqrtf(sqr(wo.x) + sqr(wo.z)), pwy = sqrtf(sqr(wo.y) + sqr(wo.z));
-    const bool fx = small_win && pwx > 2.f * chord, fy = small_win && pwy > 2.f * chord;
-    const float awo = fx ? wo.x / pwx : 0.f, bwo = fy ? wo.y / pwy : 0.f;
-    const float tolx = fx ? 1.5f * chord / (pwx - chord) + 1e-5f : inf_f(), toly = fy ? 1.5f * chord / (pwy - chord) + 1e-5f : inf_f();
-    const float cos_g = g.dir.x, sin_g = g.dir.y;
-    S4 result = s4(0.f);
-    for (int lx = -half; lx <= half; ++lx) {
+    // calls f(lx, ly, i) for every lobe whose window contains wo, in the reference's loop order
+    template <class F> PLTB_HD void for_each_inside(V3 wo, F &&f) const {
+        const float cos_g = g.dir.x, sin_g = g.dir.y;
+        for (int lx = -half; lx <= half; ++lx) {
 #pragma unroll 1
-        for (int ly = -half; ly <= half; ++ly) {
-            const float lrx = cos_g * (float) lx - sin_g * (float) ly, lry = sin_g * (float) lx + cos_g * (float) ly;
+            for (int ly = -half; ly <= half; ++ly) {
+                const float lrx = cos_g * (float) lx - sin_g * (float) ly, lry = sin_g * (float) lx + cos_g * (float) ly;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float da = wl_um[i] * lrx * g.inv_period.x - sin_i.x, db = wl_um[i] * lry * g.inv_period.y - sin_i.y;
-                if (!(fabsf(da) <= 1.0f && fabsf(db) <= 1.0f)) continue;   // lobe_active == false: adds 0
-                if (fabsf(da - awo) > tolx || fabsf(db - bwo) > toly) continue;   // cannot be inside the window
-                const float m = (sqr(da) - 1) / (sqr(da * db) - 1), qq = 1 - sqr(db) * m;
-                const V3 c = mk3(da * sqrtf(fmaxf(0.0f, qq)), db * sqrtf(m), sqrtf(fmaxf(0.0f, 1 - sqr(da) * qq - sqr(db) * m)));
-                bool inside;
-                if (small_win) inside = dot(c, wo) >= 0.f && sqnorm(wo - c) < chord_sq;
-                else inside = fabsf(unit_angle(c, wo)) < a_win;
-                if (!inside) continue;
-                const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
-                float ix = term[i][alx], iy = one_d ? ix : term[i][aly];
-                float lobe_intensity = g.multiplier * ix * iy;
-                if (lx == 0 && ly == 0) result.v[i] += lobe_intensity;
-                else result.v[i] += lobe_intensity * coh[i];
+                for (int i = 0; i < 4; ++i) {
+                    const float da = wl_um[i] * lrx * g.inv_period.x - sin_i.x, db = wl_um[i] * lry * g.inv_period.y - sin_i.y;
+                    if (!(fabsf(da) <= 1.0f && fabsf(db) <= 1.0f)) continue;   // lobe_active == false: adds 0
+                    if (fabsf(da - awo) > tolx || fabsf(db - bwo) > toly) continue;   // cannot be inside the window
+                    const float m = (sqr(da) - 1) / (sqr(da * db) - 1), qq = 1 - sqr(db) * m;
+                    const V3 c = mk3(da * sqrtf(fmaxf(0.0f, qq)), db * sqrtf(m), sqrtf(fmaxf(0.0f, 1 - sqr(da) * qq - sqr(db) * m)));
+                    bool inside;
+                    if (small_win) inside = dot(c, wo) >= 0.f && sqnorm(wo - c) < chord_sq;
+                    else inside = fabsf(unit_angle(c, wo)) < a_win;
+                    if (inside) f(lx, ly, i);
+                }
             }
         }
     }
+};
+
+PLTB_HD void grating_scan(const GratingLoop &gl, V3 wo, GratingHits &h) {
+    h.need = 0; h.n = 0;
+    const bool one_d = gl.g.is_1d();
+    gl.for_each_inside(wo, [&](int lx, int ly, int i) {
+        const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
+        if (alx) h.need |= 1u << (8 * i + alx);
+        if (aly && !one_d) h.need |= 1u << (8 * i + aly);
+        if (h.n < GratingHits::kMax) h.hit[h.n] = (uint16_t) ((lx + 4) | ((ly + 4) << 4) | (i << 8));
+        h.n++;
+    });
+}
+
+PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const GratingLoop &gl, V3 wi, V2 uv, const S4 &wl, V3 wo,
+                          const GratingHits &h) {
+    const Grating &g = gl.g;
+    S4 result = s4(0.f);
+    if (h.n > 0) {
+        const bool one_d = g.is_1d(), rescan = h.n > GratingHits::kMax;
+        float term[4][PLTB_MAX_LOBES / 2 + 1], coh[4];
+        const float angle_offset = fabsf(unit_angle(reflect(wi), wo));
+        for (int i = 0; i < 4; ++i) {
+            const float a = kFourPi * g.q / (gl.wl_um[i] * fabsf(wi.z));
+            term[i][0] = 1.0f;
+            for (int l = 1; l <= gl.half; ++l)
+                if (rescan || (h.need >> (8 * i + l)) & 1u) term[i][l] = g.axis_term(sc.bessel, a, l);
+            // Coherence(m_coherence, 1.0).inv_coherence_det(k), include/mitsuba/plt/plt.h:57-100
+            float k = kTwoPi / gl.wl_um[i];
+            float s = k / (kTwoPi * (1.0f * 1e+3f));
+            float d00 = s * b.f[8], d01 = s * 0.f;
+            float det = fmsub(d00, d00, d01 * d01);
+            float inv_det = isnan_(det) ? 0.0f : det;
+            float ac = expf(-0.5f * angle_offset * inv_det * angle_offset);
+            coh[i] = isnan_(ac) ? 0.0f : ac;
+        }
+        auto add = [&](int lx, int ly, int i) {
+            const int alx = lx < 0 ? -lx : lx, aly = ly < 0 ? -ly : ly;
+            float ix = term[i][alx], iy = one_d ? ix : term[i][aly];
+            float lobe_intensity = g.multiplier * ix * iy;
+            if (lx == 0 && ly == 0) result.v[i] += lobe_intensity;
+            else result.v[i] += lobe_intensity * coh[i];
+        };
+        if (rescan) gl.for_each_inside(wo, add);
+        else
+            for (int k = 0; k < h.n; ++k) add((int) (h.hit[k] & 15) - 4, (int) ((h.hit[k] >> 4) & 15) - 4, (int) (h.hit[k] >> 8));
+    }
+    V3 H = normalize(wo + wi);
     S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
     if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
     return F * result;
+}
+
+PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    GratingLoop gl; gl.init(b, wi, uv, wl, wo);
+    GratingHits h; grating_scan(gl, wo, h);
+    return grating_finish(sc, b, gl, wi, uv, wl, wo, h);
 }
 
 PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
