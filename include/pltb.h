@@ -216,6 +216,7 @@ typedef struct pltb_stats {
     uint64_t grating_vertices;  /* of which on a roughgrating BSDF */
     uint64_t nee_other, nee_grating; /* NEE work items processed by the two k_nee launches (queue sizes) */
     uint64_t passes;            /* wavefront passes the render was split into */
+    uint64_t nee_grating_eval;  /* roughgrating NEE items that reached a lobe window and had their Bessel terms evaluated */
     float ms_total;             /* device time of the whole call (CUDA events) */
     /* per-kernel device time, summed over passes; filled only with PLTB_RENDER_PROFILE */
     float ms_sample, ms_nee_grating, ms_nee_other, ms_splat, ms_develop, ms_reduce, ms_copy;

@@ -80,7 +80,7 @@ class SampleDump(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("samples", u64), ("closest_rays", u64), ("shadow_rays", u64), ("kernel_launches", u64),
-                ("vertices", u64), ("grating_vertices", u64), ("nee_other", u64), ("nee_grating", u64), ("passes", u64),
+                ("vertices", u64), ("grating_vertices", u64), ("nee_other", u64), ("nee_grating", u64), ("passes", u64), ("nee_grating_eval", u64),
                 ("ms_total", f32), ("ms_sample", f32), ("ms_nee_grating", f32),
                 ("ms_nee_other", f32), ("ms_splat", f32), ("ms_develop", f32), ("ms_reduce", f32), ("ms_copy", f32)]
 

@@ -263,6 +263,7 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
     rc |= alloc((void **) &st.v_wiz_shape, nv * sizeof(float2));
     rc |= alloc((void **) &st.queue[0], nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.queue[1], nv * sizeof(uint32_t));
+    rc |= alloc((void **) &st.queue_eval, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.counts, kCountsTotal * sizeof(uint32_t));
     if (rc) { free_state(c); return rc; }
     st.chunk = chunk;
@@ -352,7 +353,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         PROF();
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
         PROF();
-        launches += 4;
+        launches += 5;
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0
@@ -397,6 +398,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         stats->vertices = h[2]; stats->grating_vertices = h[3];
         stats->nee_other = h[4]; stats->nee_grating = h[5];
         stats->passes = n_pass;
+        stats->nee_grating_eval = h[6];
         stats->kernel_launches = launches;
         CU(cudaEventElapsedTime(&stats->ms_total, c->ev[0], c->ev[1]));
         if (profile) {

@@ -142,9 +142,17 @@ __global__ void __launch_bounds__(128) k_nee(const __grid_constant__ DeviceScene
     const uint32_t *queue = st.queue[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + Class, (unsigned long long) n);   // queue sizes
+    DevPush push;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee<Class>(sc, st, queue[e], cnt);
+        stage_nee<Class>(sc, st, queue[e], push, cnt);
     flush_counters(cnt, st.counters);
+}
+
+__global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+    const uint32_t n = st.counts[kCountsNee + 2];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 6, (unsigned long long) n);
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_nee_eval(sc, st, st.queue_eval[e]);
 }
 
 __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
@@ -184,7 +192,7 @@ void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, i
     else k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce);
 }
 void launch_nee(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
-    if (cls) k_nee<1><<<grid, 128, 0, s>>>(sc, st);
+    if (cls) { k_nee<1><<<grid, 128, 0, s>>>(sc, st); k_nee_eval<<<grid, 128, 0, s>>>(sc, st); }
     else k_nee<0><<<grid, 128, 0, s>>>(sc, st);
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,

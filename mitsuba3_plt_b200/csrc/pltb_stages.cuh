@@ -177,8 +177,8 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 }
 
 // solve_replay_NEE (plt.py:221-300) for one queued vertex
-template <int Class>
-PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entry, uint32_t cnt[4]) {
+template <int Class, class Push>
+PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push, uint32_t cnt[4]) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
     float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r];
@@ -226,11 +226,53 @@ PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entr
     S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
     V3 wo = si.sh.to_local(ds.d);
     const pltb_bsdf *b = si_bsdf(sc, si.shape);
+    S4 a = f4_to_s4(st.v_alpha[r]);
+    if (Class == 1) {
+        // RoughGrating::wbsdf_eval is only non-zero inside the few-degree windows around the diffraction lobes: 9 % of the NEE
+        // directions on cbox-grating, 6 % once unlit samples are excluded.  For well-formed inputs (finite, unit wi / wo,
+        // finite throughput: then every factor of the product is finite) an unlit sample or one outside every window
+        // contributes exactly 0, as in the reference; the rest is compacted into `queue_eval` so that the Bessel terms are
+        // evaluated by dense warps (k_nee_eval).  Anything else takes the generic path below.
+        V3 wi_f = si.wi, wo_f = wo;
+        twosided_flip(b, wi_f, wo_f);
+        const float fsum = wi_f.x + wi_f.y + wi_f.z + wo_f.x + wo_f.y + wo_f.z + a.v[0] + a.v[1] + a.v[2] + a.v[3] +
+                           em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
+        const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
+        if (sane) {
+            const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
+            bool inside = false;
+            if (lit) {
+                GratingLoop gl; gl.init(*b, wi_f, si.uv, wl, wo_f);
+                GratingHits h; grating_scan(gl, wo_f, h);
+                inside = h.n > 0;
+            }
+            if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
+            float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
+            float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
+            st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
+            st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);       // v_w is free once the sample phase is over
+            push(st.queue_eval, st.counts + kCountsNee + 2, entry);
+            return;
+        }
+    }
     S4 bsdf_val = wbsdf_eval<Class>(sc, b, si.wi, si.uv, wl, wo);
     float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-    S4 a = f4_to_s4(st.v_alpha[r]);
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
+}
+
+// second half of solve_replay_NEE for the roughgrating vertices whose light direction falls inside a lobe window
+PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t entry) {
+    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = (size_t) depth * st.chunk + local;
+    const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
+    const float2 ws = st.v_wiz_shape[r];
+    const V3 wi = mk3(a2.w, a3.w, ws.x), wo = mk3(w4.x, w4.y, w4.z);
+    const V2 uv = mk2(a0.w, a1.w);
+    const S4 wl = f4_to_s4(st.wl[local]);
+    const pltb_bsdf *b = si_bsdf(sc, (int32_t) f2u(ws.y));
+    S4 bsdf_val = wbsdf_eval<1>(sc, b, wi, uv, wl, wo);
+    st.v_nee[r] = s4_to_f4((f4_to_s4(st.v_nee[r]) * bsdf_val) * f4_to_s4(st.v_alpha[r]));
 }
 
 // plt_solve_phase accumulation order (plt.py:191-216) + _splat_to_block (common.py:370-397); returns L
