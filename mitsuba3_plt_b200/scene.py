@@ -181,7 +181,10 @@ class FlatScene:
                 off = self._push_data(self.d65_table(scale))
                 return self._add_tex(type=capi.TEX_D65, flags=1, offset=off, count=95,
                                      p=[coeff[0], coeff[1], coeff[2], 360.0, 830.0])
-            if np.any(rgb < 0) or np.any(rgb > 1):
+            # xml.cpp:49-51,1153-1154: eta / k / int_ior / ext_ior become `srgb` with unbounded=true (no range check; the
+            # coefficient fetch itself still clamps to [0, 1], ext/rgb2spec/rgb2spec.c:80-82)
+            unbounded = name in ("eta", "k", "int_ior", "ext_ior")
+            if (np.any(rgb < 0) or np.any(rgb > 1)) and not unbounded:
                 raise RuntimeError(f"Invalid RGB reflectance value {list(rgb)}, must be in the range [0, 1]!")
             coeff = spectra.srgb_model_fetch(rgb)
             return self._add_tex(type=capi.TEX_SRGB, p=list(coeff), mean=float(np.asarray(spectra.srgb_model_mean(coeff)).reshape(-1)[0]))

@@ -11,6 +11,7 @@ Measured from the reference meshes (scenes/cbox*/meshes/*.ply): box = [-1,1]^3, 
 0.50592, spheres centred at (-0.4782,-0.64555,-0.1665) r 0.3568, (0.1512,-0.7712,0.5576) r 0.2274,
 (0.4599,-0.69485,-0.1575) r 0.2988.
 """
+import math
 import os
 import struct
 import tempfile
@@ -173,19 +174,140 @@ def write_cbox(directory, grating):
     return path
 
 
-_BUILDERS = {"cbox": lambda d: write_cbox(d, False), "cbox-grating": lambda d: write_cbox(d, True)}
+def _xf(m):
+    return '<transform name="to_world"><matrix value="' + " ".join(repr(float(v)) for v in m) + '"/></transform>'
+
+
+def write_veach_mis(directory):
+    """C4 (`scenes/veach-mis/scene.xml`) equivalent: four tilted `cube` plates with Beckmann rough conductors of increasing
+    roughness, two diffuse `rectangle` walls, three spherical area lights of radius 1 / 0.5 / 0.05, tent filter."""
+    os.makedirs(directory, exist_ok=True)
+    x = ['<scene version="3.0.0">\n  <default name="integrator" value="plt"/>\n  <default name="spp" value="512"/>\n'
+         '  <default name="resy" value="720"/>\n  <default name="resx" value="1280"/>\n  <default name="max_depth" value="7"/>\n'
+         '  <integrator type="$integrator"><integer name="max_depth" value="$max_depth"/>'
+         '<integer name="rr_depth" value="50"/></integrator>\n'
+         '  <sensor type="perspective"><float name="fov" value="35"/>' +
+         _xf([-4.37113e-08, 0, -1, 28.2792, 0, 1, 0, 3.5, 1, 0, -4.37113e-08, 1.23612e-06, 0, 0, 0, 1]) +
+         '<sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>'
+         '<film type="hdrfilm"><integer name="width" value="$resx"/><integer name="height" value="$resy"/>'
+         '<string name="pixel_format" value="rgb"/><rfilter type="tent"/></film></sensor>\n']
+    x.append(_diffuse("DiffuseBSDF", "0.5, 0.5, 0.5"))
+    x.append(_diffuse("NullBSDF", "0, 0, 0"))
+    plates = [("Smooth", 0.01, [0.805757, 0.0961775, 0, 0.264069, -0.673242, 0.115108, 0, 4.09801]),
+              ("Glossy", 0.05, [0.972057, 0.0567134, 0, 3.06163, -0.396994, 0.138865, 0, 2.71702]),
+              ("Rough", 0.1, [1.03191, 0.0277252, 0, 7.09981, -0.194077, 0.147415, 0, 1.81891]),
+              ("SuperRough", 0.25, [1.04217, 0.0182831, 0, 10.6769, -0.127982, 0.148882, 0, 1.23376])]
+    for name, alpha, rows in plates:
+        x.append(f'  <bsdf type="twosided" id="{name}BSDF"><bsdf type="roughconductor"><float name="alpha" value="{alpha}"/>'
+                 '<string name="distribution" value="beckmann"/><rgb name="specular_reflectance" value="0.3, 0.3, 0.3"/>'
+                 '<rgb name="eta" value="0.200438, 0.924033, 1.10221"/><rgb name="k" value="3.91295, 2.45285, 2.14219"/>'
+                 '</bsdf></bsdf>\n')
+    for name, alpha, rows in plates:
+        x.append(f'  <shape type="cube" id="{name}">{_xf(rows + [0, 0, 4, 0, 0, 0, 0, 1])}<ref id="{name}BSDF"/></shape>\n')
+    x.append('  <shape type="rectangle">' + _xf([9.9, 0, 0, 4.9, 0, -4.32743e-07, 9.9, 0, 0, -23.76, -1.03858e-06, 0, 0, 0, 0, 1]) +
+             '<ref id="DiffuseBSDF"/></shape>\n')
+    x.append('  <shape type="rectangle">' +
+             _xf([-4.32743e-07, -4.32743e-07, 9.9, -5, -9.9, 1.89158e-14, -4.32743e-07, 9.9, 0, -23.76, -1.03858e-06, 0, 0, 0, 0, 1]) +
+             '<ref id="DiffuseBSDF"/></shape>\n')
+    for r, z, L in ((1, -2.8, 7.59909), (0.5, 0, 30.3964), (0.05, 2.7, 3039.64)):
+        x.append(f'  <shape type="sphere"><float name="radius" value="{r}"/><point name="center" x="0" y="6.5" z="{z}"/>'
+                 f'<ref id="NullBSDF"/><emitter type="area"><rgb name="radiance" value="{L}, {L}, {L}"/></emitter></shape>\n')
+    x.append("</scene>\n")
+    path = os.path.join(directory, "scene.xml")
+    with open(path, "w") as f:
+        f.write("".join(x))
+    return path
+
+
+def _grating_diffract(wi, lobe, wl_um, inv_period, grating_angle=0.0):
+    """DiffractionGrating::diffract (include/mitsuba/plt/diffractiongrating.h:201-226), non-radial grating, float64;
+    only used to place the spectrograph's sensors."""
+    gd = (math.cos(grating_angle), math.sin(grating_angle))
+    sin_i = []
+    for c in (wi[0], wi[1]):
+        pp = math.sqrt(c * c + wi[2] * wi[2])
+        sin_i.append(c / pp if pp > 1.1920929e-07 else 0.0)
+    lr = (gd[0] * lobe[0] - gd[1] * lobe[1], gd[1] * lobe[0] + gd[0] * lobe[1])
+    a = wl_um * lr[0] * inv_period[0] - sin_i[0]
+    b = wl_um * lr[1] * inv_period[1] - sin_i[1]
+    m = (a * a - 1) / (a * a * b * b - 1)
+    q = 1 - b * b * m
+    return (a * math.sqrt(max(0.0, q)), b * math.sqrt(m), math.sqrt(max(0.0, 1 - a * a * q - b * b * m)))
+
+
+def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_wl=400.0, max_wl=700.0, use_srfs=True):
+    """C3: the scene `scripts/spectrograph/scene.py:57-175` builds -- a batch of `n` orthographic 1x1 sensors, each looking
+    along the second-order diffraction direction of its wavelength with a Gaussian SRF (`gen_srfs.py`), one `rectangle`
+    with a ggx sinusoidal `roughgrating`, one `directional` light whose irradiance is `spectrum`:
+    "bbody_<K>" (blackbody), "d65", "prior" (uniform 1)."""
+    from .xmlscene import look_at
+    os.makedirs(os.path.join(directory, "spectra"), exist_ok=True)
+    delta = (max_wl - min_wl) / (n + 2)
+    domain = np.linspace(min_wl, max_wl, points)
+    measured = np.linspace(min_wl, max_wl, n + 2)[1:-1]
+    # shading frame of the patch (s, t, n) and the light direction (scene.py:82-93)
+    fs, ft, fn = (0.0, -1.0, 0.0), (0.0, 0.0, 1.0), (1.0, 0.0, 0.0)
+    inc = math.radians(-15) - math.pi / 2
+    light = (math.sin(inc), 0.0, math.cos(inc))
+    to_local = lambda v: tuple(sum(a * b for a, b in zip(f, v)) for f in (fs, ft, fn))
+    to_world = lambda v: tuple(fs[i] * v[0] + ft[i] * v[1] + fn[i] * v[2] for i in range(3))
+    ll = to_local(light)
+    x = ['<scene version="2.1.0">\n  <default name="spp" value="512"/>\n'
+         '  <integrator type="plt"><integer name="max_depth" value="7"/><integer name="rr_depth" value="50"/></integrator>\n'
+         '  <sensor type="batch">\n']
+    for i, wl in enumerate(measured):
+        std = delta / 4
+        srf = np.exp(-np.square(domain - wl) / (2 * std ** 2))
+        srf /= np.trapezoid(srf, domain)
+        with open(os.path.join(directory, "spectra", f"srf_{i}.spd"), "w") as f:
+            for a, b in zip(domain, srf):
+                f.write(f"{np.float32(a)!r} {np.float32(b)!r}\n".replace("np.float32(", "").replace(")", ""))
+        d = to_world(_grating_diffract((-ll[0], -ll[1], -ll[2]), (2, 0), float(wl) * 1e-3, (0.7, 0.7)))
+        m = look_at([0.4 * c for c in d], [0, 0, 0], [0, 0, 1])
+        srf_xml = f'<spectrum name="srf" filename="spectra/srf_{i}.spd"/>' if use_srfs else ""
+        x.append(f'    <sensor type="orthographic" name="sensor{i}">{_xf(m.reshape(-1))}<film type="hdrfilm">'
+                 '<integer name="width" value="1"/><integer name="height" value="1"/>'
+                 f'<boolean name="sample_border" value="false"/></film>{srf_xml}</sensor>\n')
+    x.append(f'    <film type="hdrfilm"><integer name="width" value="{n}"/><integer name="height" value="1"/>'
+             '<boolean name="sample_border" value="false"/></film>\n'
+             '    <sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>\n  </sensor>\n')
+    if spectrum.startswith("bbody_"):
+        irr = f'<spectrum type="blackbody" name="irradiance"><float name="temperature" value="{float(spectrum[6:])}"/></spectrum>'
+    elif spectrum == "d65":
+        irr = '<spectrum type="d65" name="irradiance"/>'
+    elif spectrum == "prior":
+        irr = '<spectrum type="uniform" name="irradiance"><float name="value" value="1.0"/></spectrum>'
+    else:
+        raise RuntimeError(f'spectrograph: unknown spectrum "{spectrum}"')
+    x.append(f'  <emitter type="directional"><vector name="direction" x="{light[0]!r}" y="{light[1]!r}" z="{light[2]!r}"/>'
+             f'{irr}</emitter>\n')
+    x.append('  <shape type="rectangle"><bsdf type="twosided"><bsdf type="roughgrating">'
+             '<string name="distribution" value="ggx"/><string name="lobe_type" value="sinusoidal"/>'
+             '<float name="height" value="0.05"/><float name="inv_period_x" value="0.7"/><float name="inv_period_y" value="0.7"/>'
+             '<boolean name="radial" value="false"/><integer name="lobes" value="5"/><float name="multiplier" value="10.0"/>'
+             '<float name="grating_angle" value="0.0"/><float name="alpha" value="0.03"/></bsdf></bsdf>' +
+             _xf([0, 0, 0.1, 0, -0.1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 1]) + '</shape>\n</scene>\n')
+    path = os.path.join(directory, "scene.xml")
+    with open(path, "w") as f:
+        f.write("".join(x))
+    return path
+
+
+_BUILDERS = {"cbox": lambda d: write_cbox(d, False), "cbox-grating": lambda d: write_cbox(d, True),
+             "veach-mis": write_veach_mis, "spectrograph": write_spectrograph}
 
 
 def scene_path(name, cache_dir=None):
     """Materialise builtin scene `name` (once per process/cache dir) and return the path of its XML file."""
-    if name not in _BUILDERS:
+    base, _, arg = name.partition(":")   # "spectrograph:d65", "spectrograph:bbody_3000", "spectrograph:prior"
+    if base not in _BUILDERS:
         raise RuntimeError(f'unknown builtin scene "{name}" (have: {", ".join(sorted(_BUILDERS))})')
     cache_dir = cache_dir or os.path.join(tempfile.gettempdir(), f"pltb200_scenes_{os.getuid()}")
-    d = os.path.join(cache_dir, name)
+    d = os.path.join(cache_dir, name.replace(":", "_"))
     xml = os.path.join(d, "scene.xml")
     if not os.path.exists(xml):
         tmp = tempfile.mkdtemp(dir=os.path.dirname(d) if os.path.isdir(os.path.dirname(d)) else None)
-        _BUILDERS[name](tmp)
+        _BUILDERS[base](tmp, arg) if arg else _BUILDERS[base](tmp)
         os.makedirs(cache_dir, exist_ok=True)
         try:
             os.rename(tmp, d)
