@@ -141,7 +141,7 @@ struct GratingLoop {
     V2 sin_i;
     float wl_um[4];
     float a_win, chord_sq, awo, bwo, tolx, toly;
-    int half;
+    int half, lx0, lx1, ly0, ly1;   // lobe ranges that can pass the pre-filter (whole [-half, half] when it is off)
     bool small_win;
 
     PLTB_HD void init(const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
@@ -161,13 +161,42 @@ struct GratingLoop {
         awo = fx ? wo.x / pwx : 0.f; bwo = fy ? wo.y / pwy : 0.f;
         tolx = fx ? 1.5f * chord / (pwx - chord) + 1e-5f : inf_f();
         toly = fy ? 1.5f * chord / (pwy - chord) + 1e-5f : inf_f();
+        // The same two tests bound the lobe indices: per wavelength the rotated lobe (lrx, lry) must lie in a box around
+        // ((awo + sin_i.x) / (wl ipx), (bwo + sin_i.y) / (wl ipy)); rotating the union of the four boxes back gives integer
+        // ranges for lx, ly.  The loops below still apply the tests themselves, so this only skips iterations that fail them
+        // (196 -> ~10 per item on cbox-grating); margins cover the rounding of this float arithmetic.
+        lx0 = ly0 = -half; lx1 = ly1 = half;
+        if (fx && fy && g.inv_period.x > 1e-6f && g.inv_period.y > 1e-6f) {
+            float ax0 = inf_f(), ax1 = -inf_f(), ay0 = inf_f(), ay1 = -inf_f();
+            const float cx0 = fmaxf(awo - tolx, -1.f) + sin_i.x, cx1 = fminf(awo + tolx, 1.f) + sin_i.x;
+            const float cy0 = fmaxf(bwo - toly, -1.f) + sin_i.y, cy1 = fminf(bwo + toly, 1.f) + sin_i.y;
+            for (int i = 0; i < 4; ++i) {
+                const float rx = 1.f / (wl_um[i] * g.inv_period.x), ry = 1.f / (wl_um[i] * g.inv_period.y);
+                ax0 = fminf(ax0, fminf(cx0 * rx, cx1 * rx)); ax1 = fmaxf(ax1, fmaxf(cx0 * rx, cx1 * rx));
+                ay0 = fminf(ay0, fminf(cy0 * ry, cy1 * ry)); ay1 = fmaxf(ay1, fmaxf(cy0 * ry, cy1 * ry));
+            }
+            if (ax0 <= ax1 && ay0 <= ay1 && finite_(ax0 + ax1 + ay0 + ay1)) {
+                const float mx = 1e-3f * (1.f + fmaxf(fabsf(ax0), fabsf(ax1))), my = 1e-3f * (1.f + fmaxf(fabsf(ay0), fabsf(ay1)));
+                ax0 -= mx; ax1 += mx; ay0 -= my; ay1 += my;
+                const float cg = g.dir.x, sg = g.dir.y;   // l = R^T lr
+                const float xa = cg * ax0, xb = cg * ax1, xc = sg * ay0, xd = sg * ay1;
+                const float ya = -sg * ax0, yb = -sg * ax1, yc = cg * ay0, yd = cg * ay1;
+                const float fl0 = fminf(xa, xb) + fminf(xc, xd) - 0.01f, fl1 = fmaxf(xa, xb) + fmaxf(xc, xd) + 0.01f;
+                const float gl0 = fminf(ya, yb) + fminf(yc, yd) - 0.01f, gl1 = fmaxf(ya, yb) + fmaxf(yc, yd) + 0.01f;
+                const float fh = (float) half;
+                lx0 = (int) ceilf(fmaxf(fl0, -fh)); lx1 = (int) floorf(fminf(fl1, fh));
+                ly0 = (int) ceilf(fmaxf(gl0, -fh)); ly1 = (int) floorf(fminf(gl1, fh));
+            } else if (!(ax0 <= ax1 && ay0 <= ay1)) {
+                lx0 = 1; lx1 = 0;   // the box is empty (NaN-free): nothing can pass
+            }
+        }
     }
     // calls f(lx, ly, i) for every lobe whose window contains wo, in the reference's loop order
     template <class F> PLTB_HD void for_each_inside(V3 wo, F &&f) const {
         const float cos_g = g.dir.x, sin_g = g.dir.y;
-        for (int lx = -half; lx <= half; ++lx) {
+        for (int lx = lx0; lx <= lx1; ++lx) {
 #pragma unroll 1
-            for (int ly = -half; ly <= half; ++ly) {
+            for (int ly = ly0; ly <= ly1; ++ly) {
                 const float lrx = cos_g * (float) lx - sin_g * (float) ly, lry = sin_g * (float) lx + cos_g * (float) ly;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {

@@ -264,6 +264,7 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
     rc |= alloc((void **) &st.queue[0], nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.queue[1], nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.queue_eval, nv * sizeof(uint32_t));
+    rc |= alloc((void **) &st.shadow_q, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.counts, kCountsTotal * sizeof(uint32_t));
     if (rc) { free_state(c); return rc; }
     st.chunk = chunk;
@@ -347,13 +348,14 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
             if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches += 2; }
         }
         PROF();
-        launch_nee(scene->dev, st, 1, nee_grid, s);
+        launch_nee_light(scene->dev, st, nee_grid, s);
+        launch_nee_post(scene->dev, st, 0, nee_grid, s);
         PROF();
-        launch_nee(scene->dev, st, 0, nee_grid, s);
+        launch_nee_post(scene->dev, st, 1, nee_grid, s);
         PROF();
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
         PROF();
-        launches += 5;
+        launches += 8;
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0
@@ -406,8 +408,8 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
             for (uint64_t p = 0; p < n_pass; ++p) {
                 cudaEvent_t *e = &c->prof[5 * p];
                 CU(cudaEventElapsedTime(&ms, e[0], e[1])); stats->ms_sample += ms;
-                CU(cudaEventElapsedTime(&ms, e[1], e[2])); stats->ms_nee_grating += ms;
-                CU(cudaEventElapsedTime(&ms, e[2], e[3])); stats->ms_nee_other += ms;
+                CU(cudaEventElapsedTime(&ms, e[1], e[2])); stats->ms_nee_other += ms;     // light + shadow rays + post<0>
+                CU(cudaEventElapsedTime(&ms, e[2], e[3])); stats->ms_nee_grating += ms;   // post<1> + eval
                 CU(cudaEventElapsedTime(&ms, e[3], e[4])); stats->ms_splat += ms;
             }
             cudaEvent_t *t = &c->prof[5 * n_pass];

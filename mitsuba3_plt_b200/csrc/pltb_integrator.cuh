@@ -243,15 +243,16 @@ struct PassState {
     uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
     uint32_t *shade_q[2];      // hits of the current bounce by material class: 0 everything else, 1 roughgrating
     uint32_t *queue[2];        // NEE work items of the whole pass: entry = sample_local | depth << 27
-    uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee<1> -> k_nee_eval)
+    uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee_post<1> -> k_nee_eval)
+    uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>)
     // counters, zeroed once per pass: [4 * i + 0] live count of bounce i, [4 * i + 1 + c] shade_q[c] count of bounce i;
-    // the NEE queue counts sit at [4 * PLTB_MAX_DEPTH + 4 + c], the queue_eval count after them
+    // the NEE queue counts sit at [kCountsNee + c], then the queue_eval count, the shadow_q count and the shadow-ray cursor
     uint32_t *counts;
     // statistics
     unsigned long long *counters;  // closest, shadow, vertices, grating vertices, nee_other, nee_grating
 };
 constexpr int kCountsNee = 4 * PLTB_MAX_DEPTH + 4;
-constexpr int kCountsTotal = kCountsNee + 3;
+constexpr int kCountsTotal = kCountsNee + 5;
 
 struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;

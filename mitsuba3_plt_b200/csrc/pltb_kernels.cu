@@ -61,16 +61,18 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
 // two thirds of the lanes idle.  Persistent warps instead: every lane owns a resumable Traversal; whenever lanes finish, the
 // warp reserves new rays for them with one atomicAdd on the bounce's cursor, then all lanes advance by a bounded number of
 // inner-node steps followed by one leaf step (while-while order).
+// Shadow = true: the same loop over the NEE shadow-ray list (any-hit; an occluded vertex gets ds.pdf = 0 in its record).
+template <bool Shadow>
 __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
-    const uint32_t n = st.counts[4 * bounce];
-    uint32_t *cursor = st.counts + 4 * bounce + 3;
+    const uint32_t n = Shadow ? st.counts[kCountsNee + 3] : st.counts[4 * bounce];
+    uint32_t *cursor = Shadow ? st.counts + kCountsNee + 4 : st.counts + 4 * bounce + 3;
     const unsigned lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     Traversal tr;
     tr.done = true;
     bool active = false, exhausted = false;
-    uint32_t local = 0;
+    size_t local = 0;   // path id (closest hit) or vertex record index (shadow)
     for (;;) {
         __syncwarp();
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -82,12 +84,19 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
             if (!active) {
                 const uint32_t e = base + __popc(need & lt_mask);
                 if (e < n) {
-                    local = st.live[e];
-                    float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
-                    Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
+                    Ray ray;
+                    if (Shadow) {
+                        const uint32_t entry = st.shadow_q[e];
+                        local = (size_t) (entry >> 27) * st.chunk + (entry & 0x7FFFFFFu);
+                        ray = nee_shadow_ray(st, local);
+                    } else {
+                        local = st.live[e];
+                        float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
+                        ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
+                        cnt[0]++;
+                    }
                     tr.begin(sc, ray);
                     active = true;
-                    cnt[0]++;
                 }
             }
             exhausted = base + __popc(need) >= n;   // warp-uniform
@@ -96,8 +105,13 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
 #pragma unroll 1
         for (int k = 0; k < 6; ++k)
             if (active && !tr.done && tr.node >= 0) tr.inner_step(sc);
-        if (active && !tr.done && tr.node < 0) tr.leaf_step<false>(sc);
+        if (active && !tr.done && tr.node < 0) tr.template leaf_step<Shadow>(sc);
         if (active && tr.done) {
+            if (Shadow) {
+                if (tr.best.shape >= 0) st.v_w[local].w = 0.f;   // occluded: ds.pdf = 0 (scene.cpp:330-340)
+                active = false;
+                continue;
+            }
             // results are written in place; k_classify walks the live list in order afterwards so that the shade / NEE work
             // lists stay (nearly) sorted by sample id and the per-sample state accesses of later kernels stay coalesced
             st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? 0xFFFFFFFFu : tr.best.prim));
@@ -136,16 +150,26 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceSce
     flush_counters(cnt, st.counters);
 }
 
-template <int Class>
-__global__ void __launch_bounds__(128) k_nee(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[kCountsNee + Class];
-    const uint32_t *queue = st.queue[Class];
+// NEE step 1 for the queue of one material class (the stage itself is class-independent)
+__global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                                   int cls) {
+    const uint32_t n = st.counts[kCountsNee + cls];
+    const uint32_t *queue = st.queue[cls];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + Class, (unsigned long long) n);   // queue sizes
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + cls, (unsigned long long) n);   // queue sizes
     DevPush push;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee<Class>(sc, st, queue[e], push, cnt);
+        stage_nee_light(sc, st, queue[e], push, cnt);
     flush_counters(cnt, st.counters);
+}
+
+template <int Class>
+__global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+    const uint32_t n = st.counts[kCountsNee + Class];
+    const uint32_t *queue = st.queue[Class];
+    DevPush push;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_nee_post<Class>(sc, st, queue[e], push);
 }
 
 __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
@@ -184,16 +208,22 @@ void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams 
     k_raygen<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp);
 }
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
-    k_trace<<<grid, 128, 0, s>>>(sc, st, bounce);
+    k_trace<false><<<grid, 128, 0, s>>>(sc, st, bounce);
     k_classify<<<grid, 256, 0, s>>>(sc, st, bounce);
 }
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
     if (cls) k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce);
     else k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce);
 }
-void launch_nee(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
-    if (cls) { k_nee<1><<<grid, 128, 0, s>>>(sc, st); k_nee_eval<<<grid, 128, 0, s>>>(sc, st); }
-    else k_nee<0><<<grid, 128, 0, s>>>(sc, st);
+// emitter sampling for both queues, then all shadow rays in one persistent-warp launch
+void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s) {
+    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 1);
+    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 0);
+    k_trace<true><<<grid, 128, 0, s>>>(sc, st, 0);
+}
+void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
+    if (cls) { k_nee_post<1><<<grid, 128, 0, s>>>(sc, st); k_nee_eval<<<grid, 128, 0, s>>>(sc, st); }
+    else k_nee_post<0><<<grid, 128, 0, s>>>(sc, st);
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint64_t dump_cap, cudaStream_t s) {

@@ -176,19 +176,20 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     }
 }
 
-// solve_replay_NEE (plt.py:221-300) for one queued vertex
-template <int Class, class Push>
-PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push, uint32_t cnt[4]) {
+// solve_replay_NEE (plt.py:221-300) for one queued vertex, in three steps so that every step runs in dense warps:
+//   stage_nee_light  emitter sampling (Scene::sample_emitter_direction without the visibility test) and the emitter weight of
+//                    the unoccluded sample; vertices with a non-zero pdf are appended to the shadow-ray list
+//   k_trace<true>    any-hit traversal of the shadow rays by persistent warps; an occluded sample gets ds.pdf = 0, which is
+//                    what scene.cpp:330-340 does
+//   stage_nee_post   wbsdf_eval / wbsdf_pdf, MIS weight, times the replayed throughput
+// Between the steps the vertex record carries {ds.p, +-ds.pdf (sign bit: ds.delta)} in v_w (free once the sample phase is
+// over) and the emitter weight in v_nee.
+template <class Push>
+PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push, uint32_t cnt[4]) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
-    float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r];
-    float2 ws = st.v_wiz_shape[r];
-    SI si;
-    si.t = 0.f;
-    si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z); si.uv = mk2(a0.w, a1.w);
-    si.sh.s = mk3(a2.x, a2.y, a2.z); si.sh.n = mk3(a3.x, a3.y, a3.z); si.sh.t = cross(si.sh.n, si.sh.s);
-    si.wi = mk3(a2.w, a3.w, ws.x);
-    si.shape = (int32_t) f2u(ws.y);
+    const float4 a0 = st.v_p_u[r];
+    const V3 p = mk3(a0.x, a0.y, a0.z);
     const S4 wl = f4_to_s4(st.wl[local]);
     PCG32 rng; rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local];
     for (uint32_t k = 0; k < 2 * depth; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
@@ -205,25 +206,55 @@ PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entr
     const pltb_emitter &em = sc.emitters[index];
     DirectionSample ds;
     if (em.type == PLTB_EMITTER_AREA) {
-        ds = shape_sample_direction(sc, sc.shapes[em.shape], si.p, sample);   // AreaLight::sample_direction (area.cpp:116-168)
+        ds = shape_sample_direction(sc, sc.shapes[em.shape], p, sample);   // AreaLight::sample_direction (area.cpp:116-168)
     } else {   // DirectionalEmitter::sample_direction (src/emitters/directional.cpp:149-176)
         V3 dirn = mk3(em.direction[0], em.direction[1], em.direction[2]);
         ds.d = -dirn;
         float dist = 2.f * em.bsphere_radius;
-        ds.p = fmadd3(ds.d, dist, si.p);
+        ds.p = fmadd3(ds.d, dist, p);
         ds.n = dirn; ds.pdf = 1.f; ds.delta = true; ds.dist = dist; ds.uv = mk2(0.f, 0.f);
     }
     ds.pdf *= sc.emitter_pmf;
-    if (ds.pdf != 0.f) {
-        cnt[1]++;
-        Hit sh = bvh_intersect<true>(sc, si.spawn_ray_to(ds.p));
-        if (sh.shape >= 0) ds.pdf = 0.f;
-    }
-    ds.d = normalize(ds.p - si.p);   // plt.py:264-269
+    ds.d = normalize(ds.p - p);   // plt.py:264-269
     S4 em_val = s4(0.f);
     if (em.type == PLTB_EMITTER_AREA) { if (dot(ds.d, ds.n) < 0.f) em_val = tex_eval(sc, em.radiance, wl, ds.uv); }
     else em_val = tex_eval(sc, em.radiance, wl, ds.uv);
-    S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
+    const S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
+    st.v_nee[r] = s4_to_f4(em_weight);
+    st.v_w[r] = mkf4(ds.p.x, ds.p.y, ds.p.z, ds.delta ? -ds.pdf : ds.pdf);
+    if (ds.pdf != 0.f) {
+        cnt[1]++;
+        push(st.shadow_q, st.counts + kCountsNee + 3, entry);
+    }
+}
+
+// The shadow ray of a queued vertex (SurfaceInteraction::spawn_ray_to, interaction.h:145-152), rebuilt from the record.
+PLTB_HD Ray nee_shadow_ray(const PassState &st, size_t r) {
+    const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], w4 = st.v_w[r];
+    SI si;
+    si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z);
+    return si.spawn_ray_to(mk3(w4.x, w4.y, w4.z));
+}
+
+template <int Class, class Push>
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
+    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = (size_t) depth * st.chunk + local;
+    const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
+    const float2 ws = st.v_wiz_shape[r];
+    SI si;
+    si.t = 0.f;
+    si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z); si.uv = mk2(a0.w, a1.w);
+    si.sh.s = mk3(a2.x, a2.y, a2.z); si.sh.n = mk3(a3.x, a3.y, a3.z); si.sh.t = cross(si.sh.n, si.sh.s);
+    si.wi = mk3(a2.w, a3.w, ws.x);
+    si.shape = (int32_t) f2u(ws.y);
+    const S4 wl = f4_to_s4(st.wl[local]);
+    DirectionSample ds;
+    ds.p = mk3(w4.x, w4.y, w4.z);
+    ds.delta = signbit_(w4.w);
+    ds.pdf = fabsf(w4.w);            // 0 when the shadow ray was occluded
+    ds.d = normalize(ds.p - si.p);
+    const S4 em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_nee[r]) : s4(0.f);
     V3 wo = si.sh.to_local(ds.d);
     const pltb_bsdf *b = si_bsdf(sc, si.shape);
     S4 a = f4_to_s4(st.v_alpha[r]);
@@ -250,7 +281,7 @@ PLTB_HD void stage_nee(const DeviceScene &sc, const PassState &st, uint32_t entr
             float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
             st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
-            st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);       // v_w is free once the sample phase is over
+            st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);
             push(st.queue_eval, st.counts + kCountsNee + 2, entry);
             return;
         }

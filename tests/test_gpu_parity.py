@@ -10,6 +10,9 @@ CASES = [  # (scene, res, spp, seed)
     ("cbox", 64, 8, 0),
     ("cbox-grating", 64, 8, 0),
     ("cbox-grating", 48, 16, 7),
+    ("veach-mis", 64, 8, 1),                 # C4: rough conductors, sphere lights, tent filter
+    ("spectrograph:bbody_3000", 1, 256, 0),  # C3: batch of 150 orthographic sensors with SRFs, directional blackbody light
+    ("spectrograph:d65", 1, 64, 3),
 ]
 
 
