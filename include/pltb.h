@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define PLTB_ABI_VERSION 1
+#define PLTB_ABI_VERSION 2
 #define PLTB_MAX_DEPTH 16      /* upper bound on the `max_depth` plugin parameter (plt.py:37) */
 #define PLTB_MAX_LOBES 9       /* diffractionGratingsMaxLobes (include/mitsuba/plt/diffractiongrating.h:24) */
 
@@ -82,6 +82,16 @@ enum {
     PLTB_BSDF_ROUGHCONDUCTOR = 4,/* src/bsdfs/roughconductor.cpp tex[0..2] as conductor (tex[2] may be -1),
                                                                  f[1] = alpha_u, f[2] = alpha_v, u[0] = distribution,
                                                                  u[1] = sample_visible */
+    PLTB_BSDF_PRINCIPLED = 6,    /* src/bsdfs/principled.cpp (without a transmission lobe: spec_trans absent or 0)
+                                                                 tex[0] = base_color, f[0] = eta (from `eta` or `specular`,
+                                                                 principled.cpp:217-231), f[1] = roughness, f[2] = anisotropic,
+                                                                 f[3] = metallic, f[4] = clearcoat, f[5] = clearcoat_gloss,
+                                                                 f[6] = sheen, f[7] = sheen_tint, f[8] = flatness,
+                                                                 f[9] = spec_tint, f[10] = spec_trans (lobe weights only; the
+                                                                 refraction lobe itself is not on the path and the loader
+                                                                 rejects spec_trans != 0), u[0] = PLTB_PRINCIPLED_HAS_* bits,
+                                                                 u[1..3] = float bits of main_specular / clearcoat /
+                                                                 diffuse_reflectance _sampling_rate */
     PLTB_BSDF_ROUGHGRATING = 5   /* src/bsdfs/roughgrating.cpp   as roughconductor, plus f[3] = grating_angle,
                                                                  f[4] = inv_period_x, f[5] = inv_period_y, f[6] = height,
                                                                  f[7] = multiplier, f[8] = coherence, u[2] = lobes,
@@ -90,13 +100,17 @@ enum {
 };
 enum { PLTB_BSDF_FLAG_TWOSIDED = 1 };   /* wrapped in src/bsdfs/twosided.cpp (single nested BRDF) */
 enum { PLTB_MICROFACET_BECKMANN = 0, PLTB_MICROFACET_GGX = 1 };
+/* get_flag() of src/bsdfs/principledhelpers.h:95-106: the property is present and not a float equal to 0 */
+enum { PLTB_PRINCIPLED_HAS_ANISOTROPIC = 1, PLTB_PRINCIPLED_HAS_METALLIC = 2, PLTB_PRINCIPLED_HAS_CLEARCOAT = 4,
+       PLTB_PRINCIPLED_HAS_SHEEN = 8, PLTB_PRINCIPLED_HAS_SHEEN_TINT = 16, PLTB_PRINCIPLED_HAS_FLATNESS = 32,
+       PLTB_PRINCIPLED_HAS_SPEC_TINT = 64, PLTB_PRINCIPLED_HAS_SPEC_TRANS = 128 };
 
 typedef struct pltb_bsdf {
     uint32_t type;
     uint32_t flags;
     int32_t tex[4];
     uint32_t u[4];
-    float f[10];
+    float f[12];
 } pltb_bsdf;
 
 /* Shapes (src/shapes/{ply,cube,rectangle,sphere}.cpp) */
@@ -172,7 +186,8 @@ typedef struct pltb_scene_desc {
     const pltb_sensor *sensors;  /* n_sensors >= 1; > 1 == `batch` sensor */
     pltb_film film;
     /* colour tables shared by the film conversion (include/mitsuba/core/spectrum.h:126-181) */
-    const float *cie_srgb;       /* 3 * 95: linear Rec.709 matching functions on [360, 830] nm, 5 nm step */
+    const float *cie_srgb;       /* 4 * 95 on [360, 830] nm, 5 nm step: linear Rec.709 matching functions R, G, B (film
+                                    conversion), then the CIE 1931 Y function (luminance() of the principled BSDF) */
 } pltb_scene_desc;
 
 /* ---- render call -------------------------------------------------------------------------------------------- */

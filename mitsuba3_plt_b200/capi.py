@@ -10,14 +10,17 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpltb200.so")
+if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu_ab.sh)
+    LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
-PLTB_ABI_VERSION = 1
+PLTB_ABI_VERSION = 2
 PLTB_MAX_DEPTH = 16
 
 # enums (include/pltb.h)
 TEX_UNIFORM, TEX_SRGB, TEX_D65, TEX_REGULAR, TEX_IRREGULAR, TEX_BITMAP, TEX_BLACKBODY = range(7)
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = range(3)
-BSDF_NULL, BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_DIELECTRIC, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHGRATING = range(6)
+BSDF_NULL, BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_DIELECTRIC, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHGRATING, BSDF_PRINCIPLED = range(7)
+PRINCIPLED_HAS = {"anisotropic": 1, "metallic": 2, "clearcoat": 4, "sheen": 8, "sheen_tint": 16, "flatness": 32, "spec_tint": 64}
 BSDF_FLAG_TWOSIDED = 1
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 SHAPE_MESH, SHAPE_SPHERE, SHAPE_RECTANGLE = range(3)
@@ -37,7 +40,7 @@ class Texture(C.Structure):
 
 
 class Bsdf(C.Structure):
-    _fields_ = [("type", u32), ("flags", u32), ("tex", i32 * 4), ("u", u32 * 4), ("f", f32 * 10)]
+    _fields_ = [("type", u32), ("flags", u32), ("tex", i32 * 4), ("u", u32 * 4), ("f", f32 * 12)]
 
 
 class Shape(C.Structure):

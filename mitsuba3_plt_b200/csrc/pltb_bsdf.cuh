@@ -2,6 +2,7 @@
 // including the TwoSidedBRDF wrapper.  JIT-variant semantics (see oracle/plt_oracle.cpp header).
 #pragma once
 #include "pltb_shading.cuh"
+#include "pltb_principled.cuh"
 
 namespace pltb {
 
@@ -51,6 +52,9 @@ PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &
             o.weight = w;
             return o;
         }
+        case PLTB_BSDF_PRINCIPLED:
+            principled_sample(sc, b, wi, uv, wl, s1, s2, o.wo, o.pdf, o.eta, o.type, o.weight);
+            return o;
         case PLTB_BSDF_ROUGHCONDUCTOR: {  // src/bsdfs/roughconductor.cpp:225-311
             if (!(cos_theta_i > 0.f)) return o;
             Microfacet distr = make_mf(b);
@@ -278,6 +282,7 @@ PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t t
         case PLTB_BSDF_DIFFUSE:  // diffuse.cpp:127-142
             if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return s4(0.f);
             return (tex_eval(sc, b.tex[0], wl, uv) * kInvPi) * cos_theta_o;
+        case PLTB_BSDF_PRINCIPLED: return principled_eval(sc, b, wi, uv, wl, wo);
         case PLTB_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:313-390
             if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return s4(0.f);
             V3 H = normalize(wo + wi);
@@ -298,6 +303,7 @@ PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
     switch (type) {
         case PLTB_BSDF_DIFFUSE: return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? kInvPi * wo.z : 0.f;
+        case PLTB_BSDF_PRINCIPLED: return principled_pdf(b, wi, wo);
         case PLTB_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:392-430
             V3 m = normalize(wo + wi);
             bool active = cos_theta_i > 0.f && cos_theta_o > 0.f && dot(wi, m) > 0.f && dot(wo, m) > 0.f;
@@ -325,6 +331,10 @@ PLTB_HD S4 bsdf_weight_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t
             if (wo.z > 0.0f) { if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv); }
             else { if (b.tex[3] >= 0) w = w * tex_eval(sc, b.tex[3], wl, uv); }
             return w;
+        }
+        case PLTB_BSDF_PRINCIPLED: {  // base wbsdf_weight: eval / pdf (bsdf.cpp:85-97)
+            float p = principled_pdf(b, wi, wo);
+            return p > 0.0f ? principled_eval(sc, b, wi, uv, wl, wo) / p : s4(0.f);
         }
         case PLTB_BSDF_ROUGHCONDUCTOR:
         case PLTB_BSDF_ROUGHGRATING: {  // base wbsdf_weight, src/render/bsdf.cpp:85-97

@@ -151,7 +151,7 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     if (d->abi_version != PLTB_ABI_VERSION) return fail(PLTB_ERR_INVALID, "pltb_scene_create: ABI version mismatch");
     if (d->n_sensors < 1) return fail(PLTB_ERR_INVALID, "pltb_scene_create: scene has no sensor");
     for (uint32_t i = 0; i < d->n_bsdfs; ++i) {
-        if (d->bsdfs[i].type > PLTB_BSDF_ROUGHGRATING) return fail(PLTB_ERR_UNSUPPORTED, "unsupported BSDF type");
+        if (d->bsdfs[i].type > PLTB_BSDF_PRINCIPLED) return fail(PLTB_ERR_UNSUPPORTED, "unsupported BSDF type");
         if (d->bsdfs[i].type == PLTB_BSDF_ROUGHGRATING && (d->bsdfs[i].u[2] < 1 || d->bsdfs[i].u[2] > PLTB_MAX_LOBES))
             return fail(PLTB_ERR_INVALID, "roughgrating: lobes must be in [1, 9]");
     }
@@ -181,7 +181,7 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     rc |= upload(s->allocs, d->emitters, d->n_emitters, &ds.emitters);
     rc |= upload(s->allocs, d->area_cdf, d->n_area_cdf, &ds.area_cdf);
     rc |= upload(s->allocs, d->sensors, d->n_sensors, &ds.sensors);
-    rc |= upload(s->allocs, d->cie_srgb, 3 * 95, &ds.cie_srgb);
+    rc |= upload(s->allocs, d->cie_srgb, 4 * 95, &ds.cie_srgb);
     if (rc) { pltb_scene_release(s); return PLTB_ERR_CUDA; }
     s->d_sensors = (pltb_sensor *) ds.sensors;
     s->sensors.assign(d->sensors, d->sensors + d->n_sensors);

@@ -33,8 +33,16 @@ PLTB_HD float fmadd(float a, float b, float c) { return fmaf(a, b, c); }
 PLTB_HD float fmsub(float a, float b, float c) { return fmaf(a, b, -c); }
 PLTB_HD float fnmadd(float a, float b, float c) { return fmaf(-a, b, c); }
 PLTB_HD float sqr(float x) { return x * x; }
+#if defined(__CUDA_ARCH__) && defined(PLTB_FAST_RCP)
+PLTB_HD float rcp(float x) { return __frcp_rn(x); }   // == 1.f / x (correctly rounded) without the division slow path
+#else
 PLTB_HD float rcp(float x) { return 1.f / x; }
+#endif
+#if defined(__CUDA_ARCH__) && defined(PLTB_FAST_RSQRT)
+PLTB_HD float rsqrt_(float x) { return rsqrtf(x); }   // MUFU.RSQ, <= 2 ulp (what Dr.Jit's CUDA backend emits for dr::rsqrt)
+#else
 PLTB_HD float rsqrt_(float x) { return 1.f / sqrtf(x); }
+#endif
 PLTB_HD float safe_sqrt(float x) { return sqrtf(fmaxf(x, 0.f)); }
 PLTB_HD uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 PLTB_HD float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
@@ -187,6 +195,33 @@ PLTB_NI float bessel_j(const BesselTables &bt, float x, int nu) {
     float center = 45.f + nu_abs;
     float weight_fn = 1.0f / (1.0f + expf(-1.5f * (fabsf(x) - center)));
     return nsign * ((1.0f - weight_fn) * bessel_j_small(bt, x, nua) + weight_fn * bessel_j_asymp(x, nua));
+}
+// Reduced-precision J_nu for *sampling decisions only* (DiffractionGrating::sample_lobe: which lobe is drawn and its discrete
+// pdf): the Simpson terms use MUFU.COS after a two-constant reduction to [-pi, pi] (absolute error ~5e-7 per term, ~1e-7 in
+// J).  Everything that scales radiance (lobe_intensity in wbsdf_sample / wbsdf_eval) keeps the precise cosf above: with the
+// nanometre-unit call of roughgrating.cpp:440 (N2) J_1 is ~4e-4, where 1e-7 would already be a 2e-4 relative error.
+PLTB_HD float cos_fast(float a) {
+#if defined(__CUDA_ARCH__)
+    const float k = rintf(a * 0.15915494309189535f);
+    float r = fmaf(-k, 6.2831854820251465f, a);
+    r = fmaf(-k, -1.7484555e-7f, r);
+    return __cosf(r);
+#else
+    return cosf(a);
+#endif
+}
+PLTB_NI float bessel_j_fast(const BesselTables &bt, float x, int nu) {   // nu >= 0
+    const float fnu = (float) nu;
+    float I_odd = 0.f, I_even = 0.f;
+#pragma unroll 1
+    for (int i = 1; i < 19; i += 2) {
+        I_odd += cos_fast(fnu * bt.t[i] - x * bt.sin_t[i]);
+        I_even += cos_fast(fnu * bt.t[i + 1] - x * bt.sin_t[i + 1]);
+    }
+    const float fa = cos_fast(fnu * bt.t[0] - x * bt.sin_t[0]), fb = cos_fast(fnu * bt.t[19] - x * bt.sin_t[19]);
+    const float small_ = kInvPi * (bt.h_over_3 * (fa + 4.0f * I_odd + 2.0f * I_even + fb));
+    const float weight_fn = 1.0f / (1.0f + expf(-1.5f * (fabsf(x) - (45.f + fnu))));
+    return (1.0f - weight_fn) * small_ + weight_fn * bessel_j_asymp(x, nu);
 }
 PLTB_HD float sinc_(float x) { float xx = fabsf(x); return xx < 1e-5f ? 1.0f : sinf(xx) / xx; }
 

@@ -224,6 +224,11 @@ struct Grating {
         if (gtype == 1) return sinf(a / 2.0f) * sinc_(kPi * fl / 2.0f);
         return 1.f / sqrtf(fabsf(fl));
     }
+    // the same for sample_lobe's selection weights (sinusoidal gratings: reduced-precision Bessel, see bessel_j_fast)
+    PLTB_HD float axis_term_select(const BesselTables &bt, float a, int l) const {
+        if (l != 0 && (type & 0xFu) == 0) return sqr(bessel_j_fast(bt, a, l));
+        return axis_term(bt, a, l);
+    }
     PLTB_HD float lobe_intensity(const BesselTables &bt, int lx, int ly, V3 wi, float wl) const {
         const float a = kFourPi * q / (wl * fabsf(wi.z));
         float ix = axis_term(bt, a, lx);
@@ -235,7 +240,9 @@ struct Grating {
         float total = 0.0f;
         const uint32_t n = lobes / 2 + 1;
         for (uint32_t l = 0; l < n; ++l) {
-            float li = lobe_intensity(bt, (int) l, 0, wi, wl);
+            // lobe_intensity((l, 0)): the y term is order 0 (== 1) unless the grating is 1-D, where it repeats the x term
+            const float a = kFourPi * q / (wl * fabsf(wi.z)), ix = axis_term_select(bt, a, (int) l);
+            float li = multiplier * ix * (is_1d() ? ix : 1.0f);
             if (l == 0) li /= 2.0f;
             total += li;
             intensities[l] = li;

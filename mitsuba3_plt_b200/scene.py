@@ -371,6 +371,36 @@ class FlatScene:
             if lt not in types:
                 raise RuntimeError(f"Grating surface type {lt} not supported!")
             b.u[3] = types[lt] | (0x10 if inner.get("radial", False) else 0)
+        elif t == "principled":  # src/bsdfs/principled.cpp:180-236
+            b.type = capi.BSDF_PRINCIPLED
+
+            def get_flag(name):  # principledhelpers.h:95-106
+                if name not in inner:
+                    return False
+                v = inner[name]
+                return not (isinstance(v, float) and v == 0.0)
+            if get_flag("spec_trans"):
+                raise RuntimeError("principled: a transmission lobe (spec_trans != 0) is outside the plt hot path")
+            b.tex[0] = self.texture(inner, "base_color", 0.5)
+            b.f[1] = self.scalar(inner, "roughness", 0.5)
+            slots = {"anisotropic": 2, "metallic": 3, "clearcoat": 4, "sheen": 6, "sheen_tint": 7, "flatness": 8, "spec_tint": 9}
+            flags = 0
+            for name, slot in slots.items():
+                b.f[slot] = self.scalar(inner, name, 0.0)
+                if get_flag(name):
+                    flags |= capi.PRINCIPLED_HAS[name]
+            b.f[5] = self.scalar(inner, "clearcoat_gloss", 0.0)
+            b.u[0] = flags
+            rates = [F32(inner.get("main_specular_sampling_rate", 1.0)), F32(inner.get("clearcoat_sampling_rate", 1.0)),
+                     F32(inner.get("diffuse_reflectance_sampling_rate", 1.0))]
+            b.u[1], b.u[2], b.u[3] = (int(np.asarray(r, dtype=F32).view(np.uint32)) for r in rates)
+            if "eta" in inner and "specular" in inner:
+                raise RuntimeError('Specified an invalid index of refraction property, either use "eta" or "specular" !')
+            if "eta" in inner:
+                b.f[0] = float(inner["eta"])
+            else:
+                specular = F32(inner.get("specular", 0.5))
+                b.f[0] = F32(2.0) * (F32(1.0) / (F32(1.0) - np.sqrt(F32(0.08) * specular, dtype=F32))) - F32(1.0)
         else:
             raise RuntimeError(f'Plugin "{t}" not found (bsdf outside the plt hot path)')
         self.bsdfs.append(b)
@@ -604,7 +634,8 @@ class FlatScene:
         self.a_cdf = cat(self.area_cdf, (0,), F32)
         if self.a_cdf.size == 0:
             self.a_cdf = np.zeros(1, F32)
-        self.a_cie = np.ascontiguousarray(spectra.cie_tables()["srgb"], dtype=F32)
+        tabs = spectra.cie_tables()
+        self.a_cie = np.ascontiguousarray(np.concatenate([tabs["srgb"], tabs["xyz"][1:2]]), dtype=F32)   # R, G, B, Y rows
         # scene bounding sphere for directional emitters (src/render/scene.cpp:70-80, BoundingSphere from bbox)
         if np.all(np.isfinite(self.bbox[0])):
             c = (self.bbox[0] + self.bbox[1]) * 0.5

@@ -219,6 +219,54 @@ def write_veach_mis(directory):
     return path
 
 
+def write_gratingcap(directory):
+    """C5 (`scenes/gratingcap/gratingcap.xml`) equivalent: a thin vertical grating strip (`Plane.ply`: x = 0, |y| <= 10.690928,
+    |z| <= 0.18630536, uv as in the file) lit by a directional light, and a half-cylinder projection screen (`Circle.ply`:
+    radius 5, 15 columns at -78.75 deg ... +78.75 deg, y in [0, 4.0269127], 28 triangles, every uv = (0, 1) as in the file)
+    with a `principled` BSDF.  Camera, materials and light copied parameter by parameter (gratingcap.xml:15-79); the file's
+    `path` integrator is replaced by the one the scripts pass (`-i plt`)."""
+    os.makedirs(os.path.join(directory, "meshes"), exist_ok=True)
+    m = lambda n: os.path.join(directory, "meshes", n)
+    hy, hz = 10.690928, 0.18630536
+    p, t, f = quad((0, -hy, hz), (0, hy, hz), (0, hy, -hz), (0, -hy, -hz), uv=((0, 1), (1, 1), (1, 0), (0, 0)))
+    write_ply(m("Plane.ply"), p, f, None, t)
+    ang = np.radians(-78.75 + 11.25 * np.arange(15))
+    pos, faces = [], []
+    for a in ang:
+        pos += [(5 * math.cos(a), 0.0, 5 * math.sin(a)), (5 * math.cos(a), 4.0269127, 5 * math.sin(a))]
+    for k in range(14):
+        a0, a1, b0, b1 = 2 * k, 2 * k + 1, 2 * k + 2, 2 * k + 3
+        faces += [(a0, b0, b1), (a0, b1, a1)]
+    write_ply(m("Circle.ply"), pos, faces, None, np.tile(np.float32([0, 1]), (30, 1)))
+    x = ['<scene version="2.1.0">\n  <default name="spp" value="512"/>\n  <default name="resx" value="800"/>\n'
+         '  <default name="resy" value="600"/>\n  <integrator type="plt"><integer name="max_depth" value="7"/>'
+         '<integer name="rr_depth" value="50"/></integrator>\n'
+         '  <sensor type="perspective" id="elm__1"><string name="fov_axis" value="x"/><float name="fov" value="39.597755"/>'
+         '<float name="principal_point_offset_x" value="0.000000"/><float name="principal_point_offset_y" value="-0.000000"/>'
+         '<float name="near_clip" value="0.100000"/><float name="far_clip" value="100.000000"/>'
+         '<transform name="to_world"><rotate x="1" angle="-153.5592908827048"/><rotate y="1" angle="59.25153588002377"/>'
+         '<rotate z="1" angle="-179.999991348578"/><translate value="-4.074883 6.534825 4.860810"/></transform>'
+         '<sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>'
+         '<film type="hdrfilm"><integer name="width" value="$resx"/><integer name="height" value="$resy"/></film></sensor>\n',
+         '  <bsdf type="twosided" id="mat-grating"><bsdf type="roughgrating"><string name="lobe_type" value="sinusoidal"/>'
+         '<float name="height" value="0.04"/><float name="inv_period" value="0.9"/><boolean name="radial" value="false"/>'
+         '<integer name="lobes" value="7"/><float name="grating_angle" value="0"/><float name="multiplier" value="10"/>'
+         '<float name="alpha" value="0.01"/></bsdf></bsdf>\n',
+         '  <bsdf type="twosided" id="mat-screen"><bsdf type="principled"><rgb value="0.800000 0.800000 0.800000" name="base_color"/>'
+         '<rgb value="1.000000 1.000000 1.000000" name="spec_tint"/><float name="spec_trans" value="0.000000"/>'
+         '<float name="metallic" value="0.000000"/><float name="anisotropic" value="0.000000"/>'
+         '<float name="roughness" value="0.250000"/><float name="sheen" value="0.000000"/>'
+         '<rgb value="1.000000 1.000000 1.000000" name="sheen_tint"/><float name="clearcoat" value="0.000000"/>'
+         '<float name="clearcoat_gloss" value="0.000900"/><float name="specular" value="0.500000"/></bsdf></bsdf>\n',
+         '  <emitter type="directional" id="elm__4"><rgb value="100.000000 100.000000 100.000000" name="irradiance"/>' +
+         _xf([0.382683, 0, -0.923880, 5, -0.923880, 0, -0.382683, 5, 0, 1, 0, 0, 0, 0, 0, 1]) + '</emitter>\n',
+         _mesh("Plane.ply", "mat-grating", True), _mesh("Circle.ply", "mat-screen", True), "</scene>\n"]
+    path = os.path.join(directory, "scene.xml")
+    with open(path, "w") as f:
+        f.write("".join(x))
+    return path
+
+
 def _grating_diffract(wi, lobe, wl_um, inv_period, grating_angle=0.0):
     """DiffractionGrating::diffract (include/mitsuba/plt/diffractiongrating.h:201-226), non-radial grating, float64;
     only used to place the spectrograph's sensors."""
@@ -294,7 +342,8 @@ def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_
 
 
 _BUILDERS = {"cbox": lambda d: write_cbox(d, False), "cbox-grating": lambda d: write_cbox(d, True),
-             "veach-mis": write_veach_mis, "spectrograph": write_spectrograph}
+             "veach-mis": write_veach_mis, "spectrograph": write_spectrograph,
+             "gratingcap": write_gratingcap}
 
 
 def scene_path(name, cache_dir=None):

@@ -923,6 +923,210 @@ inline S4 conductor_F(const Scene &sc, const pltb_bsdf &b, const SI &si, float c
     return F;
 }
 
+/* ---- principled BSDF without a transmission lobe (src/bsdfs/principled.cpp, principledhelpers.h) ------------------ */
+inline float dr_lerp(float a, float b, float t) { return fmadd(b, t, fnmadd(a, t, a)); }
+inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline float schlick_weight(float cos_i) { /* principledhelpers.h:108-112 */
+    float m = std::min(std::max(1.0f - cos_i, 0.0f), 1.0f);
+    return sqr(sqr(m)) * m;
+}
+inline float schlick_R0_eta(float eta) { return sqr((eta - 1.0f) / (eta + 1.0f)); }
+inline float calc_schlick(float R0, float cos_theta_i, float eta) { /* principledhelpers.h:114-128 */
+    bool outside = cos_theta_i >= 0.0f;
+    float rcp_eta = rcp(eta), eta_it = outside ? eta : rcp_eta, eta_ti = outside ? rcp_eta : eta;
+    float cos_theta_t_sqr = fnmadd(fnmadd(cos_theta_i, cos_theta_i, 1.0f), sqr(eta_ti), 1.0f);
+    float cos_theta_t = safe_sqrt(cos_theta_t_sqr);
+    return eta_it > 1.0f ? dr_lerp(schlick_weight(std::fabs(cos_theta_i)), 1.0f, R0) : dr_lerp(schlick_weight(cos_theta_t), 1.0f, R0);
+}
+inline bool mac_mic_compatibility(V3 m, V3 wi, V3 wo, float cos_theta_i, bool reflection) { /* :134-146 */
+    V3 ms(mulsign(m.x, cos_theta_i), mulsign(m.y, cos_theta_i), mulsign(m.z, cos_theta_i));
+    if (reflection) return dot(wi, ms) > 0.0f && dot(wo, ms) > 0.0f;
+    V3 mn(mulsign_neg(m.x, cos_theta_i), mulsign_neg(m.y, cos_theta_i), mulsign_neg(m.z, cos_theta_i));
+    return dot(wi, ms) > 0.0f && dot(wo, mn) > 0.0f;
+}
+/* mitsuba::luminance(value, wavelengths) in spectral mode: mean(cie1931_y(wl) * value) (spectrum.h:272-295,414-429) */
+inline float spectral_luminance(const Scene &sc, const S4 &value, const S4 &wl) {
+    const float *y = sc.d->cie_srgb + 3 * 95;
+    float acc[4];
+    for (int i = 0; i < 4; ++i) {
+        float t = (wl[i] - 360.f) * (94.f / (830.f - 360.f));
+        bool active = wl[i] >= 360.f && wl[i] <= 830.f;
+        uint32_t i0 = (uint32_t) std::min(std::max((int32_t) t, 0), 93), i1 = i0 + 1;
+        float w1 = t - (float) i0, w0 = 1.f - w1;
+        acc[i] = (active ? fmadd(w0, y[i0], w1 * y[i1]) : 0.f) * value[i];
+    }
+    return (acc[0] + acc[1] + acc[2] + acc[3]) * 0.25f;
+}
+struct Principled {
+    float eta, roughness, anisotropic, metallic, clearcoat, clearcoat_gloss, sheen, sheen_tint, flatness, spec_tint, spec_trans;
+    float spec_srate, clearcoat_srate, diff_refl_srate;
+    bool has_anisotropic, has_metallic, has_clearcoat, has_sheen, has_sheen_tint, has_flatness, has_spec_tint, has_spec_trans;
+    explicit Principled(const pltb_bsdf &b) {
+        const uint32_t h = b.u[0];
+        has_anisotropic = h & PLTB_PRINCIPLED_HAS_ANISOTROPIC; has_metallic = h & PLTB_PRINCIPLED_HAS_METALLIC;
+        has_clearcoat = h & PLTB_PRINCIPLED_HAS_CLEARCOAT; has_sheen = h & PLTB_PRINCIPLED_HAS_SHEEN;
+        has_sheen_tint = h & PLTB_PRINCIPLED_HAS_SHEEN_TINT; has_flatness = h & PLTB_PRINCIPLED_HAS_FLATNESS;
+        has_spec_tint = h & PLTB_PRINCIPLED_HAS_SPEC_TINT; has_spec_trans = h & PLTB_PRINCIPLED_HAS_SPEC_TRANS;
+        eta = b.f[0]; roughness = b.f[1];
+        anisotropic = has_anisotropic ? b.f[2] : 0.f; metallic = has_metallic ? b.f[3] : 0.f;
+        clearcoat = has_clearcoat ? b.f[4] : 0.f; clearcoat_gloss = b.f[5];
+        sheen = has_sheen ? b.f[6] : 0.f; sheen_tint = b.f[7];
+        flatness = has_flatness ? b.f[8] : 0.f; spec_tint = has_spec_tint ? b.f[9] : 0.f;
+        spec_trans = has_spec_trans ? b.f[10] : 0.f;
+        spec_srate = as_float(b.u[1]); clearcoat_srate = as_float(b.u[2]); diff_refl_srate = as_float(b.u[3]);
+    }
+    Microfacet spec_distr() const { /* calc_dist_params (principledhelpers.h:214-226); GGX, sample_visible */
+        float r2 = sqr(roughness);
+        if (!has_anisotropic) { float a = std::max(0.001f, r2); return Microfacet(PLTB_MICROFACET_GGX, a, a, true); }
+        float aspect = std::sqrt(1.0f - 0.9f * anisotropic);
+        return Microfacet(PLTB_MICROFACET_GGX, std::max(0.001f, r2 / aspect), std::max(0.001f, r2 * aspect), true);
+    }
+    /* lobe selection probabilities, front side, no transmission (principled.cpp:376-399 == :760-786) */
+    void probs(float F_spec, float &p_spec, float &p_cc, float &p_diff, bool front, float &p_trans) const {
+        float brdf = (1.0f - metallic) * (1.0f - spec_trans), bsdf = has_spec_trans ? (1.0f - metallic) * spec_trans : 0.0f;
+        float ps = front ? spec_srate * (1.0f - bsdf * (1.0f - F_spec)) : F_spec;
+        float pt = has_spec_trans ? (front ? spec_srate * bsdf * (1.0f - F_spec) : (1.0f - F_spec)) : 0.0f;
+        float pc = has_clearcoat ? (front ? 0.25f * clearcoat * clearcoat_srate : 0.0f) : 0.0f;
+        float pd = front ? brdf * diff_refl_srate : 0.f;
+        float rcp_tot = rcp(ps + pt + pc + pd);
+        p_spec = ps * rcp_tot; p_cc = pc * rcp_tot; p_diff = pd * rcp_tot; p_trans = pt * rcp_tot;
+    }
+};
+/* GTR1Isotropic (principledhelpers.h:17-56) */
+struct GTR1 {
+    float alpha;
+    float eval(V3 m) const {
+        float cos_theta2 = sqr(m.z), alpha2 = sqr(alpha);
+        float result = (alpha2 - 1.f) / (kPi * std::log(alpha2) * (1.f + (alpha2 - 1.f) * cos_theta2));
+        return result * m.z > 1e-20f ? result : 0.f;
+    }
+    float pdf(V3 m) const { return m.z < 0.f ? 0.f : m.z * eval(m); }
+    V3 sample(V2 s) const {
+        float ang = (2.f * kPi) * s.x, sin_phi = std::sin(ang), cos_phi = std::cos(ang), alpha2 = sqr(alpha);
+        float cos_theta2 = (1.f - std::pow(alpha2, 1.f - s.y)) / (1.f - alpha2);
+        float sin_theta = std::sqrt(std::max(0.f, 1.f - cos_theta2)), cos_theta = std::sqrt(std::max(0.f, cos_theta2));
+        return V3(cos_phi * sin_theta, sin_phi * sin_theta, cos_theta);
+    }
+};
+inline float smith_ggx1(V3 v, V3 wh, float alpha) { /* principledhelpers.h:73-93 */
+    float alpha_2 = sqr(alpha), cos_theta = std::fabs(v.z), cos_theta_2 = sqr(cos_theta), tan_theta_2 = (1.0f - cos_theta_2) / cos_theta_2;
+    float result = 2.0f * rcp(1.0f + std::sqrt(1.0f + alpha_2 * tan_theta_2));
+    if (v.z == 1.f) result = 1.f;
+    if (dot(v, wh) * v.z <= 0.f) result = 0.f;
+    return result;
+}
+
+/* Principled::eval (principled.cpp:488-712), spec_trans == 0 */
+S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
+    const Principled P(b);
+    float cos_theta_i = si.wi.z;
+    if (!(cos_theta_i != 0.0f)) return S4(0.f);
+    S4 base_color = tex_eval(sc, b.tex[0], si.wavelengths, si.uv);
+    float brdf = (1.0f - P.metallic) * (1.0f - P.spec_trans), bsdf = (1.0f - P.metallic) * P.spec_trans;
+    float cos_theta_o = wo.z;
+    bool reflect = cos_theta_i * cos_theta_o > 0.0f;
+    bool front_side = cos_theta_i > 0.0f;
+    float inv_eta = rcp(P.eta), eta_path = front_side ? P.eta : inv_eta;
+    Microfacet spec_dist = P.spec_distr();
+    V3 wh = normalize(si.wi + wo * (reflect ? 1.0f : eta_path));
+    wh = V3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
+    FresnelResult fr = fresnel(dot(si.wi, wh), P.eta);
+    float F_spec_dielectric = fr.r;
+    bool reflection_compat = mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, true);
+    bool spec_reflect_active = reflect && reflection_compat && F_spec_dielectric > 0.0f;
+    bool clearcoat_active = P.has_clearcoat && P.clearcoat > 0.0f && reflect && reflection_compat && front_side;
+    bool diffuse_active = brdf > 0.0f && reflect && front_side;
+    bool sheen_active = P.has_sheen && P.sheen > 0.0f && reflect && (1.0f - P.metallic > 0.0f) && front_side;
+    float D = spec_dist.eval(wh), G = spec_dist.G(si.wi, wo, wh);
+    S4 value(0.f);
+    if (spec_reflect_active) {
+        float lum = P.has_spec_tint ? spectral_luminance(sc, base_color, si.wavelengths) : 1.0f;
+        /* principled_fresnel (principledhelpers.h:148-186) */
+        float cti = dot(si.wi, wh);
+        bool outside = cti >= 0.0f;
+        float eta_it = outside ? P.eta : rcp(P.eta);
+        S4 F_schlick(0.f);
+        if (P.has_metallic)
+            for (int i = 0; i < 4; ++i) F_schlick[i] += P.metallic * calc_schlick(base_color[i], cti, P.eta);
+        if (P.has_spec_tint)
+            for (int i = 0; i < 4; ++i) {
+                float c_tint = lum > 0.0f ? base_color[i] / lum : 1.0f;
+                float F0 = c_tint * schlick_R0_eta(eta_it);
+                F_schlick[i] += (1.0f - P.metallic) * P.spec_tint * calc_schlick(F0, cti, P.eta);
+            }
+        for (int i = 0; i < 4; ++i) {
+            float F_front = (1.0f - P.metallic) * (1.0f - P.spec_tint) * F_spec_dielectric + F_schlick[i];
+            float Fp = front_side ? F_front : bsdf * F_spec_dielectric;
+            value[i] += Fp * D * G / (4.0f * std::fabs(cos_theta_i));
+        }
+    }
+    if (clearcoat_active) {
+        float Fcc = calc_schlick(0.04f, dot(si.wi, wh), P.eta);
+        GTR1 mf{ dr_lerp(0.1f, 0.001f, P.clearcoat_gloss) };
+        float Dcc = mf.eval(wh);
+        float G_cc = smith_ggx1(si.wi, wh, 0.25f) * smith_ggx1(wo, wh, 0.25f);
+        float add = (P.clearcoat * 0.25f) * Fcc * Dcc * G_cc * std::fabs(cos_theta_o);
+        for (int i = 0; i < 4; ++i) value[i] += add;
+    }
+    if (diffuse_active) {
+        float Fo = schlick_weight(std::fabs(cos_theta_o)), Fi = schlick_weight(std::fabs(cos_theta_i));
+        float f_diff = (1.0f - 0.5f * Fi) * (1.0f - 0.5f * Fo);
+        float cos_theta_d = dot(wh, wo);
+        float Rr = 2.0f * P.roughness * sqr(cos_theta_d);
+        float f_retro = Rr * (Fo + Fi + Fo * Fi * (Rr - 1.0f));
+        float lobe;
+        if (P.has_flatness) {
+            float Fss90 = Rr / 2.0f;
+            float Fss = dr_lerp(1.0f, Fss90, Fo) * dr_lerp(1.0f, Fss90, Fi);
+            float f_ss = 1.25f * (Fss * (1.0f / (std::fabs(cos_theta_o) + std::fabs(cos_theta_i)) - 0.5f) + 0.5f);
+            lobe = dr_lerp(f_diff + f_retro, f_ss, P.flatness);
+        } else lobe = f_diff + f_retro;
+        for (int i = 0; i < 4; ++i) value[i] += brdf * std::fabs(cos_theta_o) * base_color[i] * kInvPi * lobe;
+        if (sheen_active) {
+            float Fd = schlick_weight(std::fabs(cos_theta_d));
+            if (P.has_sheen_tint) {
+                float lum = spectral_luminance(sc, base_color, si.wavelengths);
+                for (int i = 0; i < 4; ++i) {
+                    float c_tint = lum > 0.0f ? base_color[i] / lum : 1.0f;
+                    float c_sheen = dr_lerp(1.0f, c_tint, P.sheen_tint);
+                    value[i] += P.sheen * (1.0f - P.metallic) * Fd * c_sheen * std::fabs(cos_theta_o);
+                }
+            } else {
+                float add = P.sheen * (1.0f - P.metallic) * Fd * std::fabs(cos_theta_o);
+                for (int i = 0; i < 4; ++i) value[i] += add;
+            }
+        }
+    }
+    return value;
+}
+
+/* Principled::pdf (principled.cpp:714-834), spec_trans == 0 */
+float principled_pdf(const pltb_bsdf &b, const SI &si, V3 wo) {
+    const Principled P(b);
+    float cos_theta_i = si.wi.z;
+    if (!(cos_theta_i != 0.0f)) return 0.0f;
+    bool front_side = cos_theta_i > 0.0f;
+    float eta_path = front_side ? P.eta : rcp(P.eta), cos_theta_o = wo.z;
+    bool reflect = cos_theta_i * cos_theta_o > 0.0f;
+    V3 wh = normalize(si.wi + wo * (reflect ? 1.0f : eta_path));
+    wh = V3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
+    Microfacet spec_distr = P.spec_distr();
+    FresnelResult fr = fresnel(dot(si.wi, wh), P.eta);
+    float p_spec, p_cc, p_diff, p_trans;
+    P.probs(fr.r, p_spec, p_cc, p_diff, front_side, p_trans);
+    float dwh_dwo_abs = std::fabs(rcp(4.0f * dot(wo, wh)));
+    float pdf = 0.0f;
+    bool macmic = mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, true) && reflect;
+    V3 wi_s(mulsign(si.wi.x, cos_theta_i), mulsign(si.wi.y, cos_theta_i), mulsign(si.wi.z, cos_theta_i));
+    if (macmic) pdf += p_spec * spec_distr.pdf(wi_s, wh) * dwh_dwo_abs;
+    if (reflect) pdf += p_diff * (kInvPi * wo.z);
+    if (P.has_clearcoat) {
+        GTR1 cc{ dr_lerp(0.1f, 0.001f, P.clearcoat_gloss) };
+        if (macmic) pdf += p_cc * cc.pdf(wh) * dwh_dwo_abs;
+    }
+    return pdf;
+}
+
 /* `si` already has the twosided flip applied (wi.z = |wi.z|). */
 SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, float s1, V2 s2, V2 lobe_s2) {
     SampleOut o;
@@ -957,6 +1161,47 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
                 w = w * sqr(f.eta_ti);
             }
             o.weight = w;
+            return o;
+        }
+        case PLTB_BSDF_PRINCIPLED: { /* src/bsdfs/principled.cpp:330-486, spec_trans == 0 */
+            if (!(cos_theta_i != 0.0f)) return o;
+            const Principled P(b);
+            bool front_side = cos_theta_i > 0.0f;
+            Microfacet spec_distr = P.spec_distr();
+            V3 wi_s(mulsign(si.wi.x, cos_theta_i), mulsign(si.wi.y, cos_theta_i), mulsign(si.wi.z, cos_theta_i));
+            float mpdf; V3 m_spec = spec_distr.sample(wi_s, s2, mpdf);
+            FresnelResult fr = fresnel(dot(si.wi, m_spec), P.eta);
+            bool active = front_side;   /* (front_side || bsdf > 0) with bsdf == 0 */
+            float p_spec, p_cc, p_diff, p_trans;
+            P.probs(fr.r, p_spec, p_cc, p_diff, front_side, p_trans);
+            float curr = 0.0f;
+            bool sample_diffuse = active && s1 < p_diff;
+            curr += p_diff;
+            bool sample_clearcoat = P.has_clearcoat && active && s1 >= curr && s1 < curr + p_cc;
+            curr += p_cc;
+            curr += p_trans;   /* prob_spec_trans: 0 on this path (the loader rejects spec_trans != 0) */
+            bool sample_spec_reflect = active && s1 >= curr;
+            o.bs.eta = 1.0f;
+            if (sample_spec_reflect) {
+                V3 wo = reflect(si.wi, m_spec);
+                o.bs.wo = wo; o.bs.type = F_GlossyReflection;
+                active = active && mac_mic_compatibility(m_spec, si.wi, wo, cos_theta_i, true) && cos_theta_i * wo.z > 0.0f;
+            }
+            if (sample_clearcoat) {
+                GTR1 cc{ dr_lerp(0.1f, 0.001f, P.clearcoat_gloss) };
+                V3 m_cc = cc.sample(s2);
+                V3 wo = reflect(si.wi, m_cc);
+                o.bs.wo = wo; o.bs.type = F_GlossyReflection;
+                active = active && mac_mic_compatibility(m_cc, si.wi, wo, cos_theta_i, true) && cos_theta_i * wo.z > 0.0f;
+            }
+            if (sample_diffuse) {
+                V3 wo = square_to_cosine_hemisphere(s2);
+                o.bs.wo = wo; o.bs.type = F_DiffuseReflection;
+                active = active && cos_theta_i * wo.z > 0.0f;
+            }
+            o.bs.pdf = active ? principled_pdf(b, si, o.bs.wo) : 0.0f;
+            active = active && o.bs.pdf > 0.0f;
+            if (active) o.weight = principled_eval(sc, b, si, o.bs.wo) / o.bs.pdf;
             return o;
         }
         case PLTB_BSDF_ROUGHCONDUCTOR: { /* src/bsdfs/roughconductor.cpp:225-311 */
@@ -1035,6 +1280,7 @@ S4 bsdf_eval_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
             if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return S4(0.f);
             return (tex_eval(sc, b.tex[0], si.wavelengths, si.uv) * kInvPi) * cos_theta_o;
         }
+        case PLTB_BSDF_PRINCIPLED: return principled_eval(sc, b, si, wo);
         case PLTB_BSDF_ROUGHCONDUCTOR: { /* roughconductor.cpp:313-390 */
             if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return S4(0.f);
             V3 H = normalize(wo + si.wi);
@@ -1092,6 +1338,7 @@ float bsdf_pdf_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
     switch (b.type) {
         case PLTB_BSDF_DIFFUSE: return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? kInvPi * wo.z : 0.f;
+        case PLTB_BSDF_PRINCIPLED: return principled_pdf(b, si, wo);
         case PLTB_BSDF_ROUGHCONDUCTOR: { /* roughconductor.cpp:392-430 */
             V3 m = normalize(wo + si.wi);
             bool active = cos_theta_i > 0.f && cos_theta_o > 0.f && dot(si.wi, m) > 0.f && dot(wo, m) > 0.f;
@@ -1124,6 +1371,10 @@ S4 bsdf_weight_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
             if (selected_r) { if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], si.wavelengths, si.uv); }
             else { if (b.tex[3] >= 0) w = w * tex_eval(sc, b.tex[3], si.wavelengths, si.uv); }
             return w;
+        }
+        case PLTB_BSDF_PRINCIPLED: { /* base wbsdf_weight: eval / pdf (bsdf.cpp:85-97) */
+            float p = principled_pdf(b, si, wo);
+            return p > 0.0f ? principled_eval(sc, b, si, wo) / p : S4(0.f);
         }
         case PLTB_BSDF_ROUGHCONDUCTOR:
         case PLTB_BSDF_ROUGHGRATING: {
@@ -1764,5 +2015,20 @@ void plt_oracle_spectrum_to_srgb(const float *cie_srgb, const float *value, cons
     spectrum_to_srgb(cie_srgb, v, w, rgb);
 }
 float plt_oracle_srgb_model_eval(const float *c, float wl) { return srgb_model_eval(c, wl); }
+/* Principled::eval / ::pdf for a spatially uniform base colour (KAT against src/bsdfs/tests/test_principled.py:124-200);
+ * cie is the 4 x 95 table of pltb_scene_desc (its Y row defines luminance()). out = { eval[4], pdf } */
+void plt_oracle_principled_eval_pdf(const pltb_bsdf *b_in, float base_color, const float *cie, const float *wi, const float *wo,
+                                    const float *wl, float *out) {
+    pltb_texture t{}; t.type = PLTB_TEX_UNIFORM; t.p[0] = base_color;
+    pltb_bsdf b = *b_in; b.tex[0] = 0;
+    pltb_scene_desc d{}; d.textures = &t; d.n_textures = 1; d.cie_srgb = cie;
+    Scene sc; sc.d = &d;
+    SI si; si.wi = V3(wi[0], wi[1], wi[2]); si.uv = V2{ 0.f, 0.f };
+    for (int i = 0; i < 4; ++i) si.wavelengths[i] = wl[i];
+    V3 w(wo[0], wo[1], wo[2]);
+    S4 e = principled_eval(sc, b, si, w);
+    for (int i = 0; i < 4; ++i) out[i] = e[i];
+    out[4] = principled_pdf(b, si, w);
+}
 
 } // extern "C"

@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from parity import MAX_RMSE, MIN_FRACTION, relative_mse, sample_agreement
+from parity import MAX_RMSE, MIN_FRACTION, max_finiteness_mismatch, relative_mse, sample_agreement
 
 pytestmark = pytest.mark.gpu
 
@@ -13,6 +13,7 @@ CASES = [  # (scene, res, spp, seed)
     ("veach-mis", 64, 8, 1),                 # C4: rough conductors, sphere lights, tent filter
     ("spectrograph:bbody_3000", 1, 256, 0),  # C3: batch of 150 orthographic sensors with SRFs, directional blackbody light
     ("spectrograph:d65", 1, 64, 3),
+    ("gratingcap", 96, 8, 0),                # C5: principled screen + non-radial grating strip, directional light
 ]
 
 
@@ -29,7 +30,6 @@ def test_per_sample_radiance(mi, oracle, integ, name, res, spp, seed):
     img = integ.render(sc, spp=spp, seed=seed, dump=dump)
     ref = oracle.render(sc.flat, spp, seed=seed, dump=True)
     assert integ.last_stats["kernel_launches"] >= 4
-    np.testing.assert_array_equal(dump["wavelengths"], ref["wavelengths"]) if False else None
     wl_frac = sample_agreement(dump["wavelengths"], ref["wavelengths"])
     assert wl_frac == 1.0, f"sampled wavelengths differ: {wl_frac}"
     frac = sample_agreement(dump["radiance"], ref["radiance"])
@@ -39,7 +39,7 @@ def test_per_sample_radiance(mi, oracle, integ, name, res, spp, seed):
         a, b = integ.last_stats[k], ref["stats"][k]
         assert abs(a - b) <= max(4, 1e-3 * b), (k, a, b)
     rmse, mism = relative_mse(img, ref["image"])
-    assert rmse <= MAX_RMSE and mism <= 0.01, (rmse, mism)
+    assert rmse <= MAX_RMSE and mism <= max_finiteness_mismatch(img.shape[0] * img.shape[1]), (rmse, mism)
 
 
 def test_rr_and_depth_variants(mi, oracle):
@@ -73,6 +73,29 @@ def test_spp_window_union_is_bit_identical(mi, integ):
         parts.append(L.reshape(32 * 32, 4, 4))
     union = np.concatenate(parts, axis=1).reshape(-1, 4)
     np.testing.assert_array_equal(union.view(np.uint32), full["radiance"].view(np.uint32))
+
+
+def test_animation_frames(mi, oracle, integ):
+    """C5: camera animation of disk_animation.py:108-134 -- sensor to_world updated in place on the device copy
+    (pltb_scene_update_sensor), seed = frame index; each frame must match the oracle run on the updated host scene."""
+    from mitsuba3_plt_b200 import animation, scenes
+    sc = scenes.load("gratingcap", resx=64, resy=48)
+    sc.device()   # create the device copy first so that the in-place update path is what gets exercised
+    params = mi.traverse(sc)
+    key = next(iter(params))
+    initial = params[key]
+    for i in (0, 7, 23):
+        params[key] = animation.camera_to_world(initial, i, 24)
+        params.update()
+        dump = {}
+        img = integ.render(sc, spp=4, seed=i, dump=dump)
+        ref = oracle.render(sc.flat, 4, seed=i, dump=True)
+        assert sample_agreement(dump["wavelengths"], ref["wavelengths"]) == 1.0
+        frac = sample_agreement(dump["radiance"], ref["radiance"])
+        assert frac >= MIN_FRACTION, (i, frac)
+    frames = animation.render_frames(sc, integ, frames=24, spp=1, indices=[3, 4])
+    assert sorted(frames) == [3, 4] and frames[3].shape == (48, 64, 3)
+    assert not np.array_equal(frames[3], frames[4])
 
 
 def test_accumulate_and_raw_film(mi, oracle, integ):

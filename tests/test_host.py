@@ -38,6 +38,42 @@ def test_reference_scene_files_load(mi):
     assert s.film_size() == (500, 500) and s.flat.spp == 64 and s.flat.desc.n_faces == 2892
 
 
+def test_gratingcap_and_animation_path(mi, oracle):
+    """C5: builtin gratingcap scene (principled + roughgrating + directional), camera path of disk_animation.py:112-123 and
+    the frame deal across ranks; the principled loader's property rules (principled.cpp:189-231)."""
+    from mitsuba3_plt_b200 import animation, capi, scenes
+    sc = scenes.load("gratingcap", resx=40, resy=30)
+    d = sc.flat.desc
+    assert d.n_faces == 30 and d.n_shapes == 2 and d.n_emitters == 1
+    pr = [b for b in sc.flat.bsdfs if b.type == capi.BSDF_PRINCIPLED][0]
+    assert pr.u[0] == capi.PRINCIPLED_HAS["spec_tint"] | capi.PRINCIPLED_HAS["sheen_tint"]   # float 0 properties: no flag
+    assert abs(pr.f[0] - 1.5) < 1e-6 and abs(pr.f[1] - 0.25) < 1e-7 and pr.f[9] == 1.0     # specular 0.5 -> eta 1.5
+    if os.path.isdir(REF):   # same numbers from the reference's own files (XML + the two PLYs)
+        r = mi.load_file(f"{REF}/scenes/gratingcap/gratingcap.xml", resx=40, resy=30)
+        a = oracle.render(sc.flat, 4, seed=2, dump=True, film=False)
+        b = oracle.render(r.flat, 4, seed=2, dump=True, film=False)
+        from parity import sample_agreement   # procedural vertices differ from the file's in the last float32 bit
+        assert sample_agreement(a["radiance"], b["radiance"]) >= 0.9995
+    with pytest.raises(RuntimeError, match="either use"):
+        mi.load_dict({"type": "scene", "s": {"type": "rectangle", "bsdf": {"type": "principled", "eta": 1.3, "specular": 0.2}}})
+    # camera path
+    assert animation.easing(0, 240) == 0.0 and abs(animation.easing(120, 240) - 0.5) < 1e-7
+    init = mi.traverse(sc)["elm__1.to_world"]
+    np.testing.assert_allclose(animation.camera_to_world(init, 0, 240).matrix, init.matrix, atol=1e-12)
+    last = animation.camera_to_world(init, 239, 240).matrix
+    e = animation.easing(239, 240)
+    want = (mi.Transform().rotate([0, 1, 0], -90 * e).translate([-2.7 * e, 0, 2.1 * e]) @ init).matrix
+    np.testing.assert_allclose(last, want, atol=1e-12)
+    deal = [animation.frames_of_rank(240, r, 8) for r in range(8)]
+    assert sorted(sum(deal, [])) == list(range(240)) and all(len(x) == 30 for x in deal)
+    # in-place sensor update reaches the flattened scene the oracle (and the device copy) read
+    p = mi.traverse(sc)
+    p["elm__1.to_world"] = animation.camera_to_world(init, 60, 240)
+    p.update()
+    got = np.array(list(sc.flat.c_sensors[0].to_world), np.float32).reshape(4, 4)
+    np.testing.assert_allclose(got, animation.camera_to_world(init, 60, 240).matrix.astype(np.float32), rtol=0, atol=0)
+
+
 def test_plugin_parameters_and_errors(mi):
     it = mi.load_dict({"type": "plt"})
     assert (it.max_depth, it.rr_depth) == (16, 4)          # plt.py:37-38
