@@ -180,6 +180,9 @@ def run_ours(args):
                                         "kernel_launches")], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(cnt)
+        dist.barrier()
+        ctx.close()
+        dist.destroy_process_group()
     if rank != 0:
         return
     samples, closest, shadow, verts, gverts, launches = (int(x) for x in cnt.tolist())

@@ -93,9 +93,17 @@ def test_animation_frames(mi, oracle, integ):
         assert sample_agreement(dump["wavelengths"], ref["wavelengths"]) == 1.0
         frac = sample_agreement(dump["radiance"], ref["radiance"])
         assert frac >= MIN_FRACTION, (i, frac)
-    frames = animation.render_frames(sc, integ, frames=24, spp=1, indices=[3, 4])
-    assert sorted(frames) == [3, 4] and frames[3].shape == (48, 64, 3)
-    assert not np.array_equal(frames[3], frames[4])
+    params[key] = initial
+    params.update()
+    frames = animation.render_frames(sc, integ, frames=24, spp=8, indices=[2, 12])
+    assert sorted(frames) == [2, 12] and frames[2].shape == (48, 64, 3)
+    assert np.nanmax(frames[2]) > 0 and np.nanmax(frames[12]) > 0 and not np.array_equal(frames[2], frames[12])
+    # the loop restores the initial camera; frame 12 rendered by hand is the same image (up to the order of the film's atomics)
+    assert np.array_equal(mi.traverse(sc)[key].matrix, initial.matrix)
+    params[key] = animation.camera_to_world(initial, 12, 24)
+    params.update()
+    again = integ.render(sc, spp=8, seed=12)
+    np.testing.assert_allclose(again, frames[12], rtol=1e-4, atol=1e-6)
 
 
 def test_accumulate_and_raw_film(mi, oracle, integ):
