@@ -355,7 +355,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         PROF();
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
         PROF();
-        launches += 8;
+        launches += do_splat ? 9 : 8;   // raygen, 3 x nee_light, 3 x nee_post, gather (+ splat)
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0

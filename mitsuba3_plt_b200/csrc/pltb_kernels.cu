@@ -8,6 +8,7 @@
 // Path state lives in SoA arrays indexed depth-major (pltb_integrator.cuh) so warp accesses are coalesced float4s; queue
 // appends use warp-aggregated atomics (match_any + popc + one atomicAdd per group).
 #include <cuda_runtime.h>
+#include <cstdlib>
 
 #include "pltb_stages.cuh"
 #include "pltb_launch.h"
@@ -179,19 +180,151 @@ __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ Device
         stage_nee_eval(sc, st, st.queue_eval[e]);
 }
 
+// plt_solve_phase accumulation (plt.py:191-216), one thread per sample at full occupancy: the records of a path sit one DRAM
+// round trip apart (depth-major arrays), so the loads are issued four vertices at a time before the ordered sum consumes them.
+// The sum L is left in p_ray_o (dead after the last k_trace) for the splat kernels; optional per-sample dump.
+__global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassState st, const __grid_constant__ PassParams pp,
+                                                float *dump_wl, float *dump_L, uint64_t dump_cap) {
+    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= pp.count) return;
+    const uint32_t n = st.n_vertices[local];
+    S4 L = s4(0.f);
+    for (uint32_t base = 0; base < n; base += 4) {
+        float4 em[4], ne[4];
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j)
+            if (base + j < n) {
+                const size_t r = (size_t) (base + j) * st.chunk + local;
+                em[j] = st.v_em[r]; ne[j] = st.v_nee[r];
+            }
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j)
+            if (base + j < n) { L = L + f4_to_s4(em[j]); L = L + f4_to_s4(ne[j]); }
+    }
+    st.p_ray_o[local] = s4_to_f4(L);
+    if (dump_cap) {
+        uint32_t pix, s_rel;
+        split_work(pp, pp.first + local, pix, s_rel);
+        const uint64_t di = (uint64_t) pix * pp.spp_count + s_rel;   // dump order: pixel-major, then sample (include/pltb.h)
+        if (di < dump_cap) {
+            if (dump_L) reinterpret_cast<float4 *>(dump_L)[di] = s4_to_f4(L);
+            if (dump_wl) reinterpret_cast<float4 *>(dump_wl)[di] = st.wl[local];
+        }
+    }
+}
+
+// generic film splat (box filter, filters wider than 5x5): one thread per sample, one vector atomic per tap
 __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
-                                               const __grid_constant__ PassParams pp, float *accum, int do_splat,
-                                               float *dump_wl, float *dump_L, uint64_t dump_cap) {
+                                               const __grid_constant__ PassParams pp, float *accum) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= pp.count) return;
     DevFilm film{ accum };
-    S4 L = stage_splat(sc, st, pp, local, film, do_splat != 0);
-    uint32_t pix, s_rel;
-    split_work(pp, pp.first + local, pix, s_rel);
-    const uint64_t di = (uint64_t) pix * pp.spp_count + s_rel;   // dump order: pixel-major, then sample (include/pltb.h)
-    if (di < dump_cap) {
-        if (dump_L) reinterpret_cast<float4 *>(dump_L)[di] = s4_to_f4(L);
-        if (dump_wl) reinterpret_cast<float4 *>(dump_wl)[di] = st.wl[local];
+    float values[4];
+    splat_values(sc, st, local, f4_to_s4(st.p_ray_o[local]), values);
+    splat_taps(sc, pp, values, st.film_pos[local], film);
+}
+
+// Film splat through per-lane register tiles and per-warp shared-memory strips.  A warp owns 32 consecutive window pixels of
+// one row and up to kSplatS sample indices of the pass.  All samples of a lane belong to the same pixel, so their
+// (2 NR + 1)^2 filter taps land on the same footprint: they are summed in registers first (no memory traffic at all), the 32
+// footprints are then merged into the warp's (32 + 2 NR) x (2 NR + 1) strip in shared memory with plain read-modify-writes
+// -- at a fixed tap (ys, xs) the 32 lanes touch 32 distinct columns, so a __syncwarp() between taps is all the ordering that
+// is needed (no shared atomics, which are CAS loops for float) -- and the strip is flushed with one red.global.add.v4.f32 per
+// strip pixel: 180 instead of 6400 film atomics per 256 samples for the 5x5 Gaussian.  Lanes whose position does not floor
+// to their own pixel (x + u rounding up to x + 1 in float32), or whose pixel sits on another row than lane 0's (window width
+// not a multiple of 32), take the per-tap global path.
+constexpr int kSplatWarps = 4, kSplatS = 8;
+template <int NR>
+__global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_constant__ DeviceScene sc,
+                                                                  const __grid_constant__ PassState st,
+                                                                  const __grid_constant__ PassParams pp, float *accum,
+                                                                  uint32_t s_lo, uint32_t s_hi, uint32_t n_strips, uint32_t n_warps) {
+    constexpr int kTaps = 2 * NR + 1, kCols = 32 + 2 * NR, kPlane = kTaps * kCols;
+    __shared__ float4 smem[kSplatWarps * kPlane];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t gw = blockIdx.x * kSplatWarps + warp;
+    if (gw >= n_warps) return;                       // whole warps leave together; there is no block-level barrier below
+    const uint32_t strip = gw % n_strips, s_first = s_lo + (gw / n_strips) * kSplatS;
+    const uint32_t pix = strip * 32 + lane;
+    const bool valid_pix = pix < pp.n_pix;
+    const uint32_t row = pix / pp.crop_w;
+    const int x = (int) (pp.crop_x + (pix - row * pp.crop_w)), y = (int) (pp.crop_y + row);
+    const int x0 = __shfl_sync(0xffffffffu, x, 0), y0 = __shfl_sync(0xffffffffu, y, 0);
+    const bool same_row = valid_pix && y == y0;      // then x == x0 + lane
+    DevFilm film{ accum };
+    float4 acc[kTaps][kTaps];
+#pragma unroll
+    for (int ys = 0; ys < kTaps; ++ys)
+#pragma unroll
+        for (int xs = 0; xs < kTaps; ++xs) acc[ys][xs] = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool dirty = false;
+    // per-sample inputs are fetched one iteration ahead: the loop is a chain of dependent DRAM reads otherwise
+    struct Fetch { bool in; float4 L, wl, sw; float2 pos; };
+    auto fetch = [&](uint32_t k) {
+        Fetch f;
+        const uint64_t w = (uint64_t) (s_first + k) * pp.n_pix + pix;
+        f.in = k < (uint32_t) kSplatS && s_first + k <= s_hi && valid_pix && w >= pp.first && w < pp.first + pp.count;
+        if (f.in) {
+            const uint32_t local = (uint32_t) (w - pp.first);
+            f.L = st.p_ray_o[local]; f.wl = st.wl[local]; f.sw = st.sensor_w[local]; f.pos = st.film_pos[local];
+        }
+        return f;
+    };
+    Fetch nxt = fetch(0);
+#pragma unroll 1
+    for (uint32_t k = 0; k < (uint32_t) kSplatS && s_first + k <= s_hi; ++k) {
+        const Fetch cur = nxt;
+        nxt = fetch(k + 1);
+        if (!cur.in) continue;
+        float values[4];
+        splat_values(sc, f4_to_s4(cur.L), f4_to_s4(cur.wl), f4_to_s4(cur.sw), values);
+        const float2 pos = cur.pos;
+        if (!(same_row && (int) floorf(pos.x) == x && (int) floorf(pos.y) == y)) {
+            splat_taps(sc, pp, values, pos, film);
+            continue;
+        }
+        dirty = true;
+        float wx[kTaps], wy[kTaps];
+        float relx = ((float) (x - NR) + .5f) - pos.x, rely = ((float) (y - NR) + .5f) - pos.y;
+#pragma unroll
+        for (int t = 0; t < kTaps; ++t) {
+            wx[t] = rfilter_eval(sc.film, relx); wy[t] = rfilter_eval(sc.film, rely);
+            relx += 1; rely += 1;
+        }
+#pragma unroll
+        for (int ys = 0; ys < kTaps; ++ys)
+#pragma unroll
+            for (int xs = 0; xs < kTaps; ++xs) {
+                const float wgt = wy[ys] * wx[xs];
+                float4 &a = acc[ys][xs];
+                a.x += values[0] * wgt; a.y += values[1] * wgt; a.z += values[2] * wgt; a.w += values[3] * wgt;
+            }
+    }
+    if (!__any_sync(0xffffffffu, dirty)) return;
+    // merge the 32 register footprints into the warp's strip
+    float4 *tile = smem + warp * kPlane;
+    for (int i = lane; i < kPlane; i += 32) tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+#pragma unroll
+    for (int ys = 0; ys < kTaps; ++ys)
+#pragma unroll
+        for (int xs = 0; xs < kTaps; ++xs) {
+            if (dirty) {
+                float4 *t = tile + ys * kCols + lane + xs, v = *t;
+                const float4 a = acc[ys][xs];
+                v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+                *t = v;
+            }
+            __syncwarp();
+        }
+    const int W = (int) pp.film_w, H = (int) pp.film_h;
+    for (int i = lane; i < kPlane; i += 32) {
+        const int r = i / kCols, c = i - r * kCols;
+        const int xx = x0 - NR + c, yy = y0 - NR + r;
+        if (xx < 0 || yy < 0 || xx >= W || yy >= H) continue;
+        const float4 v = tile[i];
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)   // NaN != 0: poisoned taps reach the film as before
+            atomicAdd(reinterpret_cast<float4 *>(accum) + ((size_t) yy * W + xx), v);
     }
 }
 
@@ -227,7 +360,19 @@ void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int gr
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint64_t dump_cap, cudaStream_t s) {
-    k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum, do_splat, dump_wl, dump_L, dump_cap);
+    k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, (dump_wl || dump_L) ? dump_cap : 0);
+    if (!do_splat) return;
+    // separable filters with 3x3 (tent, r = 1) or 5x5 (gaussian, r = 2) taps go through the register tiles / shared strips
+    const int nr = sc.film.rfilter == PLTB_RFILTER_BOX ? 0 : (int) ceilf(sc.film.radius - .5f);
+    if ((nr == 1 || nr == 2) && !getenv("PLTB_SPLAT_DIRECT")) {
+        const uint32_t s_lo = (uint32_t) (pp.first / pp.n_pix), s_hi = (uint32_t) ((pp.first + pp.count - 1) / pp.n_pix);
+        const uint32_t n_strips = (pp.n_pix + 31) / 32, n_chunks = (s_hi - s_lo) / kSplatS + 1;
+        const uint32_t n_warps = n_strips * n_chunks, grid = (n_warps + kSplatWarps - 1) / kSplatWarps;
+        if (nr == 1) k_splat_strip<1><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
+        else k_splat_strip<2><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
+        return;
+    }
+    k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum);
 }
 void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, cudaStream_t s) {
     k_develop<<<(unsigned) ((n_pixels + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4 *>(accum), rgb, n_pixels);

@@ -306,29 +306,34 @@ PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t
     st.v_nee[r] = s4_to_f4((f4_to_s4(st.v_nee[r]) * bsdf_val) * f4_to_s4(st.v_alpha[r]));
 }
 
-// plt_solve_phase accumulation order (plt.py:191-216) + _splat_to_block (common.py:370-397); returns L
-template <class Film>
-PLTB_HD S4 stage_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Film &film, bool do_splat) {
+// plt_solve_phase accumulation order (plt.py:191-216): emissive and NEE terms of every recorded vertex, in depth order
+PLTB_HD S4 splat_gather(const PassState &st, uint32_t local, uint32_t n) {
     S4 L = s4(0.f);
-    const uint32_t n = st.n_vertices[local];
     for (uint32_t i = 0; i < n; ++i) {
         const size_t r = (size_t) i * st.chunk + local;
         L = L + f4_to_s4(st.v_em[r]);
         L = L + f4_to_s4(st.v_nee[r]);
     }
-    if (!do_splat) return L;
-    const S4 wl = f4_to_s4(st.wl[local]);
-    float values[4];
-    spectrum_to_srgb(sc.cie_srgb, L * f4_to_s4(st.sensor_w[local]), wl, values);
+    return L;
+}
+PLTB_HD S4 splat_gather(const PassState &st, uint32_t local) { return splat_gather(st, local, st.n_vertices[local]); }
+// _splat_to_block (common.py:370-397): sensor weight, spectrum -> sRGB, channels [R, G, B, W = 1]
+PLTB_HD void splat_values(const DeviceScene &sc, const S4 &L, const S4 &wl, const S4 &sensor_w, float values[4]) {
+    spectrum_to_srgb(sc.cie_srgb, L * sensor_w, wl, values);
     values[3] = 1.f;
-    const float2 pos = st.film_pos[local];
+}
+PLTB_HD void splat_values(const DeviceScene &sc, const PassState &st, uint32_t local, const S4 &L, float values[4]) {
+    splat_values(sc, L, f4_to_s4(st.wl[local]), f4_to_s4(st.sensor_w[local]), values);
+}
+// ImageBlock::put (src/render/imageblock.cpp:429-500), one atomic per tap straight into the film
+template <class Film>
+PLTB_HD void splat_taps(const DeviceScene &sc, const PassParams &pp, const float values[4], float2 pos, Film &film) {
     const int W = (int) pp.film_w, H = (int) pp.film_h;
     if (sc.film.rfilter == PLTB_RFILTER_BOX) {
         int px = (int) floorf(pos.x), py = (int) floorf(pos.y);
         if (px >= 0 && py >= 0 && px < W && py < H) film.add((size_t) py * W + px, values, 1.f);
-        return L;
+        return;
     }
-    // ImageBlock::put, coalesced path (src/render/imageblock.cpp:429-500)
     const int nr = (int) ceilf(sc.film.radius - .5f), count = 2 * nr + 1;
     const int px = (int) floorf(pos.x) - nr, py = (int) floorf(pos.y) - nr;
     float relx = ((float) px + .5f) - pos.x, rely = ((float) py + .5f) - pos.y;
@@ -346,6 +351,15 @@ PLTB_HD S4 stage_splat(const DeviceScene &sc, const PassState &st, const PassPar
             film.add((size_t) yy * W + xx, values, wy[ys] * wx[xs]);
         }
     }
+}
+// stage 3 for one sample; returns L
+template <class Film>
+PLTB_HD S4 stage_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Film &film, bool do_splat) {
+    S4 L = splat_gather(st, local);
+    if (!do_splat) return L;
+    float values[4];
+    splat_values(sc, st, local, L, values);
+    splat_taps(sc, pp, values, st.film_pos[local], film);
     return L;
 }
 
