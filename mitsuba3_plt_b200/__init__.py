@@ -25,13 +25,13 @@ import os
 
 import numpy as np
 
-from . import capi
+from . import capi, imageio
 from .scene import FlatScene, flatten
 from .xmlscene import Color, Properties, SpectrumValue, Transform, dict_to_tree, load_file_tree
 
 __all__ = ["set_variant", "variant", "load_file", "load_dict", "render", "traverse", "register_integrator",
            "PLTIntegrator", "Scene", "Properties", "ScalarTransform4f", "Transform4f", "Context", "context",
-           "init_distributed", "Bitmap", "is_spectral", "is_polarized"]
+           "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized"]
 
 ScalarTransform4f = Transform4f = Transform
 
@@ -383,11 +383,24 @@ def render(scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, s
 
 
 class Bitmap:
-    """Minimal mi.Bitmap: wraps an (H, W, C) float32 array; `write` supports .npy and 8-bit sRGB .png
-    (src/core/bitmap.cpp write paths for EXR are outside the hot path)."""
+    """Minimal mi.Bitmap: wraps an (H, W, C) float32 array, or reads one from an .exr / .png / .npy file; `write` supports
+    .exr (linear float32), .npy and 8-bit sRGB .png (src/core/bitmap.cpp; imageio.py)."""
 
     def __init__(self, array):
+        if isinstance(array, (str, os.PathLike)):
+            path = os.fspath(array)
+            ext = path.rsplit(".", 1)[-1].lower()
+            if ext == "exr":
+                array = imageio.read_exr(path)[0]
+            elif ext == "npy":
+                array = np.load(path)
+            else:
+                from PIL import Image
+                array = np.asarray(Image.open(path), dtype=np.float32) / 255.0
         self.array = np.asarray(array, dtype=np.float32)
+
+    def __array__(self, dtype=None, copy=None):
+        return self.array if dtype is None else self.array.astype(dtype)
 
     def convert(self, srgb_gamma=True):
         a = np.nan_to_num(self.array, nan=0.0, posinf=1.0, neginf=0.0).clip(0, 1)
@@ -396,8 +409,11 @@ class Bitmap:
         return (a * 255 + 0.5).astype(np.uint8)
 
     def write(self, path):
-        if path.endswith(".npy"):
-            np.save(path, self.array)
-            return
-        from PIL import Image
-        Image.fromarray(self.convert()).save(path)
+        imageio.write_bitmap(path, self.array)
+
+
+class util:
+    """mi.util: the two helpers the PLT scripts use (scripts/rendering/main-headless.py:60-73)."""
+    write_bitmap = staticmethod(lambda path, data, write_async=False: imageio.write_bitmap(
+        path, data.array if isinstance(data, Bitmap) else data, write_async))
+    convert_to_bitmap = staticmethod(lambda data, uint8_srgb=True: Bitmap(data))

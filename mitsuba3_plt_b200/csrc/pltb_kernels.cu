@@ -139,6 +139,8 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
     }
 }
 
+// (register budget: ptxas settles on 128 registers = 4 blocks/SM; forcing 3, 5, 6 or 8 blocks/SM measured 495 / 477 / 490 / 466 ms
+// against 462 ms for the whole sample phase, profiles/r01_ab_shade_occupancy.txt)
 template <int Class>
 __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {

@@ -121,6 +121,32 @@ def test_xml_defaults_refs_transforms(mi, tmp_path):
         mi.load_file(str(tmp_path / "bad.xml"))
 
 
+def test_image_files(mi, tmp_path):
+    """mi.util.write_bitmap / mi.Bitmap for .exr (FLOAT / HALF, NONE / ZIPS / ZIP), .png, .npy"""
+    from mitsuba3_plt_b200 import imageio
+    rng = np.random.default_rng(1)
+    img = (rng.random((19, 33, 3)) * 4).astype(np.float32)
+    img[3, 5] = [np.nan, np.inf, -1.0]
+    for comp in ("none", "zips", "zip"):
+        p = str(tmp_path / f"a_{comp}.exr")
+        imageio.write_exr(p, img, compression=comp)
+        back, names = imageio.read_exr(p)
+        assert names == ["R", "G", "B"]
+        np.testing.assert_array_equal(back.view(np.uint32), img.view(np.uint32))
+    imageio.write_exr(str(tmp_path / "h.exr"), img[..., :1], half=True, compression="zip")
+    back, names = imageio.read_exr(str(tmp_path / "h.exr"))
+    assert names == ["Y"] and np.allclose(back[0, :, 0], img[0, :, 0].astype(np.float16).astype(np.float32))
+    mi.util.write_bitmap(str(tmp_path / "r.exr"), img)
+    np.testing.assert_array_equal(np.asarray(mi.Bitmap(str(tmp_path / "r.exr")))[0], img[0])
+    mi.util.write_bitmap(str(tmp_path / "r.png"), mi.Bitmap(img))
+    png = np.asarray(mi.Bitmap(str(tmp_path / "r.png")))
+    assert png.shape == (19, 33, 3) and png.max() == 1.0 and png[3, 5, 0] == 0.0   # NaN -> 0, clamp, sRGB curve
+    with pytest.raises(RuntimeError, match="not an OpenEXR"):
+        imageio.read_exr(str(tmp_path / "r.png"))
+    with pytest.raises(RuntimeError, match="unsupported file extension"):
+        mi.util.write_bitmap(str(tmp_path / "r.tiff"), img)
+
+
 def test_ply_round_trip(tmp_path):
     from mitsuba3_plt_b200 import scenes
     from mitsuba3_plt_b200.scene import load_ply
