@@ -228,7 +228,7 @@ def run_ours(args):
         out["cpu_baseline"] = {"value": round(c["samples"] / c["seconds"] / 1e6, 4), "unit": "Msamples/s",
                                "cores": c["cores"], "kind": "port", "sample": c["sample"],
                                "mrays_per_s": round(c["rays"] / c["seconds"] / 1e6, 4)}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def run_reference(args):
@@ -255,11 +255,26 @@ def run_reference(args):
            "cpu_baseline": {"value": round(v, 4), "unit": "Msamples/s", "cores": last["cores"], "kind": "port",
                             "sample": last["sample"]},
            "e2e": {"value": round(v, 4), "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
+
+
+def claim_stdout():
+    """Only the JSON line may reach stdout: native libraries (NCCL prints its version banner from C) write to fd 1 directly, so
+    fd 1 is pointed at stderr for the whole run and the real stdout is kept aside for emit()."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
 
 
 if __name__ == "__main__":
     a = parse()
+    claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

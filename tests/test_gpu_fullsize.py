@@ -1,0 +1,84 @@
+"""GPU tests at BASELINE.json's full sizes.  The oracle cannot finish these in seconds, so they check (a) per-sample parity on a
+crop of the full-size frame at the full sample count ("64x64 crop x 1024 spp") and (b) size-independent
+properties: linearity of the film over sample-index windows, partition of unity of the reconstruction filter (the W channel),
+sample / pass / sub-render accounting."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from parity import MIN_FRACTION, sample_agreement
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def integ(mi):
+    return mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
+
+
+def test_c2_crop_at_full_sample_count(mi, oracle, integ):
+    """cbox-grating 1024x1024 x 1024 spp, 16x16 crop on the grating sphere (2.6e5 samples, 1.1 grating vertices each): every
+    sample's lane index, RNG stream and radiance must be those of the full frame (idx = pixel * spp + s with the *film* width), against the oracle on the same crop."""
+    from mitsuba3_plt_b200 import scenes
+    sc = scenes.load("cbox-grating", resx=1024, resy=1024)
+    crop = (316, 656, 16, 16)
+    dump = {}
+    integ.render(sc, spp=1024, seed=0, dump=dump, crop=crop)
+    assert integ.last_stats["samples"] == 16 * 16 * 1024
+    ref = oracle.render(sc.flat, 1024, seed=0, dump=True, crop=crop, film=False)
+    assert sample_agreement(dump["wavelengths"], ref["wavelengths"]) == 1.0
+    frac = sample_agreement(dump["radiance"], ref["radiance"])
+    assert frac >= MIN_FRACTION, frac
+    assert ref["stats"]["grating_vertices"] > 0.2 * ref["stats"]["samples"]   # the crop really is on the grating
+    for k in ("closest_rays", "shadow_rays", "vertices", "grating_vertices"):
+        a, b = integ.last_stats[k], ref["stats"][k]
+        assert abs(a - b) <= max(4, 1e-3 * b), (k, a, b)
+
+
+def test_c2_full_frame_linearity_and_accounting(mi, integ):
+    """1024x1024 x 32 spp (4 passes of 2^23 samples): film([0,32)) == film([0,12)) + film([12,32)) up to the order of the float
+    atomics; Gaussian W channel identical in both; counters add up."""
+    from mitsuba3_plt_b200 import capi, scenes
+    sc = scenes.load("cbox-grating", resx=1024, resy=1024)
+    ctx = mi.context()
+    L = capi.lib()
+
+    def window(lo, n, flags=0):
+        prm = capi.RenderParams(seed=5, spp=32, spp_begin=lo, spp_count=n, max_depth=7, rr_depth=50, flags=flags)
+        out = np.empty((1024, 1024, 4), np.float32)
+        st = capi.Stats()
+        capi.check(L.pltb_render(ctx._h, sc.device(ctx), C.byref(prm), out.ctypes.data, None, C.byref(st)))
+        return out, st.as_dict()
+
+    full, st = window(0, 32)
+    assert st["samples"] == 1024 * 1024 * 32 and st["passes"] == 4 and st["closest_rays"] >= st["samples"]
+    a, sa = window(0, 12)
+    b, sb = window(12, 20)
+    for k in ("samples", "closest_rays", "shadow_rays", "vertices", "grating_vertices"):
+        assert sa[k] + sb[k] == st[k], k
+    both, _ = window(12, 20, capi.RENDER_ACCUMULATE)        # accumulates onto the film left by the previous call (b)
+    np.testing.assert_allclose(both[..., 3], 2 * b[..., 3], rtol=1e-5)
+    fin = np.isfinite(full).all(-1) & np.isfinite(a).all(-1) & np.isfinite(b).all(-1)
+    assert fin.mean() > 0.9    # ~45 NaN samples per 1e6 (invalid-lobe quirk), each poisoning its 5x5 footprint
+    np.testing.assert_allclose((a + b)[fin], full[fin], rtol=2e-4, atol=1e-4)
+    # the truncated Gaussian (stddev 0.5, radius 2) is not a partition of unity, but its weight sum per sample is the same
+    # everywhere away from the border: W / spp is flat
+    w = full[8:-8, 8:-8, 3] / 32
+    assert abs(w.mean() - w[::7, ::5].mean()) < 1e-3 and 0.9 < w.mean() < 1.7
+
+
+def test_c4_full_size_two_subrenders(mi, integ):
+    """veach-mis 1920x1080 x 4096 spp = 8.49e9 samples > 2^32: two sub-renders with seeds (0, 1) whose accumulators are summed
+    (SURVEY.md 8b).  The tent filter (radius 1) is a partition of unity, so W == spp on interior pixels."""
+    from mitsuba3_plt_b200 import scenes, split_subrenders
+    sc = scenes.load("veach-mis", resx=1920, resy=1080)
+    assert split_subrenders(1920, 1080, 4096) == (2, 2048)
+    raw = integ.render(sc, spp=4096, seed=0, develop=False)
+    st = integ.last_stats
+    assert st["samples"] == 1920 * 1080 * 4096
+    assert raw.shape == (1080, 1920, 4) and np.isfinite(raw).all()
+    w = raw[2:-2, 2:-2, 3]
+    assert abs(w.mean() / 4096 - 1) < 1e-3 and abs(w.min() / 4096 - 1) < 0.1
+    img = raw[..., :3] / raw[..., 3:]
+    assert 0.01 < img.mean() < 10 and img.max() > 1.0       # the three lights are in view
