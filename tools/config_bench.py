@@ -1,0 +1,77 @@
+#!/usr/bin/env python
+"""Times every BASELINE.json config at its full size on one GPU (device time from pltb_stats, scene load / BVH build excluded)
+next to the CPU oracle on a bounded sample of the same workload (all host cores).  One JSON line per config.
+usage: python tools/config_bench.py [--cpu-seconds 6] [--only C2,C4]"""
+import argparse, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import mitsuba3_plt_b200 as mi
+from mitsuba3_plt_b200 import animation, scenes
+import oracle_lib
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--cpu-seconds", type=float, default=6.0)
+ap.add_argument("--only", default="")
+args = ap.parse_args()
+
+CONFIGS = [  # id, builtin scene, resx, resy, spp, note
+    ("C1", "cbox", 256, 256, 16, "scenes/cbox, 256x256, 16 spp"),
+    ("C2", "cbox-grating", 1024, 1024, 1024, "scenes/cbox-grating 1024x1024, 1024 spp"),
+    ("C3", "spectrograph:bbody_3000", 1, 1, 1 << 20, "spectrograph, 150 sensors x 2^20 spp (largest row of synthetic-times.csv)"),
+    ("C3p", "spectrograph:bbody_3000", 1, 1, 10_000_000, "spectrograph prior pass, 150 sensors x 1e7 spp"),
+    ("C4", "veach-mis", 1920, 1080, 4096, "scenes/veach-mis 1920x1080, 4096 spp (2 sub-renders)"),
+]
+it = mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
+only = set(filter(None, args.only.split(",")))
+
+
+def oracle_rate(sc, spp, W, H):
+    probe = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=1, film=False) if W * H > 4096 else \
+        oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=min(spp, 256), film=False)
+    rate = probe["stats"]["samples"] / max(probe["seconds"], 1e-9)
+    n = int(max(1, min(spp, args.cpu_seconds * rate / (W * H))))
+    r = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=n)
+    st = r["stats"]
+    return st["samples"] / r["seconds"] / 1e6, (st["closest_rays"] + st["shadow_rays"]) / r["seconds"] / 1e6, n
+
+
+for cid, name, rx, ry, spp, note in CONFIGS:
+    if only and cid not in only:
+        continue
+    sc = scenes.load(name, resx=rx, resy=ry)
+    W, H = sc.film_size()
+    warm = min(spp, max(1, (1 << 24) // (W * H)))
+    it.render(sc, spp=warm, seed=0, download=False)
+    t0 = time.perf_counter()
+    img = it.render(sc, spp=spp, seed=0)
+    wall = time.perf_counter() - t0
+    st = it.last_stats
+    ms = st["ms_total"]
+    cpu_ms, cpu_mr, n = oracle_rate(sc, spp, W, H)
+    print(json.dumps({"config": cid, "workload": note, "film": [W, H], "spp": spp, "samples": st["samples"],
+                      "gpu_ms": round(ms, 3), "gpu_wall_ms": round(wall * 1e3, 3),
+                      "gpu_msamples_per_s": round(st["samples"] / ms / 1e3, 2),
+                      "gpu_mrays_per_s": round((st["closest_rays"] + st["shadow_rays"]) / ms / 1e3, 2),
+                      "rays_per_sample": round((st["closest_rays"] + st["shadow_rays"]) / st["samples"], 3),
+                      "grating_vertices_per_sample": round(st["grating_vertices"] / st["samples"], 4),
+                      "passes": st["passes"], "launches": st["kernel_launches"],
+                      "image_mean": float(np.nanmean(img)), "nan_pixels": int(np.isnan(img).any(-1).sum()),
+                      "cpu_oracle_msamples_per_s": round(cpu_ms, 4), "cpu_oracle_mrays_per_s": round(cpu_mr, 4),
+                      "cpu_cores": os.cpu_count(), "cpu_sample": f"spp indices [0,{n}) of {spp}, full frame"}), flush=True)
+
+if not only or "C5" in only:
+    sc = scenes.load("gratingcap", resx=800, resy=600)
+    animation.render_frames(sc, it, frames=240, spp=1, indices=list(range(8)))
+    dev = []
+    t0 = time.perf_counter()
+    animation.render_frames(sc, it, frames=240, spp=1, on_frame=lambda i, img: dev.append(it.last_stats["ms_total"]))
+    wall = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    for i in range(4):
+        oracle_lib.render(sc.flat, 1, seed=i)
+    cpu = (time.perf_counter() - t1) / 4
+    print(json.dumps({"config": "C5", "workload": "scenes/gratingcap 800x600, 1 spp per frame x 240 frames, camera path of "
+                      "disk_animation.py", "frames_per_s": round(240 / wall, 1), "ms_per_frame_wall": round(1e3 * wall / 240, 3),
+                      "ms_per_frame_device": round(float(np.mean(dev)), 3), "gpu_msamples_per_s": round(480000 * 240 / wall / 1e6, 2),
+                      "cpu_oracle_ms_per_frame": round(cpu * 1e3, 2), "cpu_cores": os.cpu_count()}), flush=True)
