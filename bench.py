@@ -98,19 +98,28 @@ def cpu_oracle_run(args, scene, seconds, threads=0):
             "cores": threads or os.cpu_count()}
 
 
-def algorithmic_bytes(st, kernel):
-    """Algorithmic bytes moved by one kernel over the counted work (DESIGN.md "Kernels": per-unit figures).
-    k_sample : per sample 60 B of per-sample state out; per bounce record 16 B (emissive term) + 16 B (zeroed NEE slot)
-               or, for an NEE-eligible vertex, 88 B of vertex record + 4 B queue entry
-    k_nee    : per queued vertex 4 + 88 + 32 B in (entry, record, wavelengths + RNG state), 16 B out
-    k_splat  : per sample 44 B in + 32 B per bounce record in + 25 taps x 16 B x 2 (RMW) of film atomics"""
-    S, R = st["samples"], st["closest_rays"]
-    Q = st["nee_other"] + st["nee_grating"]
-    if kernel == "k_sample":
-        return 60 * S + 16 * R + 16 * (R - Q) + 92 * Q
-    if kernel == "k_nee":
-        return 140 * Q
-    return 44 * S + 32 * R + 800 * S
+def algorithmic_bytes(st):
+    """Algorithmic bytes per kernel over the counted work of one step (DESIGN.md "Rooflines": per-unit figures x counted units).
+    S samples, R closest-hit rays (R - S of them secondary), V recorded vertices (Vg on a grating), Q NEE items, Sh shadow rays.
+      k_raygen            per sample: 16 B wavelengths + 16 B sensor weight + 8 B film position + 16 B RNG state + 4 B record count,
+                          32 B ray, 16 B hit + 4 B queue entry                                                   = 112 B
+      k_shade<c>          per vertex: in 4 B entry + 16 B hit + 32 B ray + 16 B RNG + 16 B throughput + 20 B prev; out 16 B weight +
+                          16 B replayed throughput + 16 B emissive + 16 B zeroed NEE slot + 88 B NEE record + 4 B NEE entry +
+                          32 B next ray + 16 B RNG + 36 B path state + 4 B live entry                                = 364 B
+      k_trace             per secondary ray: 4 B entry + 32 B ray in, 16 B hit out                                  = 52 B
+      k_classify          per secondary ray: 4 B entry + 16 B hit in, 4 B queue entry out                           = 24 B
+      k_nee_light         per NEE item: 4 B entry + 88 B record + 16 B wavelengths + 16 B RNG in; 48 B light sample + 4 B out = 176 B
+      k_trace<shadow>     per shadow ray: 4 B entry + 32 B ray in, 4 B visibility out                               = 40 B
+      k_nee_post<c>       per NEE item: 4 B entry + 88 B record + 48 B light sample + 16 B wavelengths + 16 B throughput in, 16 B out = 188 B
+      k_nee_eval          per evaluated item: 4 B entry + 88 B record + 48 B + 16 B in, 16 B out                    = 172 B
+      k_gather            per sample 4 B + 16 B out (+ 16 B dump); per vertex 32 B                                  = 20 B + 32 B/vertex
+      k_splat             per sample 16 B L + 16 B + 16 B + 8 B in; film RMW 2 x 16 B x 180 strip pixels per 256 samples = 78.5 B"""
+    S, R, V, Vg = st["samples"], st["closest_rays"], st["vertices"], st["grating_vertices"]
+    Q0, Q1, Sh, E = st["nee_other"], st["nee_grating"], st["shadow_rays"], st["nee_grating_eval"]
+    return {"k_raygen": 112 * S, "k_shade<grating>": 364 * Vg, "k_shade<other>": 364 * (V - Vg), "k_trace": 52 * (R - S),
+            "k_classify": 24 * (R - S), "k_nee_light": 176 * (Q0 + Q1), "k_trace<shadow>": 40 * Sh,
+            "k_nee_post<other>": 188 * Q0, "k_nee_post<grating>": 188 * Q1, "k_nee_eval": 172 * E,
+            "k_gather": 20 * S + 32 * V, "k_splat": 78.5 * S}
 
 
 def run_ours(args):
@@ -190,12 +199,18 @@ def run_ours(args):
     value = samples / (ms_step * 1e-3) / 1e6
     e2e_ms = e_wall_ms / args.steps
     kern = {"k_sample": pst["ms_sample"], "k_nee": pst["ms_nee_grating"] + pst["ms_nee_other"], "k_splat": pst["ms_splat"]}
-    top = max(kern, key=kern.get)
-    n_pass = max(1, pst["passes"])
-    n_launch = n_pass * (2 if top == "k_nee" else 1)
+    per_kernel = {k: v for k, v in pst["kernels"].items() if v["launches"]}
+    top = max(per_kernel, key=lambda k: per_kernel[k]["ms"])          # the dominant CUDA kernel of the step
+    top_ms, n_launch = per_kernel[top]["ms"], per_kernel[top]["launches"]
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     peak = peaks.get("hbm_gbs", 6650.0)
-    ach = algorithmic_bytes(pst, top) / (kern[top] * 1e-3) / 1e9
+    alg = algorithmic_bytes(pst)
+    ach = alg[top] / (top_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")   # dram bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tpath):
+        t = json.load(open(tpath)).get(top)
+        traffic = t["dram_bytes_per_launch"] if t else None
     out = {
         "metric": METRIC, "value": round(value, 3), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "strong",
@@ -216,12 +231,16 @@ def run_ours(args):
                 "note": "wall clock around PLTIntegrator.render incl. sensor upload and image download to pinned host memory"},
         "kernel_ms_per_step": {k: round(v, 3) for k, v in kern.items()} | {
             "reduce": round(pst["ms_reduce"], 3), "develop": round(pst["ms_develop"], 3), "copy": round(pst["ms_copy"], 3)},
+        "kernels": {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
+                        "algorithmic_GB_per_s": round(alg[k] / max(v["ms"], 1e-6) / 1e6, 1)} for k, v in per_kernel.items()},
         "roofline": {"kernel": top, "bound": "hbm", "achieved": round(ach, 2), "peak": peak, "unit": "GB/s",
-                     "frac": round(ach / peak, 4), "traffic": None, "launches_per_step": n_launch,
-                     "avg_launch_ms": round(kern[top] / n_launch, 4),
+                     "frac": round(ach / peak, 4), "traffic": traffic, "launches_per_step": n_launch,
+                     "avg_launch_ms": round(top_ms / n_launch, 4), "algorithmic_bytes_per_launch": round(alg[top] / n_launch),
+                     "share_of_step": round(top_ms / sum(v["ms"] for v in per_kernel.values()), 4),
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (sustained copy)" if peaks else "fallback 6650 GB/s",
-                     "note": "the path is SM-issue (FP32+MUFU) bound, not HBM bound (SURVEY.md 8d); see profiles/ for "
-                             "the ncu issue-slot figures"},
+                     "note": "the path is SM-issue (FP32+MUFU) bound, not HBM bound (SURVEY.md 8d): profiles/ holds issue-slot "
+                             "utilisation, active lanes and stall mix per kernel from ncu; kernel times here come from CUDA "
+                             "events after every launch in a separate profiled step"},
     }
     if not args.no_cpu_baseline:
         c = cpu_oracle_run(args, scene, args.cpu_seconds)

@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define PLTB_ABI_VERSION 2
+#define PLTB_ABI_VERSION 3
 #define PLTB_MAX_DEPTH 16      /* upper bound on the `max_depth` plugin parameter (plt.py:37) */
 #define PLTB_MAX_LOBES 9       /* diffractionGratingsMaxLobes (include/mitsuba/plt/diffractiongrating.h:24) */
 
@@ -222,6 +222,11 @@ typedef struct pltb_sample_dump {
     uint64_t capacity;    /* number of samples the arrays can hold */
 } pltb_sample_dump;
 
+/* kernels of one wavefront pass, in launch order (csrc/pltb_kernels.cu) */
+enum { PLTB_K_RAYGEN = 0, PLTB_K_SHADE_GRATING, PLTB_K_SHADE_OTHER, PLTB_K_TRACE, PLTB_K_CLASSIFY, PLTB_K_NEE_LIGHT,
+       PLTB_K_TRACE_SHADOW, PLTB_K_NEE_POST_OTHER, PLTB_K_NEE_POST_GRATING, PLTB_K_NEE_EVAL, PLTB_K_GATHER, PLTB_K_SPLAT,
+       PLTB_K_COUNT };
+
 typedef struct pltb_stats {
     uint64_t samples;
     uint64_t closest_rays;
@@ -235,6 +240,9 @@ typedef struct pltb_stats {
     float ms_total;             /* device time of the whole call (CUDA events) */
     /* per-kernel device time, summed over passes; filled only with PLTB_RENDER_PROFILE */
     float ms_sample, ms_nee_grating, ms_nee_other, ms_splat, ms_develop, ms_reduce, ms_copy;
+    /* per CUDA kernel (PLTB_K_*): device time summed over its launches and the number of launches; PLTB_RENDER_PROFILE only */
+    float ms_kernel[16];
+    uint32_t launches_kernel[16];
 } pltb_stats;
 
 typedef struct pltb_context pltb_context;

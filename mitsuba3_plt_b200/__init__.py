@@ -323,7 +323,11 @@ class PLTIntegrator:
                 dst = out.ctypes.data if (last and out is not None and download) else None
                 capi.check(L.pltb_render(ctx._h, dev, C.byref(prm), dst, C.byref(dmp) if dmp else None, C.byref(st)))
                 for f, _ in capi.Stats._fields_:
-                    setattr(total, f, getattr(total, f) + getattr(st, f))
+                    if f in ("ms_kernel", "launches_kernel"):
+                        for j in range(16):
+                            getattr(total, f)[j] += getattr(st, f)[j]
+                    else:
+                        setattr(total, f, getattr(total, f) + getattr(st, f))
         finally:
             self._cancel_ctx = None
         self.last_stats = total.as_dict()

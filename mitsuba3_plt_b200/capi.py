@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libpltb200.so")
 if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu_ab.sh)
     LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
-PLTB_ABI_VERSION = 2
+PLTB_ABI_VERSION = 3
 PLTB_MAX_DEPTH = 16
 
 # enums (include/pltb.h)
@@ -77,6 +77,10 @@ class RenderParams(C.Structure):
                 ("rr_depth", u32), ("flags", u32), ("crop_x", u32), ("crop_y", u32), ("crop_w", u32), ("crop_h", u32)]
 
 
+KERNEL_NAMES = ["k_raygen", "k_shade<grating>", "k_shade<other>", "k_trace", "k_classify", "k_nee_light", "k_trace<shadow>",
+                "k_nee_post<other>", "k_nee_post<grating>", "k_nee_eval", "k_gather", "k_splat"]   # PLTB_K_* (include/pltb.h)
+
+
 class SampleDump(C.Structure):
     _fields_ = [("wavelengths", PF), ("radiance", PF), ("n_rays", PU), ("capacity", u64)]
 
@@ -85,10 +89,13 @@ class Stats(C.Structure):
     _fields_ = [("samples", u64), ("closest_rays", u64), ("shadow_rays", u64), ("kernel_launches", u64),
                 ("vertices", u64), ("grating_vertices", u64), ("nee_other", u64), ("nee_grating", u64), ("passes", u64), ("nee_grating_eval", u64),
                 ("ms_total", f32), ("ms_sample", f32), ("ms_nee_grating", f32),
-                ("ms_nee_other", f32), ("ms_splat", f32), ("ms_develop", f32), ("ms_reduce", f32), ("ms_copy", f32)]
+                ("ms_nee_other", f32), ("ms_splat", f32), ("ms_develop", f32), ("ms_reduce", f32), ("ms_copy", f32),
+                ("ms_kernel", f32 * 16), ("launches_kernel", u32 * 16)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("ms_kernel", "launches_kernel")}
+        d["kernels"] = {n: {"ms": self.ms_kernel[i], "launches": self.launches_kernel[i]} for i, n in enumerate(KERNEL_NAMES)}
+        return d
 
 
 EXPORTS = ["pltb_nccl_unique_id", "pltb_context_create", "pltb_context_destroy", "pltb_scene_create", "pltb_scene_update_sensor",

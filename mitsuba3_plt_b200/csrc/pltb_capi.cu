@@ -69,6 +69,9 @@ struct pltb_context {
     int sm_count = 148;
     cudaEvent_t ev[2] = { nullptr, nullptr };
     std::vector<cudaEvent_t> prof;   // PLTB_RENDER_PROFILE: 5 events per pass + 4 for the tail
+    std::vector<cudaEvent_t> kprof;  // PLTB_RENDER_PROFILE: one event after every kernel launch (+ one at the start of a pass)
+    std::vector<int> kprof_id;       // kernel id (PLTB_K_*) that ended at kprof[i]; -1 = start marker
+    size_t kprof_n = 0;
 };
 
 struct pltb_scene {
@@ -142,6 +145,7 @@ void pltb_context_destroy(pltb_context *c) {
     cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
     cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
     for (cudaEvent_t e : c->prof) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->kprof) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -322,6 +326,18 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (profile) {
         while (c->prof.size() < 5 * n_pass + 4) { cudaEvent_t e; CU(cudaEventCreate(&e)); c->prof.push_back(e); }
     }
+    // per-kernel events: the launchers call back after every kernel (pltb_launch.h)
+    struct KHook {
+        static void mark(int kernel, void *user) {
+            pltb_context *c = (pltb_context *) user;
+            if (c->kprof_n == c->kprof.size()) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return; c->kprof.push_back(e); }
+            cudaEventRecord(c->kprof[c->kprof_n++], c->stream);
+            c->kprof_id.push_back(kernel);
+        }
+    };
+    c->kprof_n = 0; c->kprof_id.clear();
+    g_launch_hook = profile ? LaunchHook{ &KHook::mark, c } : LaunchHook{};
+    struct HookReset { ~HookReset() { g_launch_hook = LaunchHook{}; } } hook_reset;
     size_t pe = 0;
 #define PROF() do { if (profile) CU(cudaEventRecord(c->prof[pe++], s)); } while (0)
     CU(cudaEventRecord(c->ev[0], s));
@@ -339,6 +355,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         pp.count = (uint32_t) std::min<uint64_t>(st.chunk, total - first);
         CU(cudaMemsetAsync(st.counts, 0, kCountsTotal * sizeof(uint32_t), s));
         PROF();
+        if (profile) KHook::mark(-1, c);
         // sample phase as dense per-bounce wavefronts: raygen + trace(0), then shade(i) / trace(i + 1)
         launch_raygen(scene->dev, st, pp, s);
         for (uint32_t b = 0; b < prm->max_depth; ++b) {
@@ -411,6 +428,12 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
                 CU(cudaEventElapsedTime(&ms, e[1], e[2])); stats->ms_nee_other += ms;     // light + shadow rays + post<0>
                 CU(cudaEventElapsedTime(&ms, e[2], e[3])); stats->ms_nee_grating += ms;   // post<1> + eval
                 CU(cudaEventElapsedTime(&ms, e[3], e[4])); stats->ms_splat += ms;
+            }
+            for (size_t i = 1; i < c->kprof_n; ++i) {
+                const int k = c->kprof_id[i];
+                if (k < 0 || k >= PLTB_K_COUNT) continue;
+                CU(cudaEventElapsedTime(&ms, c->kprof[i - 1], c->kprof[i]));
+                stats->ms_kernel[k] += ms; stats->launches_kernel[k]++;
             }
             cudaEvent_t *t = &c->prof[5 * n_pass];
             CU(cudaEventElapsedTime(&stats->ms_reduce, t[0], t[1]));

@@ -62,6 +62,10 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
 // two thirds of the lanes idle.  Persistent warps instead: every lane owns a resumable Traversal; whenever lanes finish, the
 // warp reserves new rays for them with one atomicAdd on the bounce's cursor, then all lanes advance by a bounded number of
 // inner-node steps followed by one leaf step (while-while order).
+// (Measured and rejected: feeding the lanes through a three-stage prefetch pipeline -- warp-private pools of list positions,
+// entry and ray loads issued one round ahead -- made this kernel 1.5x slower (0.89 -> 1.37 ms per pass) at equal results: the
+// DRAM round trip of a refill is already covered by the other 20+ resident warps, while the extra per-round bookkeeping and
+// the loss of globally consecutive ray batches are not.)
 // Shadow = true: the same loop over the NEE shadow-ray list (any-hit; an occluded vertex gets ds.pdf = 0 in its record).
 template <bool Shadow>
 __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
@@ -339,30 +343,36 @@ __global__ void k_develop(const float4 *accum, float *rgb, uint64_t n_pixels) {
     rgb[3 * i] = a.x / d; rgb[3 * i + 1] = a.y / d; rgb[3 * i + 2] = a.z / d;
 }
 
+thread_local LaunchHook g_launch_hook;
+#define PLTB_AFTER(k) do { if (g_launch_hook.fn) g_launch_hook.fn((k), g_launch_hook.user); } while (0)
+
 void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s) {
-    k_raygen<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp);
+    k_raygen<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp); PLTB_AFTER(PLTB_K_RAYGEN);
 }
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
-    k_trace<false><<<grid, 128, 0, s>>>(sc, st, bounce);
-    k_classify<<<grid, 256, 0, s>>>(sc, st, bounce);
+    k_trace<false><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_TRACE);
+    k_classify<<<grid, 256, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_CLASSIFY);
 }
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
-    if (cls) k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce);
-    else k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce);
+    if (cls) { k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_GRATING); }
+    else { k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_OTHER); }
 }
 // emitter sampling for both queues, then all shadow rays in one persistent-warp launch
 void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s) {
-    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 1);
-    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 0);
-    k_trace<true><<<grid, 128, 0, s>>>(sc, st, 0);
+    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 1); PLTB_AFTER(PLTB_K_NEE_LIGHT);
+    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 0); PLTB_AFTER(PLTB_K_NEE_LIGHT);
+    k_trace<true><<<grid, 128, 0, s>>>(sc, st, 0); PLTB_AFTER(PLTB_K_TRACE_SHADOW);
 }
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
-    if (cls) { k_nee_post<1><<<grid, 128, 0, s>>>(sc, st); k_nee_eval<<<grid, 128, 0, s>>>(sc, st); }
-    else k_nee_post<0><<<grid, 128, 0, s>>>(sc, st);
+    if (cls) {
+        k_nee_post<1><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING);
+        k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL);
+    } else { k_nee_post<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint64_t dump_cap, cudaStream_t s) {
     k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, (dump_wl || dump_L) ? dump_cap : 0);
+    PLTB_AFTER(PLTB_K_GATHER);
     if (!do_splat) return;
     // separable filters with 3x3 (tent, r = 1) or 5x5 (gaussian, r = 2) taps go through the register tiles / shared strips
     const int nr = sc.film.rfilter == PLTB_RFILTER_BOX ? 0 : (int) ceilf(sc.film.radius - .5f);
@@ -372,9 +382,10 @@ void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &
         const uint32_t n_warps = n_strips * n_chunks, grid = (n_warps + kSplatWarps - 1) / kSplatWarps;
         if (nr == 1) k_splat_strip<1><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
         else k_splat_strip<2><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
+        PLTB_AFTER(PLTB_K_SPLAT);
         return;
     }
-    k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum);
+    k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
 }
 void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, cudaStream_t s) {
     k_develop<<<(unsigned) ((n_pixels + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4 *>(accum), rgb, n_pixels);

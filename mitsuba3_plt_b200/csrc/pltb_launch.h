@@ -5,6 +5,9 @@
 #include "pltb_integrator.cuh"
 
 namespace pltb {
+// Optional per-kernel hook (PLTB_RENDER_PROFILE): called by the launchers after every kernel launch with its PLTB_K_* id.
+struct LaunchHook { void (*fn)(int kernel, void *user) = nullptr; void *user = nullptr; };
+extern thread_local LaunchHook g_launch_hook;
 void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s);
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s);
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s);
