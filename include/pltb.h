@@ -131,8 +131,10 @@ typedef struct pltb_shape {
     float frame_n[3], inv_area;     /* rectangle: world normal, 1/surface area */
 } pltb_shape;
 
-/* Emitters (src/emitters/{area,directional}.cpp) */
-enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1 };
+/* Emitters (src/emitters/{area,directional,constant}.cpp).  CONSTANT is an environment emitter: rays that leave the scene see
+ * it (SurfaceInteraction::emitter(scene) of an invalid interaction, include/mitsuba/render/interaction.h:343-346); at most one
+ * environment emitter per scene (src/render/scene.cpp:60-67). */
+enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1, PLTB_EMITTER_CONSTANT = 2 };
 
 typedef struct pltb_emitter {
     uint32_t type;
@@ -140,7 +142,7 @@ typedef struct pltb_emitter {
     int32_t radiance;     /* texture index (area: radiance, directional: irradiance) */
     uint32_t pad;
     float direction[3];   /* directional: world-space direction of propagation */
-    float bsphere_radius; /* directional: scene bounding-sphere radius */
+    float bsphere_radius; /* directional / constant: scene bounding-sphere radius (constant: max(RayEpsilon, r (1 + RayEpsilon))) */
     float bsphere_center[3];
     float sampling_weight;
 } pltb_emitter;

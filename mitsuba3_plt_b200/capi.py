@@ -25,7 +25,7 @@ BSDF_FLAG_TWOSIDED = 1
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 SHAPE_MESH, SHAPE_SPHERE, SHAPE_RECTANGLE = range(3)
 SHAPE_HAS_NORMALS, SHAPE_HAS_UV, SHAPE_FLIP_NORMALS = 1, 2, 4
-EMITTER_AREA, EMITTER_DIRECTIONAL = 0, 1
+EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT = 0, 1, 2
 SENSOR_PERSPECTIVE, SENSOR_ORTHOGRAPHIC = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = range(3)
 RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT, RENDER_PROFILE = 1, 2, 4, 8, 16, 32

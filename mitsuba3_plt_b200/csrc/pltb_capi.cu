@@ -192,6 +192,11 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     ds.film = d->film;
     ds.n_faces = d->n_faces; ds.n_shapes = d->n_shapes; ds.n_emitters = d->n_emitters; ds.n_sensors = d->n_sensors;
     ds.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
+    ds.env = -1;
+    for (uint32_t i = 0; i < d->n_emitters; ++i) {
+        if (d->emitters[i].type > PLTB_EMITTER_CONSTANT) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
+        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT) ds.env = (int32_t) i;
+    }
     // Simpson nodes of math::bessel_j_small (include/mitsuba/core/math.h:204-223, 316-322), float ops as the reference
     {
         const float a = 0.f, b = kPi, h = (b - a) / (float) (20 - 1);

@@ -20,6 +20,7 @@ namespace pltb {
 
 constexpr float kPi = 3.14159265358979323846f;
 constexpr float kInvPi = 0.31830988618379067154f;
+constexpr float kInvFourPi = 0.07957747154594766788f;
 constexpr float kTwoPi = 6.28318530717958647692f;
 constexpr float kFourPi = 12.56637061435917295385f;
 constexpr float kInvSqrtPi = 0.56418958354775628695f;

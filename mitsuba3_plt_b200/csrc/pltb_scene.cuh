@@ -36,6 +36,7 @@ struct DeviceScene {
     pltb_film film;
     uint32_t n_faces, n_shapes, n_emitters, n_sensors;
     float emitter_pmf;
+    int32_t env;   // index of the environment emitter (Scene::environment(), src/render/scene.cpp:60-67), -1 if none
     BesselTables bessel;
 };
 

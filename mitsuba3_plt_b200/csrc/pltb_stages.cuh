@@ -31,6 +31,27 @@ PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32
 // Closest-hit bookkeeping shared by k_raygen (bounce 0) and k_trace (bounce >= 1): a hit is routed to the shade queue of
 // its material class; a miss finalises the path in place (plt.py:93-168 with si invalid: the five BSDF draws and the RR
 // draw are still consumed, the bounce record contributes nothing, the loop ends).
+// solve_replay_emissive (plt.py:315-405) for a ray that left the scene at bounce i when the scene has an environment emitter:
+// si.emitter(scene) of the invalid interaction is the environment (interaction.h:343-346), DirectionSample3f(scene, si, prev_si)
+// takes d = -si.wi = ray.d (records.h:173-180).  Constant background: pdf_direction = 1 / (4 pi) (constant.cpp:152-157),
+// eval = radiance (:92-96).  The replayed throughput is the prefix product of the recorded weights, as in stage_shade.
+PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
+    const pltb_emitter &e = sc.emitters[sc.env];
+    const S4 wl = f4_to_s4(st.wl[local]);
+    float last_nd_pdf = 1.f;
+    bool prev_bsdf_delta = true;
+    if (i > 0) {
+        last_nd_pdf = st.p_prev[local].w;
+        prev_bsdf_delta = (st.p_flags[local] & 1u) != 0;
+    }
+    S4 ai = s4(1.f);
+    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
+    const float em_pdf = prev_bsdf_delta ? 0.f : kInvFourPi * sc.emitter_pmf;
+    const float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
+    const S4 Le = tex_eval(sc, e.radiance, wl, mk2(0.f, 0.f));
+    return ai * (Le * mis_bsdf);
+}
+
 template <class Push>
 PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, const Hit &h, PCG32 &rng,
                        bool rng_dirty, Push &push) {
@@ -44,7 +65,7 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
         st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
         const size_t r = (size_t) i * st.chunk + local;
-        st.v_em[r] = mkf4(0.f, 0.f, 0.f, 0.f);
+        st.v_em[r] = sc.env >= 0 ? s4_to_f4(env_miss_emission(sc, st, local, i)) : mkf4(0.f, 0.f, 0.f, 0.f);
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
         st.n_vertices[local] = i + 1;
     }
@@ -207,6 +228,13 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
     DirectionSample ds;
     if (em.type == PLTB_EMITTER_AREA) {
         ds = shape_sample_direction(sc, sc.shapes[em.shape], p, sample);   // AreaLight::sample_direction (area.cpp:116-168)
+    } else if (em.type == PLTB_EMITTER_CONSTANT) {   // ConstantBackgroundEmitter::sample_direction (constant.cpp:121-150)
+        const float z = fnmadd(2.f, sample.y, 1.f), rr = safe_sqrt(fnmadd(z, z, 1.f)), a = 2.f * kPi * sample.x;
+        const V3 dir = mk3(rr * cosf(a), rr * sinf(a), z);   // warp::square_to_uniform_sphere (warp.h:250-255)
+        const V3 c = mk3(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+        const float dist = 2.f * fmaxf(em.bsphere_radius, norm(p - c));
+        ds.p = fmadd3(dir, dist, p);
+        ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
     } else {   // DirectionalEmitter::sample_direction (src/emitters/directional.cpp:149-176)
         V3 dirn = mk3(em.direction[0], em.direction[1], em.direction[2]);
         ds.d = -dirn;

@@ -512,6 +512,21 @@ class FlatScene:
     # ---- standalone emitters -------------------------------------------------------------------------------------------
     def emitter(self, p):
         t = p.plugin_name
+        if t == "constant":  # src/emitters/constant.cpp:52-67: props.texture_d65("radiance", 1.f)
+            if any(x.type == capi.EMITTER_CONSTANT for x in self.emitters):
+                raise RuntimeError("Only one environment emitter can be specified per scene.")   # scene.cpp:60-67
+            e = capi.Emitter()
+            e.type, e.shape = capi.EMITTER_CONSTANT, -1
+            v = p.get("radiance")
+            if v is None or (isinstance(v, (int, float)) and not isinstance(v, bool)):
+                e.radiance = self.texture_plugin(Properties("d65", scale=1.0 if v is None else float(v)), True)
+            else:
+                e.radiance = self.texture(p, "radiance", None, within_emitter=True)
+            if self.textures[e.radiance].type == capi.TEX_BITMAP:
+                raise RuntimeError("Expected a non-spatially varying radiance spectra!")
+            e.sampling_weight = float(p.get("sampling_weight", 1.0))
+            self.emitters.append(e)
+            return
         if t != "directional":
             raise RuntimeError(f'Plugin "{t}" not found (emitter outside the plt hot path)')
         e = capi.Emitter()
@@ -646,6 +661,10 @@ class FlatScene:
             if e.type == capi.EMITTER_DIRECTIONAL:
                 e.bsphere_center[:] = list(c.astype(F32))
                 e.bsphere_radius = r
+            elif e.type == capi.EMITTER_CONSTANT:  # ConstantBackgroundEmitter::set_scene (constant.cpp:74-89)
+                ray_eps = F32(2.0 ** -24 * 1500)   # math::RayEpsilon = dr::Epsilon<float> * 1500 (include/mitsuba/core/math.h:18)
+                e.bsphere_center[:] = list(c.astype(F32))
+                e.bsphere_radius = max(ray_eps, F32(r) * (F32(1) + ray_eps)) if np.all(np.isfinite(self.bbox[0])) else ray_eps
         self.c_shapes = (capi.Shape * max(1, len(self.shapes)))(*self.shapes)
         self.c_bsdfs = (capi.Bsdf * max(1, len(self.bsdfs)))(*self.bsdfs)
         self.c_textures = (capi.Texture * max(1, len(self.textures)))(*self.textures)

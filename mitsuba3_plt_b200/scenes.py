@@ -110,8 +110,9 @@ def _mesh(file, bsdf, face_normals, extra=""):
     return f'  <shape type="ply"><string name="filename" value="meshes/{file}"/>{fn}<ref id="{bsdf}" name="bsdf"/>{extra}</shape>\n'
 
 
-def write_cbox(directory, grating):
-    """C1 (`scenes/cbox`) or C2 (`scenes/cbox-grating`) equivalent.  Returns the path of the XML file."""
+def write_cbox(directory, grating, sky=None):
+    """C1 (`scenes/cbox`) or C2 (`scenes/cbox-grating`) equivalent.  Returns the path of the XML file.
+    `sky`: "sky" adds a `constant` environment emitter (the open cbox-grating box then sees it through its missing walls)."""
     os.makedirs(os.path.join(directory, "meshes"), exist_ok=True)
     os.makedirs(os.path.join(directory, "textures"), exist_ok=True)
     m = lambda n: os.path.join(directory, "meshes", n)
@@ -167,6 +168,10 @@ def write_cbox(directory, grating):
         x.append(_mesh("sphere_2.ply", "glass", False))
         for name, mat in (("ceiling", "white"), ("left", "red"), ("back", "white"), ("right", "green"), ("floor", "white")):
             x.append(_mesh(f"{name}.ply", mat, True))
+    if sky == "sky":
+        x.append('  <emitter type="constant"><rgb name="radiance" value="0.35 0.5 0.8"/></emitter>\n')
+    elif sky:
+        raise RuntimeError(f'unknown scene option "{sky}"')
     x.append("</scene>\n")
     path = os.path.join(directory, "scene.xml")
     with open(path, "w") as f:
@@ -341,7 +346,7 @@ def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_
     return path
 
 
-_BUILDERS = {"cbox": lambda d: write_cbox(d, False), "cbox-grating": lambda d: write_cbox(d, True),
+_BUILDERS = {"cbox": lambda d, a=None: write_cbox(d, False, a), "cbox-grating": lambda d, a=None: write_cbox(d, True, a),
              "veach-mis": write_veach_mis, "spectrograph": write_spectrograph,
              "gratingcap": write_gratingcap}
 

@@ -39,6 +39,7 @@ namespace {
 
 constexpr float kPi = 3.14159265358979323846f;
 constexpr float kInvPi = 0.31830988618379067154f;
+constexpr float kInvFourPi = 0.07957747154594766788f;
 constexpr float kTwoPi = 6.28318530717958647692f;
 constexpr float kFourPi = 12.56637061435917295385f;
 constexpr float kInvSqrtPi = 0.56418958354775628695f;
@@ -531,6 +532,7 @@ struct Scene {
     std::vector<BVHNode> nodes;
     std::vector<uint32_t> prims; /* < n_faces: triangle, else analytic shape id + n_faces */
     float emitter_pmf = 0.f;
+    int32_t env = -1; /* index of the environment emitter (Scene::environment(), scene.cpp:60-67), -1 if none */
     V3 pos(uint32_t i) const { return { d->positions[3 * i], d->positions[3 * i + 1], d->positions[3 * i + 2] }; }
     V3 nrm(uint32_t i) const { return { d->normals[3 * i], d->normals[3 * i + 1], d->normals[3 * i + 2] }; }
     V2 uv(uint32_t i) const { return { d->texcoords[2 * i], d->texcoords[2 * i + 1] }; }
@@ -1422,6 +1424,12 @@ S4 wbsdf_weight(const Scene &sc, const SI &si, V3 wo) { return twosided_call<S4>
 /* ------------------------------------------------------------------------------------------------------------
  * Emitters
  * ---------------------------------------------------------------------------------------------------------- */
+/* warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:250-255) */
+inline V3 square_to_uniform_sphere(V2 sample) {
+    float z = fnmadd(2.f, sample.y, 1.f), r = safe_sqrt(fnmadd(z, z, 1.f));
+    float a = 2.f * kPi * sample.x;
+    return V3(r * std::cos(a), r * std::sin(a), z);
+}
 struct DirectionSample { V3 p, n, d; V2 uv; float pdf = 0.f, dist = 0.f; bool delta = false; int32_t emitter = -1; };
 
 /* Mesh::sample_position (src/render/mesh.cpp:751-805) with DiscreteDistribution::sample_reuse
@@ -1658,6 +1666,17 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                     if (getenv("PLT_ORACLE_DEBUG") && std::isnan((a * Lem)[0]))
                         fprintf(stderr, "NaN EM bi=%u a=%g Lem=%g mis=%g lnd=%g empdf=%g\n", bi, a[0], Lem[0], mis_bsdf, b.last_nd_pdf, em_pdf);
                 }
+            } else if (sc.env >= 0) {
+                /* the ray escaped: si.emitter(scene) is the environment (interaction.h:343-346); DirectionSample3f(scene, si,
+                 * prev_si) takes d = -si.wi (records.h:173-180) */
+                const pltb_emitter &em = d->emitters[sc.env];
+                bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
+                /* ConstantBackgroundEmitter::pdf_direction (constant.cpp:152-157) */
+                float em_pdf = prev_delta ? 0.f : kInvFourPi * sc.emitter_pmf;
+                float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
+                S4 Le = emitter_radiance(sc, em, b.si.wavelengths, V2{ 0.f, 0.f }); /* ::eval, constant.cpp:92-96 */
+                S4 a = replay_path(sc, bb, (int) bi);
+                L = L + a * (Le * mis_bsdf);
             }
         }
         /* solve_replay_NEE, :221-300 */
@@ -1680,6 +1699,12 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                 DirectionSample ds;
                 if (em.type == PLTB_EMITTER_AREA) {
                     ds = shape_sample_direction(sc, d->shapes[em.shape], si.p, sample); /* area.cpp:116-168 */
+                } else if (em.type == PLTB_EMITTER_CONSTANT) { /* ::sample_direction, constant.cpp:121-150 */
+                    V3 dir = square_to_uniform_sphere(sample);
+                    V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+                    float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
+                    ds.p = fmadd(dir, dist, si.p);
+                    ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
                 } else { /* DirectionalEmitter::sample_direction, src/emitters/directional.cpp:149-176 */
                     V3 dirn(em.direction[0], em.direction[1], em.direction[2]);
                     ds.d = -dirn;
@@ -1859,6 +1884,8 @@ void prepare_scene(Scene &sc, const pltb_scene_desc *d) {
     if (!sc.prims.empty()) build_bvh(sc, lo, hi, 0, (uint32_t) sc.prims.size());
     else { BVHNode n{}; for (int k = 0; k < 3; ++k) { n.lo[k] = kInf; n.hi[k] = -kInf; } n.count = 0; n.left = n.right = 0; sc.nodes.push_back(n); sc.prims.clear(); sc.nodes[0].first = 0; }
     sc.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
+    for (uint32_t i = 0; i < d->n_emitters; ++i)
+        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT) sc.env = (int32_t) i;
 }
 
 } // namespace

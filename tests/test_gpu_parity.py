@@ -14,6 +14,8 @@ CASES = [  # (scene, res, spp, seed)
     ("spectrograph:bbody_3000", 1, 256, 0),  # C3: batch of 150 orthographic sensors with SRFs, directional blackbody light
     ("spectrograph:d65", 1, 64, 3),
     ("gratingcap", 96, 8, 0),                # C5: principled screen + non-radial grating strip, directional light
+    ("cbox-grating:sky", 64, 8, 2),          # `constant` environment emitter: escaped rays, uniform-sphere NEE (8f f3, first step)
+    ("cbox:sky", 48, 8, 4),
 ]
 
 
@@ -40,6 +42,23 @@ def test_per_sample_radiance(mi, oracle, integ, name, res, spp, seed):
         assert abs(a - b) <= max(4, 1e-3 * b), (k, a, b)
     rmse, mism = relative_mse(img, ref["image"])
     assert rmse <= MAX_RMSE and mism <= max_finiteness_mismatch(img.shape[0] * img.shape[1]), (rmse, mism)
+
+
+def test_environment_furnace(mi, oracle, integ):
+    """a large diffuse plane (albedo 0.5) under a uniform `constant` sky of radiance 1 reflects 0.5: emission of escaped rays
+    and uniform-sphere NEE with their MIS weights (constant.cpp:92-157) sum to the analytic value, and match the oracle"""
+    T = mi.Transform
+    sc = mi.load_dict({"type": "scene",
+                       "sensor": {"type": "perspective", "fov": 20, "to_world": T().look_at([0, 0, 5], [0, 0, 0], [0, 1, 0]),
+                                  "film": {"type": "hdrfilm", "width": 32, "height": 32}},
+                       "plane": {"type": "rectangle", "to_world": T().scale([50, 50, 1]),
+                                 "bsdf": {"type": "diffuse", "reflectance": {"type": "uniform", "value": 0.5}}},
+                       "sky": {"type": "constant", "radiance": {"type": "uniform", "value": 1.0}}})
+    dump = {}
+    integ.render(sc, spp=64, seed=1, dump=dump)
+    assert abs(dump["radiance"].mean() - 0.5) < 5e-3
+    ref = oracle.render(sc.flat, 64, seed=1, dump=True, film=False)
+    assert sample_agreement(dump["radiance"], ref["radiance"]) >= MIN_FRACTION
 
 
 def test_rr_and_depth_variants(mi, oracle):

@@ -74,6 +74,27 @@ def test_gratingcap_and_animation_path(mi, oracle):
     np.testing.assert_allclose(got, animation.camera_to_world(init, 60, 240).matrix.astype(np.float32), rtol=0, atol=0)
 
 
+def test_constant_environment_emitter(mi, oracle):
+    """`constant` environment emitter (src/emitters/constant.cpp) in the loader and the oracle: furnace value, one per scene"""
+    from mitsuba3_plt_b200 import capi, scenes
+    T = mi.Transform
+    d = {"type": "scene",
+         "sensor": {"type": "perspective", "fov": 20, "to_world": T().look_at([0, 0, 5], [0, 0, 0], [0, 1, 0]),
+                    "film": {"type": "hdrfilm", "width": 8, "height": 8}},
+         "plane": {"type": "rectangle", "to_world": T().scale([50, 50, 1]),
+                   "bsdf": {"type": "diffuse", "reflectance": {"type": "uniform", "value": 0.5}}},
+         "sky": {"type": "constant", "radiance": {"type": "uniform", "value": 1.0}}}
+    sc = mi.load_dict(d)
+    e = sc.flat.emitters[0]
+    assert e.type == capi.EMITTER_CONSTANT and e.bsphere_radius > 50 * np.sqrt(2) and sc.flat.desc.n_emitters == 1
+    L = oracle.render(sc.flat, 256, seed=1, max_depth=3, dump=True, film=False)["radiance"]
+    assert abs(L.mean() - 0.5) < 5e-3
+    with pytest.raises(RuntimeError, match="Only one environment emitter"):
+        mi.load_dict(dict(d, sky2={"type": "constant"}))
+    sky = scenes.load("cbox-grating:sky", resx=16, resy=16)
+    assert sky.flat.desc.n_emitters == 2 and sky.flat.textures[sky.flat.emitters[1].radiance].type == capi.TEX_D65
+
+
 def test_plugin_parameters_and_errors(mi):
     it = mi.load_dict({"type": "plt"})
     assert (it.max_depth, it.rr_depth) == (16, 4)          # plt.py:37-38
