@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define PLTB_ABI_VERSION 3
+#define PLTB_ABI_VERSION 4
 #define PLTB_MAX_DEPTH 16      /* upper bound on the `max_depth` plugin parameter (plt.py:37) */
 #define PLTB_MAX_LOBES 9       /* diffractionGratingsMaxLobes (include/mitsuba/plt/diffractiongrating.h:24) */
 
@@ -131,10 +131,10 @@ typedef struct pltb_shape {
     float frame_n[3], inv_area;     /* rectangle: world normal, 1/surface area */
 } pltb_shape;
 
-/* Emitters (src/emitters/{area,directional,constant}.cpp).  CONSTANT is an environment emitter: rays that leave the scene see
+/* Emitters (src/emitters/{area,directional,constant,envmap}.cpp).  CONSTANT and ENVMAP are environment emitters: rays that leave the scene see
  * it (SurfaceInteraction::emitter(scene) of an invalid interaction, include/mitsuba/render/interaction.h:343-346); at most one
  * environment emitter per scene (src/render/scene.cpp:60-67). */
-enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1, PLTB_EMITTER_CONSTANT = 2 };
+enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1, PLTB_EMITTER_CONSTANT = 2, PLTB_EMITTER_ENVMAP = 3 };
 
 typedef struct pltb_emitter {
     uint32_t type;
@@ -145,6 +145,15 @@ typedef struct pltb_emitter {
     float bsphere_radius; /* directional / constant: scene bounding-sphere radius (constant: max(RayEpsilon, r (1 + RayEpsilon))) */
     float bsphere_center[3];
     float sampling_weight;
+    /* envmap (src/emitters/envmap.cpp:110-243); `radiance` is the D65 whitepoint texture (m_d65) */
+    uint32_t env_warp;    /* offset in tex_data of the Hierarchical2D<Float, 0> block over luminance * sin(theta): words
+                             [n_levels, res_x, res_y, 0, {offset, width} per level] (integers as bit patterns), then the levels
+                             (include/mitsuba/core/distr_2d.h:344-470; level >= 1 in 2x2-patch order, Level::index :772-776) */
+    uint32_t env_data;    /* offset in tex_data of the (res_y, res_x, 4) array: rgb2spec coefficients + scale per texel */
+    uint32_t env_res[2];  /* res_x = bitmap width + 1 (last column repeats the first), res_y = bitmap height */
+    float env_scale;      /* `scale` plugin parameter */
+    float env_pad[3];
+    float to_world[16], to_local[16];   /* row-major 4x4 (only the linear part is used: transform_affine of directions) */
 } pltb_emitter;
 
 /* Sensors (src/sensors/{perspective,orthographic,batch}.cpp) */

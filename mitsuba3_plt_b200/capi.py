@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libpltb200.so")
 if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu_ab.sh)
     LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
-PLTB_ABI_VERSION = 3
+PLTB_ABI_VERSION = 4
 PLTB_MAX_DEPTH = 16
 
 # enums (include/pltb.h)
@@ -25,7 +25,7 @@ BSDF_FLAG_TWOSIDED = 1
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 SHAPE_MESH, SHAPE_SPHERE, SHAPE_RECTANGLE = range(3)
 SHAPE_HAS_NORMALS, SHAPE_HAS_UV, SHAPE_FLIP_NORMALS = 1, 2, 4
-EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT = 0, 1, 2
+EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2, 3
 SENSOR_PERSPECTIVE, SENSOR_ORTHOGRAPHIC = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = range(3)
 RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT, RENDER_PROFILE = 1, 2, 4, 8, 16, 32
@@ -51,7 +51,9 @@ class Shape(C.Structure):
 
 class Emitter(C.Structure):
     _fields_ = [("type", u32), ("shape", i32), ("radiance", i32), ("pad", u32), ("direction", f32 * 3),
-                ("bsphere_radius", f32), ("bsphere_center", f32 * 3), ("sampling_weight", f32)]
+                ("bsphere_radius", f32), ("bsphere_center", f32 * 3), ("sampling_weight", f32),
+                ("env_warp", u32), ("env_data", u32), ("env_res", u32 * 2), ("env_scale", f32), ("env_pad", f32 * 3),
+                ("to_world", f32 * 16), ("to_local", f32 * 16)]
 
 
 class Sensor(C.Structure):

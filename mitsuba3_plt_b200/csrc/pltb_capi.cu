@@ -194,8 +194,13 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     ds.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
     ds.env = -1;
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
-        if (d->emitters[i].type > PLTB_EMITTER_CONSTANT) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
-        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT) ds.env = (int32_t) i;
+        const pltb_emitter &e = d->emitters[i];
+        if (e.type > PLTB_EMITTER_ENVMAP) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
+        if (e.type == PLTB_EMITTER_CONSTANT || e.type == PLTB_EMITTER_ENVMAP) ds.env = (int32_t) i;
+        if (e.type == PLTB_EMITTER_ENVMAP &&
+            (e.env_res[0] < 3 || e.env_res[1] < 3 || (uint64_t) e.env_data + 4ull * e.env_res[0] * e.env_res[1] > d->n_tex_data ||
+             e.env_warp >= d->n_tex_data))
+            return fail(PLTB_ERR_INVALID, "envmap: data / warp blocks outside tex_data");
     }
     // Simpson nodes of math::bessel_j_small (include/mitsuba/core/math.h:204-223, 316-322), float ops as the reference
     {

@@ -2,6 +2,7 @@
 // material class; instantiated by the CUDA kernels of pltb_kernels.cu.
 #pragma once
 #include "pltb_integrator.cuh"
+#include "pltb_envmap.cuh"
 
 namespace pltb {
 
@@ -46,9 +47,18 @@ PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_
     }
     S4 ai = s4(1.f);
     for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
-    const float em_pdf = prev_bsdf_delta ? 0.f : kInvFourPi * sc.emitter_pmf;
+    float em_pdf = 0.f;
+    S4 Le;
+    if (e.type == PLTB_EMITTER_ENVMAP) {   // EnvironmentMapEmitter::pdf_direction / ::eval (envmap.cpp:468-484, 343-353)
+        const float4 d4 = st.p_ray_d[local];
+        const V3 d = mk3(d4.x, d4.y, d4.z);   // -si.wi of the invalid interaction
+        if (!prev_bsdf_delta) em_pdf = envmap_pdf_direction(sc, e, d) * sc.emitter_pmf;
+        Le = envmap_eval_spectrum(sc, e, envmap_dir_to_uv(xf_vector(e.to_local, d)), wl);
+    } else {
+        if (!prev_bsdf_delta) em_pdf = kInvFourPi * sc.emitter_pmf;
+        Le = tex_eval(sc, e.radiance, wl, mk2(0.f, 0.f));
+    }
     const float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
-    const S4 Le = tex_eval(sc, e.radiance, wl, mk2(0.f, 0.f));
     return ai * (Le * mis_bsdf);
 }
 
@@ -235,6 +245,11 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
         const float dist = 2.f * fmaxf(em.bsphere_radius, norm(p - c));
         ds.p = fmadd3(dir, dist, p);
         ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
+    } else if (em.type == PLTB_EMITTER_ENVMAP) {   // EnvironmentMapEmitter::sample_direction (envmap.cpp:421-466)
+        V3 dw;
+        envmap_sample_direction(sc, em, p, sample, dw, ds.dist, ds.uv, ds.pdf);
+        ds.p = p + dw * ds.dist;
+        ds.n = -dw; ds.delta = false; ds.d = dw;
     } else {   // DirectionalEmitter::sample_direction (src/emitters/directional.cpp:149-176)
         V3 dirn = mk3(em.direction[0], em.direction[1], em.direction[2]);
         ds.d = -dirn;
@@ -246,6 +261,7 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
     ds.d = normalize(ds.p - p);   // plt.py:264-269
     S4 em_val = s4(0.f);
     if (em.type == PLTB_EMITTER_AREA) { if (dot(ds.d, ds.n) < 0.f) em_val = tex_eval(sc, em.radiance, wl, ds.uv); }
+    else if (em.type == PLTB_EMITTER_ENVMAP) em_val = envmap_eval_spectrum(sc, em, ds.uv, wl);   // ::eval_direction (:486-491)
     else em_val = tex_eval(sc, em.radiance, wl, ds.uv);
     const S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
     st.v_nee[r] = s4_to_f4(em_weight);

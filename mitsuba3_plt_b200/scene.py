@@ -513,7 +513,7 @@ class FlatScene:
     def emitter(self, p):
         t = p.plugin_name
         if t == "constant":  # src/emitters/constant.cpp:52-67: props.texture_d65("radiance", 1.f)
-            if any(x.type == capi.EMITTER_CONSTANT for x in self.emitters):
+            if any(x.type in (capi.EMITTER_CONSTANT, capi.EMITTER_ENVMAP) for x in self.emitters):
                 raise RuntimeError("Only one environment emitter can be specified per scene.")   # scene.cpp:60-67
             e = capi.Emitter()
             e.type, e.shape = capi.EMITTER_CONSTANT, -1
@@ -527,6 +527,8 @@ class FlatScene:
             e.sampling_weight = float(p.get("sampling_weight", 1.0))
             self.emitters.append(e)
             return
+        if t == "envmap":
+            return self.envmap(p)
         if t != "directional":
             raise RuntimeError(f'Plugin "{t}" not found (emitter outside the plt hot path)')
         e = capi.Emitter()
@@ -540,6 +542,64 @@ class FlatScene:
         e.radiance = self.texture(p, "irradiance", None, within_emitter=True)
         if e.radiance < 0:
             e.radiance = self.texture_plugin(Properties("d65"), True)
+        e.sampling_weight = float(p.get("sampling_weight", 1.0))
+        self.emitters.append(e)
+
+    def envmap(self, p):
+        """EnvironmentMapEmitter (src/emitters/envmap.cpp:110-243): latitude-longitude bitmap -> per-texel rgb2spec coefficients
+        + scale (extra column for the periodic boundary) and a Hierarchical2D over luminance * sin(theta)."""
+        from . import distr2d, imageio
+        if any(x.type in (capi.EMITTER_CONSTANT, capi.EMITTER_ENVMAP) for x in self.emitters):
+            raise RuntimeError("Only one environment emitter can be specified per scene.")   # scene.cpp:60-67
+        if "bitmap" in p:
+            if "filename" in p:
+                raise RuntimeError('Cannot specify both "bitmap" and "filename".')
+            b = p["bitmap"]
+            rgb = np.asarray(getattr(b, "array", b), dtype=F32)
+        else:
+            path = p["filename"]
+            if not os.path.isabs(path):
+                path = os.path.join(getattr(p, "base_path", "."), path)
+            ext = path.rsplit(".", 1)[-1].lower()
+            if ext == "exr":
+                rgb = imageio.read_exr(path)[0]
+            elif ext == "npy":
+                rgb = np.load(path).astype(F32)
+            else:   # 8-bit formats are sRGB-encoded: Bitmap::convert(..., srgb_gamma = false) linearises them
+                from PIL import Image
+                rgb = spectra.srgb_to_linear(np.asarray(Image.open(path).convert("RGB"), dtype=F32) / F32(255))
+        if rgb.ndim == 2:
+            rgb = rgb[..., None]
+        if rgb.shape[2] == 1:
+            rgb = np.repeat(rgb, 3, axis=2)
+        rgb = np.ascontiguousarray(rgb[..., :3], dtype=F32)
+        H, W = rgb.shape[:2]
+        if W < 2 or H < 3:
+            raise RuntimeError("the environment map resolution must be at least 2x3 pixels")
+        lum = (F32(0.212671) * rgb[..., 0] + F32(0.715160) * rgb[..., 1] + F32(0.072169) * rgb[..., 2]).astype(F32)
+        offset = F32(0)
+        if p.get("mis_compensation", False):   # envmap.cpp:159-181
+            offset = F32(lum.astype(np.float64).sum() / (W * H))
+            if offset - min(F32(0), lum.min()) <= F32(0.01) * offset:
+                offset = F32(0)
+        scale = (rgb.max(axis=2) * F32(2)).astype(F32)
+        coeff = spectra.srgb_model_fetch(rgb / np.maximum(F32(1e-8), scale)[..., None])
+        data = np.concatenate([coeff, scale[..., None]], axis=2).astype(F32)
+        data = np.concatenate([data, data[:, :1]], axis=1)                    # last column mirrors the first
+        theta_scale = F32(1.0) / F32(H - 1) * F32(np.pi)
+        sin_theta = np.sin((np.arange(H, dtype=F32) * theta_scale).astype(F32)).astype(F32)
+        lw = (np.maximum(lum - offset, F32(0)) * sin_theta[:, None]).astype(F32)
+        lw = np.concatenate([lw, lw[:, :1]], axis=1)
+        e = capi.Emitter()
+        e.type, e.shape = capi.EMITTER_ENVMAP, -1
+        e.env_res[:] = [W + 1, H]
+        e.env_scale = float(p.get("scale", 1.0))
+        e.env_warp = self._push_data(distr2d.flatten_hierarchical(distr2d.build_hierarchical(lw), (W + 1, H)))
+        e.env_data = self._push_data(data.reshape(-1))
+        e.radiance = self.texture_plugin(Properties("d65"), False)             # m_d65 = Texture::D65(1.f)
+        tw = np.asarray(getattr(p.get("to_world"), "matrix", p.get("to_world", np.eye(4))), dtype=np.float64).reshape(4, 4)
+        e.to_world[:] = list(tw.astype(F32).reshape(-1))
+        e.to_local[:] = list(np.linalg.inv(tw).astype(F32).reshape(-1))
         e.sampling_weight = float(p.get("sampling_weight", 1.0))
         self.emitters.append(e)
 
@@ -661,7 +721,7 @@ class FlatScene:
             if e.type == capi.EMITTER_DIRECTIONAL:
                 e.bsphere_center[:] = list(c.astype(F32))
                 e.bsphere_radius = r
-            elif e.type == capi.EMITTER_CONSTANT:  # ConstantBackgroundEmitter::set_scene (constant.cpp:74-89)
+            elif e.type in (capi.EMITTER_CONSTANT, capi.EMITTER_ENVMAP):  # ::set_scene (constant.cpp:74-89, envmap.cpp:327-341)
                 ray_eps = F32(2.0 ** -24 * 1500)   # math::RayEpsilon = dr::Epsilon<float> * 1500 (include/mitsuba/core/math.h:18)
                 e.bsphere_center[:] = list(c.astype(F32))
                 e.bsphere_radius = max(ray_eps, F32(r) * (F32(1) + ray_eps)) if np.all(np.isfinite(self.bbox[0])) else ray_eps

@@ -170,6 +170,12 @@ def write_cbox(directory, grating, sky=None):
             x.append(_mesh(f"{name}.ply", mat, True))
     if sky == "sky":
         x.append('  <emitter type="constant"><rgb name="radiance" value="0.35 0.5 0.8"/></emitter>\n')
+    elif sky == "envmap":   # latitude-longitude EXR (ZIP-compressed half floats): sky gradient, ground, a small bright sun
+        from . import imageio
+        os.makedirs(os.path.join(directory, "textures"), exist_ok=True)
+        imageio.write_exr(os.path.join(directory, "textures", "sky.exr"), procedural_sky(), half=True, compression="zip")
+        x.append('  <emitter type="envmap"><string name="filename" value="textures/sky.exr"/><float name="scale" value="1.5"/>'
+                 '<transform name="to_world"><rotate y="1" angle="40"/><rotate x="1" angle="-15"/></transform></emitter>\n')
     elif sky:
         raise RuntimeError(f'unknown scene option "{sky}"')
     x.append("</scene>\n")
@@ -177,6 +183,18 @@ def write_cbox(directory, grating, sky=None):
     with open(path, "w") as f:
         f.write("".join(x))
     return path
+
+
+def procedural_sky(width=96, height=48):
+    """(height, width, 3) float32 environment map: blue-to-white sky above the horizon, dim brown ground, a 3x3-texel sun"""
+    v = (np.arange(height, dtype=np.float32) + 0.5) / height
+    u = (np.arange(width, dtype=np.float32) + 0.5) / width
+    up = np.clip(1.0 - 2.0 * v, 0.0, 1.0)[:, None]
+    sky = np.stack([0.35 + 0.5 * (1 - up), 0.5 + 0.4 * (1 - up), 0.9 + 0.0 * up], -1) * (0.6 + 0.4 * np.cos(2 * np.pi * u)[None, :, None])
+    ground = np.array([0.12, 0.09, 0.06], np.float32) * (1.0 + 0.3 * np.sin(6 * np.pi * u))[None, :, None]
+    img = np.where((v < 0.5)[:, None, None], sky, np.broadcast_to(ground, sky.shape)).astype(np.float32)
+    img[height // 5:height // 5 + 3, width // 3:width // 3 + 3] = [60.0, 52.0, 40.0]
+    return img
 
 
 def _xf(m):

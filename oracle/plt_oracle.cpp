@@ -1424,6 +1424,112 @@ S4 wbsdf_weight(const Scene &sc, const SI &si, V3 wo) { return twosided_call<S4>
 /* ------------------------------------------------------------------------------------------------------------
  * Emitters
  * ---------------------------------------------------------------------------------------------------------- */
+/* ------------------------------------------------------------------------------------------------------------
+ * Hierarchical2D<Float, 0> (include/mitsuba/core/distr_2d.h:475-700) over the flattened block built by
+ * mitsuba3_plt_b200/distr2d.py, and EnvironmentMapEmitter (src/emitters/envmap.cpp:343-560)
+ * ---------------------------------------------------------------------------------------------------------- */
+inline uint32_t as_u32(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+inline float clip01(float x) { return std::min(std::max(x, 0.f), 1.f); }
+inline float lerp_(float a, float b, float t) { return fmadd(b, t, fnmadd(a, t, a)); } /* dr::lerp */
+/* warp::interval_to_linear (warp.h:447-453) */
+inline float interval_to_linear(float v0, float v1, float sample) {
+    if (std::fabs(v0 - v1) > 1e-4f * (v0 + v1))
+        return (v0 - safe_sqrt(lerp_(sqr(v0), sqr(v1), sample))) / (v0 - v1);
+    return sample;
+}
+struct Hier2D {
+    const float *blk; uint32_t n_levels, res_x, res_y;
+    explicit Hier2D(const float *b) : blk(b), n_levels(as_u32(b[0])), res_x(as_u32(b[1])), res_y(as_u32(b[2])) {}
+    const float *level(uint32_t l) const { return blk + as_u32(blk[4 + 2 * l]); }
+    uint32_t width(uint32_t l) const { return as_u32(blk[5 + 2 * l]); }
+    static uint32_t index(uint32_t x, uint32_t y, uint32_t w) { return ((x & 1u) | (((x & ~1u) | (y & 1u)) << 1)) + (y & ~1u) * w; }
+    /* sample(), distr_2d.h:481-563 */
+    void sample(V2 s, V2 &out, float &pdf) const {
+        s.x = clip01(s.x); s.y = clip01(s.y);
+        uint32_t ox = 0, oy = 0;
+        for (int l = (int) n_levels - 2; l > 0; --l) {
+            const float *lv = level((uint32_t) l);
+            ox <<= 1; oy <<= 1;
+            uint32_t i = index(ox, oy, width((uint32_t) l));
+            float v00 = lv[i], v10 = lv[i + 1], v01 = lv[i + 2], v11 = lv[i + 3];
+            s.x = clip01(s.x); s.y = clip01(s.y);
+            float r0 = v00 + v10, r1 = v01 + v11;
+            s.y *= r0 + r1;
+            bool m = s.y > r0;
+            if (m) { oy += 1; s.y -= r0; }
+            s.y /= m ? r1 : r0;
+            float c0 = m ? v01 : v00, c1 = m ? v11 : v10;
+            s.x *= c0 + c1;
+            m = s.x > c0;
+            if (m) s.x -= c0;
+            s.x /= m ? c1 : c0;
+            if (m) ox += 1;
+        }
+        const float *l0 = level(0);
+        uint32_t w = width(0), i = ox + oy * w;
+        float v00 = l0[i], v10 = l0[i + 1], v01 = l0[i + w], v11 = l0[i + w + 1];
+        /* warp::square_to_bilinear, warp.h:480-494 */
+        float r0 = v00 + v10, r1 = v01 + v11;
+        s.y = interval_to_linear(r0, r1, s.y);
+        float c0 = lerp_(v00, v01, s.y), c1 = lerp_(v10, v11, s.y);
+        s.x = interval_to_linear(c0, c1, s.x);
+        pdf = lerp_(c0, c1, s.x);
+        float psx = 1.f / (float) (res_x - 1), psy = 1.f / (float) (res_y - 1); /* m_patch_size */
+        out.x = ((float) (int32_t) ox + s.x) * psx;
+        out.y = ((float) (int32_t) oy + s.y) * psy;
+    }
+    /* eval(), distr_2d.h:668-699 */
+    float eval(V2 pos) const {
+        pos.x = clip01(pos.x) * (float) (res_x - 1); pos.y = clip01(pos.y) * (float) (res_y - 1);
+        uint32_t ox = std::min((uint32_t) (int32_t) pos.x, res_x - 2), oy = std::min((uint32_t) (int32_t) pos.y, res_y - 2);
+        pos.x -= (float) (int32_t) ox; pos.y -= (float) (int32_t) oy;
+        const float *l0 = level(0);
+        uint32_t w = width(0), i = ox + oy * w;
+        float v00 = l0[i], v10 = l0[i + 1], v01 = l0[i + w], v11 = l0[i + w + 1];
+        return lerp_(lerp_(v00, v10, pos.x), lerp_(v01, v11, pos.x), pos.y); /* square_to_bilinear_pdf, warp.h:516-521 */
+    }
+};
+inline float safe_acos(float x) { return std::acos(std::min(std::max(x, -1.f), 1.f)); }
+/* EnvironmentMapEmitter::eval_spectrum (envmap.cpp:524-580), include_whitepoint = true */
+S4 tex_eval(const Scene &sc, int32_t id, const S4 &wl, V2 uv);
+inline float srgb_model_eval(const float *c, float wl);
+S4 envmap_eval_spectrum(const Scene &sc, const pltb_emitter &em, V2 uv, const S4 &wl) {
+    const uint32_t rx = em.env_res[0], ry = em.env_res[1];
+    uv.x -= .5f / (float) (rx - 1u);
+    uv.x -= std::floor(uv.x); uv.y -= std::floor(uv.y);
+    uv.x *= (float) (rx - 1u); uv.y *= (float) (ry - 1u);
+    uint32_t px = std::min((uint32_t) uv.x, rx - 2u), py = std::min((uint32_t) uv.y, ry - 2u);
+    float w1x = uv.x - (float) px, w1y = uv.y - (float) py, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    const float *data = sc.d->tex_data + em.env_data;
+    uint32_t index = py * rx + px;
+    const float *v00 = data + 4 * (size_t) index, *v10 = v00 + 4, *v01 = v00 + 4 * (size_t) rx, *v11 = v01 + 4;
+    S4 white = tex_eval(sc, em.radiance, wl, V2{ 0.f, 0.f });
+    S4 result;
+    float f0 = fmadd(w0x, v00[3], w1x * v10[3]), f1 = fmadd(w0x, v01[3], w1x * v11[3]), f = fmadd(w0y, f0, w1y * f1);
+    for (int i = 0; i < 4; ++i) {
+        float s00 = srgb_model_eval(v00, wl[i]), s10 = srgb_model_eval(v10, wl[i]);
+        float s01 = srgb_model_eval(v01, wl[i]), s11 = srgb_model_eval(v11, wl[i]);
+        float s0 = fmadd(w0x, s00, w1x * s10), s1 = fmadd(w0x, s01, w1x * s11), sv = fmadd(w0y, s0, w1y * s1);
+        result[i] = ((sv * f) * em.env_scale) * white[i];
+    }
+    return result;
+}
+inline V2 envmap_dir_to_uv(V3 v) { /* envmap.cpp:348-350 */
+    return V2{ std::atan2(v.x, -v.z) * (0.5f * kInvPi), safe_acos(v.y) * kInvPi };
+}
+inline float envmap_inv_sin_theta(V3 d) { /* safe_rsqrt(max(d.x^2 + d.z^2, Epsilon^2)), envmap.cpp:443-444 */
+    float v = std::max(sqr(d.x) + sqr(d.z), sqr(kEps));
+    return 1.f / std::sqrt(std::max(v, 0.f));
+}
+/* ::pdf_direction (envmap.cpp:468-484) */
+float envmap_pdf_direction(const Scene &sc, const pltb_emitter &em, V3 d_world) {
+    V3 d = xf_vector(em.to_local, d_world);
+    V2 uv = envmap_dir_to_uv(d);
+    uv.x -= .5f / (float) (em.env_res[0] - 1u);
+    uv.x -= std::floor(uv.x); uv.y -= std::floor(uv.y);
+    Hier2D warp(sc.d->tex_data + em.env_warp);
+    return warp.eval(uv) * envmap_inv_sin_theta(d) * (1.f / (2.f * sqr(kPi)));
+}
 /* warp::square_to_uniform_sphere (include/mitsuba/core/warp.h:250-255) */
 inline V3 square_to_uniform_sphere(V2 sample) {
     float z = fnmadd(2.f, sample.y, 1.f), r = safe_sqrt(fnmadd(z, z, 1.f));
@@ -1671,10 +1777,16 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                  * prev_si) takes d = -si.wi (records.h:173-180) */
                 const pltb_emitter &em = d->emitters[sc.env];
                 bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
-                /* ConstantBackgroundEmitter::pdf_direction (constant.cpp:152-157) */
-                float em_pdf = prev_delta ? 0.f : kInvFourPi * sc.emitter_pmf;
+                /* ConstantBackgroundEmitter::pdf_direction (constant.cpp:152-157) / EnvironmentMapEmitter (envmap.cpp:468-484) */
+                float em_pdf = 0.f;
+                if (!prev_delta)
+                    em_pdf = (em.type == PLTB_EMITTER_ENVMAP ? envmap_pdf_direction(sc, em, -b.si.wi) : kInvFourPi) * sc.emitter_pmf;
                 float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
-                S4 Le = emitter_radiance(sc, em, b.si.wavelengths, V2{ 0.f, 0.f }); /* ::eval, constant.cpp:92-96 */
+                S4 Le;
+                if (em.type == PLTB_EMITTER_ENVMAP) /* ::eval, envmap.cpp:343-353 */
+                    Le = envmap_eval_spectrum(sc, em, envmap_dir_to_uv(xf_vector(em.to_local, -b.si.wi)), b.si.wavelengths);
+                else
+                    Le = emitter_radiance(sc, em, b.si.wavelengths, V2{ 0.f, 0.f }); /* ::eval, constant.cpp:92-96 */
                 S4 a = replay_path(sc, bb, (int) bi);
                 L = L + a * (Le * mis_bsdf);
             }
@@ -1705,6 +1817,23 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                     float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
                     ds.p = fmadd(dir, dist, si.p);
                     ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
+                } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::sample_direction, envmap.cpp:421-466 */
+                    Hier2D warp(d->tex_data + em.env_warp);
+                    V2 uv; float pdf;
+                    warp.sample(sample, uv, pdf);
+                    uv.x += .5f / (float) (em.env_res[0] - 1u);
+                    bool act_s = pdf > 0.f;
+                    float theta = uv.y * kPi, phi = uv.x * (2.f * kPi);
+                    float st = std::sin(theta), ct = std::cos(theta), sp = std::sin(phi), cp = std::cos(phi);
+                    V3 sd(cp * st, sp * st, ct); /* dr::sphdir */
+                    V3 dl(sd.y, sd.z, -sd.x);
+                    V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+                    float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
+                    float inv_sin_theta = envmap_inv_sin_theta(dl);
+                    V3 dw = xf_vector(em.to_world, dl);
+                    ds.p = si.p + dw * dist;
+                    ds.n = -dw; ds.uv = uv; ds.delta = false; ds.d = dw; ds.dist = dist;
+                    ds.pdf = act_s ? pdf * inv_sin_theta * (1.f / (2.f * sqr(kPi))) : 0.f;
                 } else { /* DirectionalEmitter::sample_direction, src/emitters/directional.cpp:149-176 */
                     V3 dirn(em.direction[0], em.direction[1], em.direction[2]);
                     ds.d = -dirn;
@@ -1727,7 +1856,9 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                 S4 em_val(0.f);
                 if (em.type == PLTB_EMITTER_AREA) { /* AreaLight::eval_direction, area.cpp:198-208 */
                     if (dot(ds.d, ds.n) < 0.f) em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
-                } else { /* DirectionalEmitter::eval_direction, directional.cpp:189-195 */
+                } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::eval_direction, envmap.cpp:486-491 */
+                    em_val = envmap_eval_spectrum(sc, em, ds.uv, si.wavelengths);
+                } else { /* DirectionalEmitter / ConstantBackgroundEmitter::eval_direction (directional.cpp:189-195) */
                     em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
                 }
                 S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : S4(0.f);
@@ -1885,7 +2016,7 @@ void prepare_scene(Scene &sc, const pltb_scene_desc *d) {
     else { BVHNode n{}; for (int k = 0; k < 3; ++k) { n.lo[k] = kInf; n.hi[k] = -kInf; } n.count = 0; n.left = n.right = 0; sc.nodes.push_back(n); sc.prims.clear(); sc.nodes[0].first = 0; }
     sc.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
     for (uint32_t i = 0; i < d->n_emitters; ++i)
-        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT) sc.env = (int32_t) i;
+        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT || d->emitters[i].type == PLTB_EMITTER_ENVMAP) sc.env = (int32_t) i;
 }
 
 } // namespace
@@ -2057,5 +2188,33 @@ void plt_oracle_principled_eval_pdf(const pltb_bsdf *b_in, float base_color, con
     for (int i = 0; i < 4; ++i) out[i] = e[i];
     out[4] = principled_pdf(b, si, w);
 }
+
+void plt_oracle_hier2d_sample(const float *block, const float *u, float *out) { /* out: x, y, pdf */
+    V2 o; float pdf; Hier2D(block).sample(V2{ u[0], u[1] }, o, pdf); out[0] = o.x; out[1] = o.y; out[2] = pdf;
+}
+/* envmap consistency probe (the reference's own check, src/emitters/tests/test_envmap.py:43-70): for a uniform sample u,
+ * out = { ds.pdf from sample_direction, pdf_direction(ds.d), eval(si.wi = -ds.d)[0], eval_direction(ds.uv)[0], d.x, d.y, d.z } */
+void plt_oracle_envmap_probe(const pltb_scene_desc *d, const float *u, const float *wl4, float *out) {
+    Scene sc; sc.d = d;
+    const pltb_emitter *emp = nullptr;
+    for (uint32_t i = 0; i < d->n_emitters; ++i) if (d->emitters[i].type == PLTB_EMITTER_ENVMAP) emp = &d->emitters[i];
+    if (!emp) { out[0] = -1.f; return; }
+    const pltb_emitter &em = *emp;
+    S4 wl; for (int i = 0; i < 4; ++i) wl[i] = wl4[i];
+    Hier2D warp(d->tex_data + em.env_warp);
+    V2 uv; float pdf;
+    warp.sample(V2{ u[0], u[1] }, uv, pdf);
+    uv.x += .5f / (float) (em.env_res[0] - 1u);
+    float theta = uv.y * kPi, phi = uv.x * (2.f * kPi);
+    V3 sd(std::cos(phi) * std::sin(theta), std::sin(phi) * std::sin(theta), std::cos(theta));
+    V3 dl(sd.y, sd.z, -sd.x);
+    V3 dw = xf_vector(em.to_world, dl);
+    out[0] = pdf > 0.f ? pdf * envmap_inv_sin_theta(dl) * (1.f / (2.f * sqr(kPi))) : 0.f;
+    out[1] = envmap_pdf_direction(sc, em, dw);
+    out[2] = envmap_eval_spectrum(sc, em, envmap_dir_to_uv(xf_vector(em.to_local, dw)), wl)[0];
+    out[3] = envmap_eval_spectrum(sc, em, uv, wl)[0];
+    out[4] = dw.x; out[5] = dw.y; out[6] = dw.z;
+}
+float plt_oracle_hier2d_eval(const float *block, const float *pos) { return Hier2D(block).eval(V2{ pos[0], pos[1] }); }
 
 } // extern "C"

@@ -16,6 +16,8 @@ CASES = [  # (scene, res, spp, seed)
     ("gratingcap", 96, 8, 0),                # C5: principled screen + non-radial grating strip, directional light
     ("cbox-grating:sky", 64, 8, 2),          # `constant` environment emitter: escaped rays, uniform-sphere NEE (8f f3, first step)
     ("cbox:sky", 48, 8, 4),
+    ("cbox-grating:envmap", 64, 8, 5),       # `envmap` emitter (EXR file, rotated): Hierarchical2D sampling, bilinear spectral lookup
+    ("cbox:envmap", 48, 8, 6),
 ]
 
 

@@ -95,6 +95,68 @@ def test_constant_environment_emitter(mi, oracle):
     assert sky.flat.desc.n_emitters == 2 and sky.flat.textures[sky.flat.emitters[1].radiance].type == capi.TEX_D65
 
 
+def test_hierarchical2d_and_envmap(mi, oracle, tmp_path):
+    """Hierarchical2D0 against the reference's own spot checks (src/core/tests/test_distr_2d.py:9-50, "vs Mathematica") and the
+    envmap consistency checks of src/emitters/tests/test_envmap.py:43-70 (sample_direction pdf == pdf_direction, eval through
+    the direction == eval_direction through uv), on the oracle."""
+    import ctypes as C
+    from mitsuba3_plt_b200 import capi, distr2d, imageio, scenes
+    L = oracle.lib()
+    PF = C.POINTER(C.c_float)
+    L.plt_oracle_hier2d_sample.argtypes = [PF, PF, PF]
+    L.plt_oracle_hier2d_eval.argtypes, L.plt_oracle_hier2d_eval.restype = [PF, PF], C.c_float
+    L.plt_oracle_envmap_probe.argtypes = [C.POINTER(capi.SceneDesc), PF, PF, PF]
+    ref = np.array([[1, 2, 5], [9, 7, 2]], np.float32)
+    blk = distr2d.flatten_hierarchical(distr2d.build_hierarchical(ref), (3, 2))
+    b, out = blk.ctypes.data_as(PF), (C.c_float * 3)()
+
+    def sample(u):
+        L.plt_oracle_hier2d_sample(b, oracle.farr(*u), out)
+        return np.array(list(out))
+
+    assert np.allclose(sample([0, 0]), [0, 0, 8 / 35], atol=1e-6)
+    assert np.allclose(sample([1, 1]), [1, 1, 16 / 35], atol=1e-6)
+    assert np.allclose(sample([19 / 35, 0]), [0.5, 0, 16 / 35], atol=1e-6)
+    bil = lambda v00, v10, v01, v11, x, y: (v00 * (1 - x) + v10 * x) * (1 - y) + (v01 * (1 - x) + v11 * x) * y
+    assert abs(L.plt_oracle_hier2d_eval(b, oracle.farr(0.2, 0.3)) - bil(1, 2, 9, 7, .4, .3) * 8 / 35) < 1e-6
+    assert abs(L.plt_oracle_hier2d_eval(b, oracle.farr(0.7, 0.3)) - bil(2, 5, 7, 2, .4, .3) * 8 / 35) < 1e-6
+    # the density integrates to one and sampling follows it: mean of 1/pdf over samples == area of the unit square
+    rng = np.random.default_rng(3)
+    big = distr2d.flatten_hierarchical(distr2d.build_hierarchical((rng.random((13, 22)) ** 3).astype(np.float32)), (22, 13))
+    bp = big.ctypes.data_as(PF)
+    inv = []
+    for u in rng.random((4000, 2)):
+        L.plt_oracle_hier2d_sample(bp, oracle.farr(*u), out)
+        assert abs(L.plt_oracle_hier2d_eval(bp, oracle.farr(out[0], out[1])) - out[2]) <= 2e-4 * out[2] + 1e-6
+        inv.append(1.0 / out[2])
+    assert abs(np.mean(inv) - 1.0) < 0.05
+    # envmap: file round trip (EXR, ZIP, half), loader errors, probe
+    sc = scenes.load("cbox-grating:envmap", resx=16, resy=16)
+    e = [x for x in sc.flat.emitters if x.type == capi.EMITTER_ENVMAP][0]
+    assert list(e.env_res) == [97, 48] and e.env_scale == 1.5 and sc.flat.desc.n_emitters == 2
+    probe, wl = (C.c_float * 7)(), oracle.farr(450, 520, 590, 660)
+    for u in rng.random((500, 2)):
+        L.plt_oracle_envmap_probe(C.byref(sc.flat.desc), oracle.farr(*u), wl, probe)
+        assert abs(probe[0] - probe[1]) <= 1e-3 * probe[1] and abs(probe[2] - probe[3]) <= 1e-3 * probe[3] + 1e-6
+        assert abs(np.linalg.norm(probe[4:7]) - 1) < 1e-5
+    with pytest.raises(RuntimeError, match="at least 2x3"):
+        mi.load_dict({"type": "scene", "e": {"type": "envmap", "bitmap": np.ones((2, 2, 3), np.float32)}})
+    with pytest.raises(RuntimeError, match="Only one environment emitter"):
+        mi.load_dict({"type": "scene", "e": {"type": "envmap", "bitmap": np.ones((4, 4, 3), np.float32)}, "f": {"type": "constant"}})
+    # a constant map is the constant emitter: furnace value 0.5 * 0.7 * d65
+    T = mi.Transform
+    base = {"type": "scene",
+            "sensor": {"type": "perspective", "fov": 20, "to_world": T().look_at([0, 0, 5], [0, 0, 0], [0, 1, 0]),
+                       "film": {"type": "hdrfilm", "width": 8, "height": 8}},
+            "plane": {"type": "rectangle", "to_world": T().scale([50, 50, 1]),
+                      "bsdf": {"type": "diffuse", "reflectance": {"type": "uniform", "value": 0.5}}}}
+    a = mi.load_dict(dict(base, sky={"type": "envmap", "bitmap": np.full((16, 32, 3), 0.7, np.float32)}))
+    c = mi.load_dict(dict(base, sky={"type": "constant", "radiance": 0.7}))
+    ra = oracle.render(a.flat, 512, seed=1, max_depth=3, dump=True, film=False)["radiance"].mean()
+    rc = oracle.render(c.flat, 512, seed=1, max_depth=3, dump=True, film=False)["radiance"].mean()
+    assert abs(ra / rc - 1) < 0.01
+
+
 def test_plugin_parameters_and_errors(mi):
     it = mi.load_dict({"type": "plt"})
     assert (it.max_depth, it.rr_depth) == (16, 4)          # plt.py:37-38
