@@ -290,6 +290,118 @@ def write_gratingcap(directory):
     return path
 
 
+def write_disk(directory):
+    """`scenes/disk/disk.xml` equivalent (config 5, driven by disk_animation.py): a leaning optical disc with a radial
+    sinusoidal `roughgrating` (inv_period 0.8/0.8, 7 lobes, alpha 0.01; disk.xml:45-56), a 56 x 56 ground plane, a metallic
+    `principled` box with a bitmap base colour and four dark metallic feet (disk.xml:64-97), lit only by an `envmap` with the
+    file's to_world (:107-114).  The reference's EXR (`textures/empty_play_room.exr`) is missing from its snapshot, so a
+    procedural sky is written instead; geometry is regenerated with comparable triangle counts (disc 384, box 12, feet 4 x 124
+    in the original -> 4 x 64 here)."""
+    from PIL import Image
+    from . import imageio
+    os.makedirs(os.path.join(directory, "meshes"), exist_ok=True)
+    os.makedirs(os.path.join(directory, "textures"), exist_ok=True)
+    m = lambda n: os.path.join(directory, "meshes", n)
+    # disc: annulus r in [0.3, 2.4], 96 segments x 2 rings, uv centred on (0.5, 0.5) for the radial grating direction
+    seg, radii, ro = 96, (0.3, 1.35, 2.4), 2.4
+    ax, ay = math.radians(62.0), math.radians(-20.0)
+    rx = np.array([[1, 0, 0], [0, math.cos(ax), -math.sin(ax)], [0, math.sin(ax), math.cos(ax)]])
+    ry = np.array([[math.cos(ay), 0, math.sin(ay)], [0, 1, 0], [-math.sin(ay), 0, math.cos(ay)]])
+    rot, centre = ry @ rx, np.array([-0.39, 1.277, 0.273])
+    pos, uv, faces = [], [], []
+    for r in radii:
+        for k in range(seg):
+            a = 2 * math.pi * k / seg
+            lx, ly = r * math.cos(a), r * math.sin(a)
+            pos.append(centre + rot @ np.array([lx, 0.0, ly])); uv.append((0.5 + 0.5 * lx / ro, 0.5 + 0.5 * ly / ro))
+    for ring in range(2):
+        for k in range(seg):
+            a0, a1 = ring * seg + k, ring * seg + (k + 1) % seg
+            b0, b1 = a0 + seg, a1 + seg
+            faces += [(a0, b0, b1), (a0, b1, a1)]
+    write_ply(m("Circle.ply"), pos, faces, None, uv)
+    p, t, f = quad((-28.283, 0, 28.283), (28.283, 0, 28.283), (28.283, 0, -28.283), (-28.283, 0, -28.283))
+    write_ply(m("Plane_001.ply"), p, f, None, t)
+
+    def box(lo, hi):
+        lo, hi = np.array(lo, np.float32), np.array(hi, np.float32)
+        P, N, T, F = [], [], [], []
+        for axis in range(3):
+            for sgn in (-1, 1):
+                u, v = (axis + 1) % 3, (axis + 2) % 3
+                n = np.zeros(3); n[axis] = sgn
+                base = len(P)
+                for (cu, cv) in ((0, 0), (1, 0), (1, 1), (0, 1)) if sgn > 0 else ((0, 0), (0, 1), (1, 1), (1, 0)):
+                    q = np.zeros(3); q[axis] = hi[axis] if sgn > 0 else lo[axis]
+                    q[u] = hi[u] if cu else lo[u]; q[v] = hi[v] if cv else lo[v]
+                    P.append(q); N.append(n); T.append((cu, cv))
+                F += [(base, base + 1, base + 2), (base, base + 2, base + 3)]
+        return P, N, T, F
+
+    P, N, T, F = box((-2.216, 0.079, -5.391), (4.521, 1.333, -1.004))
+    write_ply(m("Object_4.ply"), P, F, N, T)
+
+    def foot(cx, cz, r=0.282, y0=-0.038, y1=0.094, n=16):
+        P, N, T, F = [], [], [], []
+        for k in range(n):            # side wall
+            a = 2 * math.pi * k / n
+            d = np.array([math.cos(a), 0, math.sin(a)])
+            P += [np.array([cx, y0, cz]) + r * d, np.array([cx, y1, cz]) + r * d]; N += [d, d]; T += [(k / n, 0), (k / n, 1)]
+        for k in range(n):
+            a0, a1, b0, b1 = 2 * k, 2 * k + 1, 2 * ((k + 1) % n), 2 * ((k + 1) % n) + 1
+            F += [(a0, a1, b1), (a0, b1, b0)]
+        for y, ny in ((y1, 1.0), (y0, -1.0)):   # caps (fans)
+            c = len(P); P.append(np.array([cx, y, cz])); N.append(np.array([0, ny, 0])); T.append((0.5, 0.5))
+            for k in range(n):
+                a = 2 * math.pi * k / n
+                P.append(np.array([cx + r * math.cos(a), y, cz + r * math.sin(a)])); N.append(np.array([0, ny, 0]))
+                T.append((0.5 + 0.5 * math.cos(a), 0.5 + 0.5 * math.sin(a)))
+            for k in range(n):
+                i0, i1 = c + 1 + k, c + 1 + (k + 1) % n
+                F.append((c, i1, i0) if ny > 0 else (c, i0, i1))
+        return P, N, T, F
+
+    for name, (cx, cz) in (("Object_6", (-1.728, -1.555)), ("Object_8", (-1.746, -4.887)), ("Object_10", (4.059, -1.555)),
+                           ("Object_12", (4.041, -4.905))):
+        P, N, T, F = foot(cx, cz)
+        write_ply(m(f"{name}.ply"), P, F, N, T)
+    Image.fromarray(uv_test_texture(256)).save(os.path.join(directory, "textures", "Material.005_baseColor.png"))
+    imageio.write_exr(os.path.join(directory, "textures", "empty_play_room.exr"), procedural_sky(128, 64), compression="zip")
+    pr = ('<rgb value="1.000000 1.000000 1.000000" name="spec_tint"/><float name="spec_trans" value="0.000000"/>'
+          '<float name="metallic" value="1.000000"/><float name="anisotropic" value="0.000000"/>'
+          '<float name="roughness" value="0.250000"/><float name="sheen" value="0.000000"/>'
+          '<rgb value="1.000000 1.000000 1.000000" name="sheen_tint"/><float name="clearcoat" value="0.000000"/>'
+          '<float name="clearcoat_gloss" value="0.000000"/><float name="specular" value="0.500000"/>')
+    x = ['<scene version="2.1.0">\n  <default name="spp" value="4096"/>\n  <default name="resx" value="800"/>\n'
+         '  <default name="resy" value="600"/>\n  <integrator type="plt"><integer name="max_depth" value="7"/>'
+         '<integer name="rr_depth" value="50"/></integrator>\n'
+         '  <sensor type="perspective" id="elm__1"><string name="fov_axis" value="x"/><float name="fov" value="39.379790"/>'
+         '<float name="near_clip" value="0.100000"/><float name="far_clip" value="100.000000"/>'
+         '<transform name="to_world"><rotate x="1" angle="-153.5592908827048"/><rotate y="1" angle="-18.26924314288295"/>'
+         '<rotate z="1" angle="-179.999991348578"/><translate value="4.924093 7.262070 11.595866"/></transform>'
+         '<sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>'
+         '<film type="hdrfilm"><integer name="width" value="$resx"/><integer name="height" value="$resy"/></film></sensor>\n',
+         '  <bsdf type="twosided" id="mat-Material.001"><bsdf type="roughgrating"><string name="lobe_type" value="sinusoidal"/>'
+         '<float name="height" value="0.04"/><float name="inv_period_x" value="0.8"/><float name="inv_period_y" value="0.8"/>'
+         '<boolean name="radial" value="true"/><integer name="lobes" value="7"/><float name="grating_angle" value="0"/>'
+         '<float name="multiplier" value="10"/><float name="alpha" value="0.01"/></bsdf></bsdf>\n',
+         '  <bsdf type="twosided" id="default-bsdf"><bsdf type="diffuse"/></bsdf>\n',
+         '  <bsdf type="twosided" id="mat-Material.005"><bsdf type="principled"><texture type="bitmap" name="base_color">'
+         '<string name="filename" value="textures/Material.005_baseColor.png"/></texture>' + pr + '</bsdf></bsdf>\n',
+         '  <bsdf type="twosided" id="mat-Material.009"><bsdf type="principled">'
+         '<rgb value="0.049707 0.049707 0.066626" name="base_color"/>' + pr + '</bsdf></bsdf>\n',
+         '  <emitter type="envmap" id="elm__7"><string name="filename" value="textures/empty_play_room.exr"/>'
+         '<float name="scale" value="1.000000"/>' + _xf([0, 0, 1, 0, 0, 1, 0, 0, -1, 0, 0, 0, 0, 0, 0, 1]) + '</emitter>\n',
+         _mesh("Circle.ply", "mat-Material.001", True), _mesh("Plane_001.ply", "default-bsdf", True),
+         _mesh("Object_4.ply", "mat-Material.005", False)]
+    x += [_mesh(f"{n}.ply", "mat-Material.009", False) for n in ("Object_6", "Object_8", "Object_10", "Object_12")]
+    x.append("</scene>\n")
+    path = os.path.join(directory, "scene.xml")
+    with open(path, "w") as f:
+        f.write("".join(x))
+    return path
+
+
 def _grating_diffract(wi, lobe, wl_um, inv_period, grating_angle=0.0):
     """DiffractionGrating::diffract (include/mitsuba/plt/diffractiongrating.h:201-226), non-radial grating, float64;
     only used to place the spectrograph's sensors."""
@@ -366,7 +478,7 @@ def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_
 
 _BUILDERS = {"cbox": lambda d, a=None: write_cbox(d, False, a), "cbox-grating": lambda d, a=None: write_cbox(d, True, a),
              "veach-mis": write_veach_mis, "spectrograph": write_spectrograph,
-             "gratingcap": write_gratingcap}
+             "gratingcap": write_gratingcap, "disk": write_disk}
 
 
 def scene_path(name, cache_dir=None):

@@ -18,6 +18,7 @@ CASES = [  # (scene, res, spp, seed)
     ("cbox:sky", 48, 8, 4),
     ("cbox-grating:envmap", 64, 8, 5),       # `envmap` emitter (EXR file, rotated): Hierarchical2D sampling, bilinear spectral lookup
     ("cbox:envmap", 48, 8, 6),
+    ("disk", 96, 8, 0),                      # scenes/disk equivalent: radial grating disc, textured metallic principled, envmap only
 ]
 
 

@@ -60,8 +60,10 @@ for cid, name, rx, ry, spp, note in CONFIGS:
                       "cpu_oracle_msamples_per_s": round(cpu_ms, 4), "cpu_oracle_mrays_per_s": round(cpu_mr, 4),
                       "cpu_cores": os.cpu_count(), "cpu_sample": f"spp indices [0,{n}) of {spp}, full frame"}), flush=True)
 
-if not only or "C5" in only:
-    sc = scenes.load("gratingcap", resx=800, resy=600)
+for c5_id, c5_scene in (("C5", "gratingcap"), ("C5d", "disk")):
+    if only and c5_id not in only:
+        continue
+    sc = scenes.load(c5_scene, resx=800, resy=600)
     animation.render_frames(sc, it, frames=240, spp=1, indices=list(range(8)))
     dev = []
     t0 = time.perf_counter()
@@ -71,7 +73,7 @@ if not only or "C5" in only:
     for i in range(4):
         oracle_lib.render(sc.flat, 1, seed=i)
     cpu = (time.perf_counter() - t1) / 4
-    print(json.dumps({"config": "C5", "workload": "scenes/gratingcap 800x600, 1 spp per frame x 240 frames, camera path of "
+    print(json.dumps({"config": c5_id, "workload": f"scenes/{c5_scene} 800x600, 1 spp per frame x 240 frames, camera path of "
                       "disk_animation.py", "frames_per_s": round(240 / wall, 1), "ms_per_frame_wall": round(1e3 * wall / 240, 3),
                       "ms_per_frame_device": round(float(np.mean(dev)), 3), "gpu_msamples_per_s": round(480000 * 240 / wall / 1e6, 2),
                       "cpu_oracle_ms_per_frame": round(cpu * 1e3, 2), "cpu_cores": os.cpu_count()}), flush=True)
