@@ -276,6 +276,10 @@ int pltb_cancel(pltb_context *ctx);
 /* Device-side helpers used by bench.py's roofline leg and by callers that keep the film on the GPU. */
 int pltb_film_device_ptr(pltb_context *ctx, float **accum_rgbw, uint64_t *n_floats);
 int pltb_synchronize(pltb_context *ctx);
+/* Page-locked host memory for `film_out` / dump buffers: the device-to-host copy of an image then runs at PCIe speed instead of
+ * through the driver's staging of pageable memory (the returned tensor of Integrator::render owns such a buffer). */
+int pltb_host_alloc(uint64_t bytes, void **out);
+void pltb_host_free(void *ptr);
 
 const char *pltb_last_error(void);
 int pltb_abi_version(void);

@@ -256,7 +256,7 @@ class PLTIntegrator:
             self.max_depth = capi.PLTB_MAX_DEPTH
         if self.rr_depth <= 0:
             raise RuntimeError('"rr_depth" must be set to a value greater than zero!')
-        self.last_stats = None
+        self._last_stats = None
         self._cancel_ctx = None
 
     def cancel(self):
@@ -322,6 +322,9 @@ class PLTIntegrator:
                 st = capi.Stats()
                 dst = out.ctypes.data if (last and out is not None and download) else None
                 capi.check(L.pltb_render(ctx._h, dev, C.byref(prm), dst, C.byref(dmp) if dmp else None, C.byref(st)))
+                if n_sub == 1:
+                    total = st          # the common case: no per-field accumulation on the host path of short renders
+                    continue
                 for f, _ in capi.Stats._fields_:
                     if f in ("ms_kernel", "launches_kernel"):
                         for j in range(16):
@@ -330,8 +333,13 @@ class PLTIntegrator:
                         setattr(total, f, getattr(total, f) + getattr(st, f))
         finally:
             self._cancel_ctx = None
-        self.last_stats = total.as_dict()
+        self._last_stats = total
         return out if download else None
+
+    @property
+    def last_stats(self):
+        """counters and device times of the last render() (pltb_stats as a dict; built on access)"""
+        return None if self._last_stats is None else self._last_stats.as_dict()
 
     def sample(self, *a, **kw):
         raise RuntimeError("PLTIntegrator.sample() is inlined into the CUDA wavefront kernels; use render()")

@@ -13,6 +13,7 @@ import math
 
 import numpy as np
 
+from . import capi
 from .xmlscene import Transform
 
 MOVE_VECTOR = (-2.7, 0.0, 2.1)   # disk_animation.py:114
@@ -46,14 +47,16 @@ def render_frames(scene, integrator, frames=240, spp=1, sensor_key=None, *, ctx=
     key = sensor_key or next(k for k in params if k.endswith(".to_world"))
     initial = params[key]
     out = {}
+    W, H = scene.film_size()
+    staging = capi.PinnedArray((H, W, 3))   # page-locked frame buffer: the per-frame image download runs at PCIe speed
     for i in (indices if indices is not None else frames_of_rank(frames, ctx.rank, ctx.world)):
         params[key] = camera_to_world(initial, i, frames, move_vector, max_rotation)
         params.update()
-        img = integrator.render(scene, spp=spp, seed=i, ctx=ctx, reduce=False)
+        img = integrator.render(scene, spp=spp, seed=i, ctx=ctx, reduce=False, out=staging.array)
         if on_frame is not None:
-            on_frame(i, img)
+            on_frame(i, img)        # valid until the next frame is rendered
         else:
-            out[i] = img
+            out[i] = img.copy()
     params[key] = initial
     params.update()
     return out

@@ -101,7 +101,7 @@ class Stats(C.Structure):
 
 
 EXPORTS = ["pltb_nccl_unique_id", "pltb_context_create", "pltb_context_destroy", "pltb_scene_create", "pltb_scene_update_sensor",
-           "pltb_scene_release", "pltb_render", "pltb_cancel", "pltb_film_device_ptr", "pltb_synchronize",
+           "pltb_scene_release", "pltb_render", "pltb_cancel", "pltb_film_device_ptr", "pltb_synchronize", "pltb_host_alloc", "pltb_host_free",
            "pltb_last_error", "pltb_abi_version"]
 
 _lib = None
@@ -128,6 +128,9 @@ def lib():
         L.pltb_cancel.argtypes = [vp]
         L.pltb_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
         L.pltb_synchronize.argtypes = [vp]
+        L.pltb_host_alloc.argtypes = [u64, C.POINTER(vp)]
+        L.pltb_host_free.argtypes = [vp]
+        L.pltb_host_free.restype = None
         L.pltb_last_error.restype = C.c_char_p
         L.pltb_abi_version.restype = C.c_int
         if L.pltb_abi_version() != PLTB_ABI_VERSION:
@@ -147,3 +150,23 @@ def fptr(a):
 
 def uptr(a):
     return a.ctypes.data_as(PU)
+
+
+class PinnedArray:
+    """float32 numpy array over page-locked host memory (pltb_host_alloc); freed with the object."""
+
+    def __init__(self, shape):
+        self.shape = tuple(int(x) for x in shape)
+        n = int(np.prod(self.shape))
+        self._ptr = C.c_void_p()
+        check(lib().pltb_host_alloc(4 * n, C.byref(self._ptr)))
+        self.array = np.ctypeslib.as_array(C.cast(self._ptr, C.POINTER(C.c_float)), shape=(n,)).reshape(self.shape)
+
+    def __del__(self):
+        try:
+            if self._ptr:
+                self.array = None
+                lib().pltb_host_free(self._ptr)
+                self._ptr = None
+        except Exception:
+            pass

@@ -232,6 +232,12 @@ void pltb_scene_release(pltb_scene *s) {
 }
 
 int pltb_cancel(pltb_context *c) { if (c) c->cancel.store(1); return 0; }
+int pltb_host_alloc(uint64_t bytes, void **out) {
+    if (!out || !bytes) return fail(PLTB_ERR_INVALID, "pltb_host_alloc: bad argument");
+    CU(cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+    return 0;
+}
+void pltb_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 int pltb_synchronize(pltb_context *c) { if (!c) return fail(PLTB_ERR_INVALID, "null context"); CU(cudaStreamSynchronize(c->stream)); return 0; }
 int pltb_film_device_ptr(pltb_context *c, float **accum, uint64_t *n) {
     if (!c) return fail(PLTB_ERR_INVALID, "null context");
