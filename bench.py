@@ -218,7 +218,7 @@ def run_ours(args):
         "materials, light and triangle counts as scenes/cbox-grating; fixed seed)",
         "config": {"workload": f"cbox-grating {args.res}x{args.res}, {args.spp} spp per step sharded over {world} GPU(s), "
                    "plt max_depth=7 rr_depth=50, gaussian rfilter", "samples_per_step": samples,
-                   "l2": "per-pass wavefront state (up to 2^23 samples x ~1.1 KB) exceeds L2; no explicit flush",
+                   "l2": "per-pass wavefront state (up to 2^25 samples x ~1.2 KB = 41 GB) exceeds L2; no explicit flush",
                    "timing": "CUDA events on the render stream inside pltb_render (pltb_stats.ms_total), max over ranks"},
         "mrays_per_s": round((closest + shadow) / (ms_step * 1e-3) / 1e6, 3),
         "rays_per_sample": round((closest + shadow) / samples, 4), "mean_depth": round(verts / samples, 4),

@@ -37,7 +37,7 @@ def test_c2_crop_at_full_sample_count(mi, oracle, integ):
 
 
 def test_c2_full_frame_linearity_and_accounting(mi, integ):
-    """1024x1024 x 32 spp (4 passes of 2^23 samples): film([0,32)) == film([0,12)) + film([12,32)) up to the order of the float
+    """1024x1024 x 32 spp (2^25 samples; 4 passes when PLTB_CHUNK_LOG2=23): film([0,32)) == film([0,12)) + film([12,32)) up to the order of the float
     atomics; Gaussian W channel identical in both; counters add up."""
     from mitsuba3_plt_b200 import capi, scenes
     sc = scenes.load("cbox-grating", resx=1024, resy=1024)
@@ -52,7 +52,7 @@ def test_c2_full_frame_linearity_and_accounting(mi, integ):
         return out, st.as_dict()
 
     full, st = window(0, 32)
-    assert st["samples"] == 1024 * 1024 * 32 and st["passes"] == 4 and st["closest_rays"] >= st["samples"]
+    assert st["samples"] == 1024 * 1024 * 32 and st["passes"] >= 1 and st["closest_rays"] >= st["samples"]
     a, sa = window(0, 12)
     b, sb = window(12, 20)
     for k in ("samples", "closest_rays", "shadow_rays", "vertices", "grating_vertices"):

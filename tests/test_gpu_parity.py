@@ -64,6 +64,30 @@ def test_environment_furnace(mi, oracle, integ):
     assert sample_agreement(dump["radiance"], ref["radiance"]) >= MIN_FRACTION
 
 
+def test_many_small_passes(mi, oracle, integ, monkeypatch):
+    """the wavefront pass loop with passes that straddle sample indices (2304 pixels, 4096-sample passes): per-sample results
+    and the film do not depend on the pass size"""
+    from mitsuba3_plt_b200 import scenes
+    sc = scenes.load("cbox-grating", resx=48, resy=48)
+    monkeypatch.setenv("PLTB_CHUNK_LOG2", "12")
+    ctx = mi.Context()          # fresh context: the pass size is fixed when the wavefront state is first allocated
+    try:
+        dump = {}
+        img = integ.render(sc, spp=16, seed=9, dump=dump, ctx=ctx)
+        assert integ.last_stats["passes"] == 9
+    finally:
+        sc.release()
+        ctx.close()
+    monkeypatch.delenv("PLTB_CHUNK_LOG2")
+    ref = oracle.render(sc.flat, 16, seed=9, dump=True)
+    assert sample_agreement(dump["radiance"], ref["radiance"]) >= MIN_FRACTION
+    rmse, mism = relative_mse(img, ref["image"])
+    assert rmse <= MAX_RMSE and mism <= max_finiteness_mismatch(48 * 48)
+    one = {}
+    integ.render(sc, spp=16, seed=9, dump=one)       # default context, one pass
+    np.testing.assert_array_equal(one["radiance"].view(np.uint32), dump["radiance"].view(np.uint32))
+
+
 def test_rr_and_depth_variants(mi, oracle):
     """plugin defaults max_depth/rr_depth (plt.py:37-38): Russian roulette active from depth 4"""
     from mitsuba3_plt_b200 import scenes
