@@ -10,17 +10,31 @@ import numpy as np
 import mitsuba3_plt_b200 as mi
 from mitsuba3_plt_b200 import animation, scenes
 
-frames, spp, rx, ry = (int(sys.argv[i]) if len(sys.argv) > i else d for i, d in ((1, 240), (2, 1), (3, 800), (4, 600)))
+args = [a for a in sys.argv[1:] if not a.startswith("--")]
+frames, spp, rx, ry = (int(args[i]) if len(args) > i else d for i, d in ((0, 240), (1, 1), (2, 800), (3, 600)))
+dist_mode = "--dist" in sys.argv    # under torchrun: frames dealt round-robin to the ranks, no collective on the data path
+ctx = mi.init_distributed() if dist_mode else mi.context()
 sc = scenes.load("gratingcap", resx=rx, resy=ry)
 it = mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
-animation.render_frames(sc, it, frames=frames, spp=spp, indices=list(range(8)))   # warm-up
+animation.render_frames(sc, it, frames=frames, spp=spp, indices=list(range(8)), ctx=ctx)   # warm-up
 dev_ms, launches = [], []
 def keep(i, img):
     dev_ms.append(it.last_stats["ms_total"]); launches.append(it.last_stats["kernel_launches"])
+if dist_mode:
+    import torch, torch.distributed as dist
+    dist.barrier(); torch.cuda.synchronize()
 t0 = time.perf_counter()
-animation.render_frames(sc, it, frames=frames, spp=spp, on_frame=keep)
+animation.render_frames(sc, it, frames=frames, spp=spp, on_frame=keep, ctx=ctx)
 dt = time.perf_counter() - t0
-print(json.dumps({"workload": f"gratingcap {rx}x{ry}, {spp} spp/frame x {frames} frames", "frames_per_s": frames / dt,
+if dist_mode:
+    t = torch.tensor([dt, float(len(dev_ms))], dtype=torch.float64, device="cuda")
+    tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    tsum = t.clone(); dist.all_reduce(tsum)
+    dt = tmax[0].item()
+    assert int(tsum[1].item()) == frames, "every frame rendered exactly once across the ranks"
+    if ctx.rank != 0:
+        sys.exit(0)
+print(json.dumps({"workload": f"gratingcap {rx}x{ry}, {spp} spp/frame x {frames} frames", "ranks": ctx.world, "frames_per_s": frames / dt,
                   "ms_per_frame_wall": 1e3 * dt / frames, "ms_per_frame_device": float(np.mean(dev_ms)),
                   "kernel_launches_per_frame": float(np.mean(launches)),
                   "Msamples_per_s_wall": rx * ry * spp * frames / dt / 1e6}))
