@@ -252,6 +252,18 @@ def test_image_files(mi, tmp_path):
         mi.util.write_bitmap(str(tmp_path / "r.tiff"), img)
 
 
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree only exists in the build container")
+def test_piz_exr_written_by_mitsuba(mi):
+    """the reference's own output files are PIZ-compressed float32 EXRs (Bitmap::write default): Huffman + wavelet + LUT decode"""
+    from mitsuba3_plt_b200 import imageio
+    img, names = imageio.read_exr(f"{REF}/results/cbox-plt/result.exr")
+    assert img.shape == (500, 500, 3) and names == ["R", "G", "B"] and np.isfinite(img).all()
+    light = img[50:70, 220:280].reshape(-1, 3)          # the area light: a flat region, identical texels up to noise
+    assert light.std(axis=0).max() < 0.05 and abs(light.mean(axis=0)[1] - light.mean(axis=0)[2]) < 0.01
+    assert img[:, :70, 0].mean() > 2 * img[:, :70, 1].mean()      # red wall on the left, green wall on the right
+    assert img[:, 430:, 1].mean() > 1.3 * img[:, 430:, 0].mean()
+
+
 def test_ply_round_trip(tmp_path):
     from mitsuba3_plt_b200 import scenes
     from mitsuba3_plt_b200.scene import load_ply

@@ -1,0 +1,42 @@
+#!/usr/bin/env python
+"""Integrator-level cross-check against the reference's OWN published render (container only: needs /root/reference).
+
+results/cbox-plt/result.exr is the reference's render of scenes/cbox/cbox.xml with `stokes{plt}` (polarized CUDA variant, 500x500,
+1024 spp, `main-headless.py`).  This renders the same scene file with the CPU oracle (unpolarized spectral restatement) and reports
+image-level agreement.  The two differ by construction in the polarization state carried along specular chains, by Monte-Carlo noise
+(the oracle uses fewer spp) and by the RGB vs spectral colour pipeline of the variant the authors used, so this is a sanity bound
+on integrator-level behaviour (geometry, light transport, film), not a bit-level pin.
+usage: python tools/compare_reference_image.py [spp] [ref=/root/reference]"""
+import json, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import mitsuba3_plt_b200 as mi
+from mitsuba3_plt_b200 import imageio
+import oracle_lib
+
+spp = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+ref = sys.argv[2] if len(sys.argv) > 2 else "/root/reference"
+want, _ = imageio.read_exr(f"{ref}/results/cbox-plt/result.exr")
+params = json.load(open(f"{ref}/results/cbox-plt/params.json"))
+sc = mi.load_file(f"{ref}/scenes/cbox/cbox.xml", resx=want.shape[1], resy=want.shape[0])
+r = oracle_lib.render(sc.flat, spp, seed=0, max_depth=7, rr_depth=50)
+img = r["image"]
+
+
+def box(a, k=8):   # k x k box filter: compares the signal, not the per-pixel noise of the lower-spp image
+    H, W = a.shape[0] // k * k, a.shape[1] // k * k
+    return a[:H, :W].reshape(H // k, k, W // k, k, 3).mean(axis=(1, 3))
+
+
+a, b = box(img), box(want)
+rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-2)))
+out = {"reference_image": "results/cbox-plt/result.exr", "reference_params": params, "oracle_spp": spp,
+       "oracle_seconds": r["seconds"], "mean_rgb_oracle": [float(x) for x in img.mean(axis=(0, 1))],
+       "mean_rgb_reference": [float(x) for x in want.mean(axis=(0, 1))],
+       "mean_ratio": [float(x) for x in img.mean(axis=(0, 1)) / want.mean(axis=(0, 1))],
+       "relative_mse_8x8_blocks": rel_mse,
+       "per_pixel_relative_mse": float(np.mean((img - want) ** 2 / (want ** 2 + 1e-2)))}
+print(json.dumps(out))
+if len(sys.argv) > 3:
+    imageio.write_bitmap(sys.argv[3], np.concatenate([img, want], axis=1))
