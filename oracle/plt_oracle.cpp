@@ -2215,6 +2215,10 @@ void plt_oracle_envmap_probe(const pltb_scene_desc *d, const float *u, const flo
     out[3] = envmap_eval_spectrum(sc, em, uv, wl)[0];
     out[4] = dw.x; out[5] = dw.y; out[6] = dw.z;
 }
+float plt_oracle_rfilter_eval(uint32_t type, float radius, float stddev, float x) {
+    pltb_film f{}; f.rfilter = type; f.radius = radius; f.stddev = stddev;
+    return rfilter_eval(f, x);
+}
 float plt_oracle_hier2d_eval(const float *block, const float *pos) { return Hier2D(block).eval(V2{ pos[0], pos[1] }); }
 
 } // extern "C"
