@@ -208,9 +208,15 @@ def run_ours(args):
     ach = alg[top] / (top_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")   # dram bytes per launch from the committed ncu --set full capture
+    traffic_note = None
     if os.path.exists(tpath):
-        t = json.load(open(tpath)).get(top)
-        traffic = t["dram_bytes_per_launch"] if t else None
+        tj = json.load(open(tpath))
+        t = tj.get(top)
+        if t:   # the capture is one pass of 2^23 samples (ncu replays every launch ~40x); a bench launch covers a larger pass
+            scale = (pst["samples"] / max(1, pst["passes"])) / tj.get("_samples_per_pass_in_capture", 1 << 23)
+            traffic = round(t["dram_bytes_per_launch"] * scale)
+            traffic_note = (f"dram__bytes_read+write per launch from profiles/ncu_traffic.json ({t['dram_bytes_per_launch']} B at "
+                            f"{tj.get('_samples_per_pass_in_capture', 1 << 23)} samples per pass) scaled by {scale:.2f} to this run's pass size")
     out = {
         "metric": METRIC, "value": round(value, 3), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "strong",
@@ -234,7 +240,7 @@ def run_ours(args):
         "kernels": {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
                         "algorithmic_GB_per_s": round(alg[k] / max(v["ms"], 1e-6) / 1e6, 1)} for k, v in per_kernel.items()},
         "roofline": {"kernel": top, "bound": "hbm", "achieved": round(ach, 2), "peak": peak, "unit": "GB/s",
-                     "frac": round(ach / peak, 4), "traffic": traffic, "launches_per_step": n_launch,
+                     "frac": round(ach / peak, 4), "traffic": traffic, "traffic_note": traffic_note, "launches_per_step": n_launch,
                      "avg_launch_ms": round(top_ms / n_launch, 4), "algorithmic_bytes_per_launch": round(alg[top] / n_launch),
                      "share_of_step": round(top_ms / sum(v["ms"] for v in per_kernel.values()), 4),
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (sustained copy)" if peaks else "fallback 6650 GB/s",

@@ -64,6 +64,7 @@ def main():
     print("\n".join(lines))
     if len(sys.argv) > 3:
         traffic["_source"] = f"ncu --set full --clock-control none, one pass of cbox-grating 1024x1024 x 8 spp ({src})"
+        traffic["_samples_per_pass_in_capture"] = int(sys.argv[4]) if len(sys.argv) > 4 else 1024 * 1024 * 8
         json.dump(traffic, open(sys.argv[3], "w"), indent=1)
 
 
