@@ -14,6 +14,11 @@ PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, 
     return F;
 }
 
+// (Measured and rejected: pooling the zero-to-two precise Bessel evaluations per lane of RoughGrating::wbsdf_sample across the
+// warp -- ballots to number the (a, order) requests, one nearly full round of bessel_j, shuffles to hand the squares back --
+// gave bit-identical results but k_shade<grating> went from 133 to 159 ms per 2^30 samples: the bookkeeping and the fragmented
+// __activemask() groups cost more than the half-empty rounds they replace.)
+
 // wi already has the twosided flip applied.
 PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl,
                                         float s1, V2 s2, V2 lobe_s2) {

@@ -67,6 +67,9 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
 // DRAM round trip of a refill is already covered by the other 20+ resident warps, while the extra per-round bookkeeping and
 // the loss of globally consecutive ray batches are not.)
 // Shadow = true: the same loop over the NEE shadow-ray list (any-hit; an occluded vertex gets ds.pdf = 0 in its record).
+#ifndef PLTB_TRACE_INNER
+#define PLTB_TRACE_INNER 6   // inner-node steps per round before the leaf step
+#endif
 template <bool Shadow>
 __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
@@ -108,7 +111,7 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
         }
         if (__ballot_sync(0xffffffffu, active) == 0) break;
 #pragma unroll 1
-        for (int k = 0; k < 6; ++k)
+        for (int k = 0; k < PLTB_TRACE_INNER; ++k)
             if (active && !tr.done && tr.node >= 0) tr.inner_step(sc);
         if (active && !tr.done && tr.node < 0) tr.template leaf_step<Shadow>(sc);
         if (active && tr.done) {
