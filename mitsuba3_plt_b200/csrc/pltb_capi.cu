@@ -373,7 +373,14 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     pp.seed = prm->seed; pp.spp = prm->spp; pp.spp_begin = prm->spp_begin; pp.spp_count = prm->spp_count;
     pp.crop_x = prm->crop_x; pp.crop_y = prm->crop_y; pp.crop_w = cw; pp.crop_h = ch;
     pp.film_w = W; pp.film_h = H; pp.n_pix = cw * ch;
-    const int nee_grid = c->sm_count * 8, wf_grid = c->sm_count * 8;
+    // grid of the grid-stride / persistent-warp kernels: up to grid_mult blocks of 128 threads per SM so that the tail of a launch
+    // is short (cbox-grating 1024 spp: x4 1531, x8 1660, x16 1691, x32 1712, x64 1728, x128 1713 Msamples/s), but no more blocks than a pass of this
+    // size can feed -- short renders (config 5: 4.8e5 samples per frame) pay for every block they launch
+    static const int grid_mult = getenv("PLTB_GRID_MULT") ? std::max(1, atoi(getenv("PLTB_GRID_MULT"))) : 64;
+    const uint64_t pass_samples = std::min<uint64_t>(total, st.chunk);
+    const int wf_grid = (int) std::min<uint64_t>((uint64_t) c->sm_count * grid_mult,
+                                                 std::max<uint64_t>(c->sm_count, (pass_samples + 511) / 512));
+    const int nee_grid = wf_grid;
     const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
     for (uint64_t first = 0; first < total; first += st.chunk) {
         if (c->cancel.load()) { cudaStreamSynchronize(s); return fail(PLTB_ERR_CANCELLED, "render cancelled"); }

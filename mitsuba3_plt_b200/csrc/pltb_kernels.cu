@@ -242,7 +242,10 @@ __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceSce
 // strip pixel: 180 instead of 6400 film atomics per 256 samples for the 5x5 Gaussian.  Lanes whose position does not floor
 // to their own pixel (x + u rounding up to x + 1 in float32), or whose pixel sits on another row than lane 0's (window width
 // not a multiple of 32), take the per-tap global path.
-constexpr int kSplatWarps = 4, kSplatS = 8;
+#ifndef PLTB_SPLAT_S
+#define PLTB_SPLAT_S 32   // sample indices per warp (8: 49.2, 16: 46.1, 32: 45.0 ms of k_splat per 2^30 samples at 32 spp per pass)
+#endif
+constexpr int kSplatWarps = 4, kSplatS = PLTB_SPLAT_S;
 template <int NR>
 __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_constant__ DeviceScene sc,
                                                                   const __grid_constant__ PassState st,
