@@ -173,11 +173,58 @@ __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ Devic
     flush_counters(cnt, st.counters);
 }
 
+// Class 1 (roughgrating): only the lit, well-formed items (about a third on cbox-grating) run the lobe-window scan, so with one item
+// per thread the scan runs at ~10 of 32 lanes.  PLTB_NEEPOST_REBALANCE: the block lists those items in shared memory and its first
+// threads scan them densely; every thread then picks up the answer for its own item (queue order and results unchanged).
+#ifndef PLTB_NEEPOST_MINB
+#define PLTB_NEEPOST_MINB 1
+#endif
+struct ScanItem { const pltb_bsdf *b; float wi[3], wo[3], uv[2], wl[4]; };
+struct GratingInsideBlock {
+    ScanItem *items; uint32_t *n_items; uint8_t *flag;
+    __device__ bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
+        if (threadIdx.x == 0) *n_items = 0;
+        __syncthreads();
+        uint32_t slot = 0;
+        if (want) {
+            slot = atomicAdd(n_items, 1u);
+            ScanItem &it = items[slot];
+            it.b = b; it.wi[0] = wi_f.x; it.wi[1] = wi_f.y; it.wi[2] = wi_f.z; it.wo[0] = wo_f.x; it.wo[1] = wo_f.y; it.wo[2] = wo_f.z;
+            it.uv[0] = uv.x; it.uv[1] = uv.y;
+            for (int i = 0; i < 4; ++i) it.wl[i] = wl.v[i];
+        }
+        __syncthreads();
+        if (threadIdx.x < *n_items) {
+            const ScanItem &it = items[threadIdx.x];
+            S4 w; for (int i = 0; i < 4; ++i) w.v[i] = it.wl[i];
+            flag[threadIdx.x] = GratingInsideDirect()(true, it.b, mk3(it.wi[0], it.wi[1], it.wi[2]), mk3(it.wo[0], it.wo[1], it.wo[2]),
+                                                      mk2(it.uv[0], it.uv[1]), w);
+        }
+        __syncthreads();
+        return want && flag[slot];
+    }
+};
+
 template <int Class>
-__global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+__global__ void __launch_bounds__(128, PLTB_NEEPOST_MINB) k_nee_post(const __grid_constant__ DeviceScene sc,
+                                                                      const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[kCountsNee + Class];
     const uint32_t *queue = st.queue[Class];
     DevPush push;
+#ifdef PLTB_NEEPOST_REBALANCE
+    if (Class == 1) {
+        __shared__ ScanItem items[128];
+        __shared__ uint32_t n_items;
+        __shared__ uint8_t flag[128];
+        GratingInsideBlock inside{ items, &n_items, flag };
+        for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
+            const uint32_t e = base + threadIdx.x;
+            const bool valid = e < n;
+            stage_nee_post<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
+        }
+        return;
+    }
+#endif
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_nee_post<Class>(sc, st, queue[e], push);
 }

@@ -280,8 +280,23 @@ PLTB_HD Ray nee_shadow_ray(const PassState &st, size_t r) {
     return si.spawn_ray_to(mk3(w4.x, w4.y, w4.z));
 }
 
-template <int Class, class Push>
-PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
+// does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<1>; k_nee_post can
+// substitute a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
+struct GratingInsideDirect {
+    PLTB_HD bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
+        if (!want) return false;
+        GratingLoop gl; gl.init(*b, wi_f, uv, wl, wo_f);
+        GratingHits h; grating_scan(gl, wo_f, h);
+        return h.n > 0;
+    }
+};
+
+template <int Class, class Push, class Inside>
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
+    if (!valid) {   // tail thread of a block-uniform loop: only takes part in the functor's barriers
+        if (Class == 1) inside_fn(false, nullptr, mk3(0.f, 0.f, 1.f), mk3(0.f, 0.f, 1.f), mk2(0.f, 0.f), s4(0.f));
+        return;
+    }
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
     const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
@@ -313,14 +328,9 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         const float fsum = wi_f.x + wi_f.y + wi_f.z + wo_f.x + wo_f.y + wo_f.z + a.v[0] + a.v[1] + a.v[2] + a.v[3] +
                            em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
         const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
+        const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
+        const bool inside = inside_fn(sane && lit, b, wi_f, wo_f, si.uv, wl);
         if (sane) {
-            const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
-            bool inside = false;
-            if (lit) {
-                GratingLoop gl; gl.init(*b, wi_f, si.uv, wl, wo_f);
-                GratingHits h; grating_scan(gl, wo_f, h);
-                inside = h.n > 0;
-            }
             if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
             float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
@@ -334,6 +344,11 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
     float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
+}
+
+template <int Class, class Push>
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
+    stage_nee_post<Class>(sc, st, entry, true, push, GratingInsideDirect());
 }
 
 // second half of solve_replay_NEE for the roughgrating vertices whose light direction falls inside a lobe window
