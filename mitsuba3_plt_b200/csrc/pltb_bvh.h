@@ -41,7 +41,10 @@ struct Builder {
     std::vector<Box> boxes;        // per prims index (by primitive id slot)
     std::vector<float> cent;       // 3 per slot
     HostBVH *out;
-    static constexpr int kBins = 16, kLeaf = 4;
+#ifndef PLTB_BVH_LEAF
+#define PLTB_BVH_LEAF 4   // primitives per leaf at which splitting stops
+#endif
+    static constexpr int kBins = 16, kLeaf = PLTB_BVH_LEAF;
 
     int32_t make_leaf(uint32_t first, uint32_t count) {
         uint32_t base = out->n_prims;

@@ -176,9 +176,7 @@ __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ Devic
 // Class 1 (roughgrating): only the lit, well-formed items (about a third on cbox-grating) run the lobe-window scan, so with one item
 // per thread the scan runs at ~10 of 32 lanes.  PLTB_NEEPOST_REBALANCE: the block lists those items in shared memory and its first
 // threads scan them densely; every thread then picks up the answer for its own item (queue order and results unchanged).
-#ifndef PLTB_NEEPOST_MINB
-#define PLTB_NEEPOST_MINB 1
-#endif
+#ifdef PLTB_NEEPOST_REBALANCE
 struct ScanItem { const pltb_bsdf *b; float wi[3], wo[3], uv[2], wl[4]; };
 struct GratingInsideBlock {
     ScanItem *items; uint32_t *n_items; uint8_t *flag;
@@ -204,9 +202,10 @@ struct GratingInsideBlock {
         return want && flag[slot];
     }
 };
+#endif
 
 template <int Class>
-__global__ void __launch_bounds__(128, PLTB_NEEPOST_MINB) k_nee_post(const __grid_constant__ DeviceScene sc,
+__global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc,
                                                                       const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[kCountsNee + Class];
     const uint32_t *queue = st.queue[Class];
@@ -220,7 +219,7 @@ __global__ void __launch_bounds__(128, PLTB_NEEPOST_MINB) k_nee_post(const __gri
         for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
             const uint32_t e = base + threadIdx.x;
             const bool valid = e < n;
-            stage_nee_post<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
+            stage_nee_post_rb<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
         }
         return;
     }

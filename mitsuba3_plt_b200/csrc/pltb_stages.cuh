@@ -280,23 +280,8 @@ PLTB_HD Ray nee_shadow_ray(const PassState &st, size_t r) {
     return si.spawn_ray_to(mk3(w4.x, w4.y, w4.z));
 }
 
-// does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<1>; k_nee_post can
-// substitute a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
-struct GratingInsideDirect {
-    PLTB_HD bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
-        if (!want) return false;
-        GratingLoop gl; gl.init(*b, wi_f, uv, wl, wo_f);
-        GratingHits h; grating_scan(gl, wo_f, h);
-        return h.n > 0;
-    }
-};
-
-template <int Class, class Push, class Inside>
-PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
-    if (!valid) {   // tail thread of a block-uniform loop: only takes part in the functor's barriers
-        if (Class == 1) inside_fn(false, nullptr, mk3(0.f, 0.f, 1.f), mk3(0.f, 0.f, 1.f), mk2(0.f, 0.f), s4(0.f));
-        return;
-    }
+template <int Class, class Push>
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
     const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
@@ -328,9 +313,14 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         const float fsum = wi_f.x + wi_f.y + wi_f.z + wo_f.x + wo_f.y + wo_f.z + a.v[0] + a.v[1] + a.v[2] + a.v[3] +
                            em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
         const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
-        const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
-        const bool inside = inside_fn(sane && lit, b, wi_f, wo_f, si.uv, wl);
         if (sane) {
+            const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
+            bool inside = false;
+            if (lit) {
+                GratingLoop gl; gl.init(*b, wi_f, si.uv, wl, wo_f);
+                GratingHits h; grating_scan(gl, wo_f, h);
+                inside = h.n > 0;
+            }
             if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
             float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
@@ -346,10 +336,80 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
 }
 
-template <int Class, class Push>
-PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
-    stage_nee_post<Class>(sc, st, entry, true, push, GratingInsideDirect());
+#ifdef PLTB_NEEPOST_REBALANCE
+// Experimental form of stage_nee_post for the block-rebalanced lobe scan of k_nee_post<1> (same arithmetic on the same inputs).
+// does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<1>; k_nee_post can
+// substitute a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
+struct GratingInsideDirect {
+    PLTB_HD bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
+        if (!want) return false;
+        GratingLoop gl; gl.init(*b, wi_f, uv, wl, wo_f);
+        GratingHits h; grating_scan(gl, wo_f, h);
+        return h.n > 0;
+    }
+};
+
+template <int Class, class Push, class Inside>
+PLTB_HD void stage_nee_post_rb(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
+    // `valid` is false for the tail threads of a block-uniform loop: they load nothing and only take part in the barriers a
+    // block-level `inside_fn` may contain, which is why that call sits at one program point that every thread reaches.
+    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = (size_t) depth * st.chunk + local;
+    SI si;
+    si.t = 0.f; si.uv = mk2(0.f, 0.f); si.wi = mk3(0.f, 0.f, 1.f);
+    S4 wl = s4(0.f), em_weight = s4(0.f), a = s4(0.f);
+    DirectionSample ds;
+    ds.delta = false; ds.pdf = 0.f;
+    V3 wo = mk3(0.f, 0.f, 1.f);
+    const pltb_bsdf *b = nullptr;
+    if (valid) {
+        const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
+        const float2 ws = st.v_wiz_shape[r];
+        si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z); si.uv = mk2(a0.w, a1.w);
+        si.sh.s = mk3(a2.x, a2.y, a2.z); si.sh.n = mk3(a3.x, a3.y, a3.z); si.sh.t = cross(si.sh.n, si.sh.s);
+        si.wi = mk3(a2.w, a3.w, ws.x);
+        si.shape = (int32_t) f2u(ws.y);
+        wl = f4_to_s4(st.wl[local]);
+        ds.p = mk3(w4.x, w4.y, w4.z);
+        ds.delta = signbit_(w4.w);
+        ds.pdf = fabsf(w4.w);            // 0 when the shadow ray was occluded
+        ds.d = normalize(ds.p - si.p);
+        em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_nee[r]) : s4(0.f);
+        wo = si.sh.to_local(ds.d);
+        b = si_bsdf(sc, si.shape);
+        a = f4_to_s4(st.v_alpha[r]);
+    }
+    if (Class == 1) {
+        // RoughGrating::wbsdf_eval is only non-zero inside the few-degree windows around the diffraction lobes: 9 % of the NEE
+        // directions on cbox-grating, 6 % once unlit samples are excluded.  For well-formed inputs (finite, unit wi / wo,
+        // finite throughput: then every factor of the product is finite) an unlit sample or one outside every window
+        // contributes exactly 0, as in the reference; the rest is compacted into `queue_eval` so that the Bessel terms are
+        // evaluated by dense warps (k_nee_eval).  Anything else takes the generic path below.
+        V3 wi_f = si.wi, wo_f = wo;
+        if (valid) twosided_flip(b, wi_f, wo_f);
+        const float fsum = wi_f.x + wi_f.y + wi_f.z + wo_f.x + wo_f.y + wo_f.z + a.v[0] + a.v[1] + a.v[2] + a.v[3] +
+                           em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
+        const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
+        const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
+        const bool inside = inside_fn(valid && sane && lit, b, wi_f, wo_f, si.uv, wl);
+        if (!valid) return;
+        if (sane) {
+            if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
+            float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
+            float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
+            st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
+            st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);
+            push(st.queue_eval, st.counts + kCountsNee + 2, entry);
+            return;
+        }
+    }
+    if (!valid) return;
+    S4 bsdf_val = wbsdf_eval<Class>(sc, b, si.wi, si.uv, wl, wo);
+    float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
+    float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
+    st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
 }
+#endif
 
 // second half of solve_replay_NEE for the roughgrating vertices whose light direction falls inside a lobe window
 PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t entry) {
