@@ -174,9 +174,13 @@ __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ Devic
 }
 
 // Class 1 (roughgrating): only the lit, well-formed items (about a third on cbox-grating) run the lobe-window scan, so with one item
-// per thread the scan runs at ~10 of 32 lanes.  PLTB_NEEPOST_REBALANCE: the block lists those items in shared memory and its first
-// threads scan them densely; every thread then picks up the answer for its own item (queue order and results unchanged).
-#ifdef PLTB_NEEPOST_REBALANCE
+// per thread the scan runs at ~10 of 32 lanes.  The block therefore lists those items in shared memory and its first threads scan
+// them densely; every thread then picks up the answer for its own item (queue order and results unchanged; same function on the
+// same inputs, only on another thread).  Measured on cbox-grating 1024 spp: k_nee_post<grating> 53.6 -> 48.6 ms per 2^30 samples,
+// 1724 -> 1738 Msamples/s (gpurun_out/ab4.log, summarised in profiles/r01_ab_neepost_bvhleaf.txt).  -DPLTB_NEEPOST_DIRECT
+// restores the one-item-per-thread form.  The barriers inside the functor need a block-uniform loop and ONE call site that
+// every thread reaches (a first version that called it from two branches deadlocked on the tail block).
+#ifndef PLTB_NEEPOST_DIRECT
 struct ScanItem { const pltb_bsdf *b; float wi[3], wo[3], uv[2], wl[4]; };
 struct GratingInsideBlock {
     ScanItem *items; uint32_t *n_items; uint8_t *flag;
@@ -210,7 +214,7 @@ __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ Device
     const uint32_t n = st.counts[kCountsNee + Class];
     const uint32_t *queue = st.queue[Class];
     DevPush push;
-#ifdef PLTB_NEEPOST_REBALANCE
+#ifndef PLTB_NEEPOST_DIRECT
     if (Class == 1) {
         __shared__ ScanItem items[128];
         __shared__ uint32_t n_items;

@@ -336,8 +336,8 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
 }
 
-#ifdef PLTB_NEEPOST_REBALANCE
-// Experimental form of stage_nee_post for the block-rebalanced lobe scan of k_nee_post<1> (same arithmetic on the same inputs).
+#ifndef PLTB_NEEPOST_DIRECT
+// Form of stage_nee_post used by the block-rebalanced lobe scan of k_nee_post<1> (same arithmetic on the same inputs).
 // does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<1>; k_nee_post can
 // substitute a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
 struct GratingInsideDirect {
