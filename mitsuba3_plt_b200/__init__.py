@@ -266,7 +266,7 @@ class PLTIntegrator:
     def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, *, ctx=None, dump=None, crop=None,
                reduce=True, profile=False, download=True, out=None):
         """Returns the developed image (H, W, 3) float32, or the raw RGBW accumulator (H, W, 4) if develop=False.
-        `dump`: optional dict that receives per-sample 'wavelengths' and 'radiance' arrays (parity mode).
+        `dump`: optional dict that receives per-sample 'wavelengths', 'radiance' and 'n_rays' arrays (parity mode).
         Multi-GPU: the spp range is sharded over the ranks of `ctx`; rank 0 returns the image, the others None."""
         if not isinstance(scene, Scene):
             raise TypeError("render(): expected a Scene")
@@ -318,7 +318,8 @@ class PLTIntegrator:
                     n = cw * ch * prm.spp_count
                     dump["wavelengths"] = np.zeros((n, 4), np.float32)
                     dump["radiance"] = np.zeros((n, 4), np.float32)
-                    dmp = capi.SampleDump(capi.fptr(dump["wavelengths"]), capi.fptr(dump["radiance"]), None, n)
+                    dump["n_rays"] = np.zeros((n, 2), np.uint32)     # closest-hit rays, shadow rays per sample
+                    dmp = capi.SampleDump(capi.fptr(dump["wavelengths"]), capi.fptr(dump["radiance"]), capi.uptr(dump["n_rays"]), n)
                 st = capi.Stats()
                 dst = out.ctypes.data if (last and out is not None and download) else None
                 capi.check(L.pltb_render(ctx._h, dev, C.byref(prm), dst, C.byref(dmp) if dmp else None, C.byref(st)))

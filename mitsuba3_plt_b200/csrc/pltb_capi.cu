@@ -65,7 +65,8 @@ struct pltb_context {
     uint32_t st_chunk = 0, st_depth = 0;
     std::vector<void *> st_allocs;
     unsigned long long *counters = nullptr;
-    float *dump_wl = nullptr, *dump_L = nullptr; uint64_t dump_cap = 0;
+    float *dump_wl = nullptr, *dump_L = nullptr; uint32_t *dump_rays = nullptr; uint64_t dump_cap = 0;
+    uint32_t *n_shadow = nullptr; uint32_t n_shadow_cap = 0;   // per-sample shadow-ray counts (only for pltb_sample_dump.n_rays)
     int sm_count = 148;
     cudaEvent_t ev[2] = { nullptr, nullptr };
     std::vector<cudaEvent_t> prof;   // PLTB_RENDER_PROFILE: 5 events per pass + 4 for the tail
@@ -143,6 +144,7 @@ void pltb_context_destroy(pltb_context *c) {
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     free_state(c);
     cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
+    cudaFree(c->dump_rays); cudaFree(c->n_shadow);
     cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
     for (cudaEvent_t e : c->prof) cudaEventDestroy(e);
     for (cudaEvent_t e : c->kprof) cudaEventDestroy(e);
@@ -335,16 +337,27 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (int rc = ensure_state(c, chunk, prm->max_depth)) return rc;
     PassState st = c->st;
     st.chunk = c->st_chunk; st.max_depth = prm->max_depth; st.rr_depth = prm->rr_depth;
-    float *d_wl = nullptr, *d_L = nullptr; uint64_t dcap = 0;
-    if (dump && (dump->wavelengths || dump->radiance)) {
+    float *d_wl = nullptr, *d_L = nullptr; uint32_t *d_rays = nullptr; uint64_t dcap = 0;
+    st.n_shadow = nullptr;
+    if (dump && (dump->wavelengths || dump->radiance || dump->n_rays)) {
         dcap = std::min<uint64_t>(dump->capacity, total);
         if (c->dump_cap < dcap) {
-            cudaFree(c->dump_wl); cudaFree(c->dump_L); c->dump_wl = c->dump_L = nullptr; c->dump_cap = 0;
+            cudaFree(c->dump_wl); cudaFree(c->dump_L); cudaFree(c->dump_rays);
+            c->dump_wl = c->dump_L = nullptr; c->dump_rays = nullptr; c->dump_cap = 0;
             CU(cudaMalloc(&c->dump_wl, dcap * 4 * sizeof(float)));
             CU(cudaMalloc(&c->dump_L, dcap * 4 * sizeof(float)));
+            CU(cudaMalloc(&c->dump_rays, dcap * 2 * sizeof(uint32_t)));
             c->dump_cap = dcap;
         }
         d_wl = c->dump_wl; d_L = c->dump_L;
+        if (dump->n_rays) {
+            if (c->n_shadow_cap < st.chunk) {
+                cudaFree(c->n_shadow); c->n_shadow = nullptr; c->n_shadow_cap = 0;
+                CU(cudaMalloc(&c->n_shadow, (size_t) st.chunk * sizeof(uint32_t)));
+                c->n_shadow_cap = st.chunk;
+            }
+            st.n_shadow = c->n_shadow; d_rays = c->dump_rays;
+        }
     }
     uint64_t launches = 0;
     const bool profile = (prm->flags & PLTB_RENDER_PROFILE) != 0;
@@ -403,7 +416,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         PROF();
         launch_nee_post(scene->dev, st, 1, nee_grid, s);
         PROF();
-        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, dcap, s);
+        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, dcap, s);
         PROF();
         launches += do_splat ? 9 : 8;   // raygen, 3 x nee_light, 3 x nee_post, gather (+ splat)
     }
@@ -436,6 +449,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (dcap) {
         if (dump->wavelengths) CU(cudaMemcpyAsync(dump->wavelengths, d_wl, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
         if (dump->radiance) CU(cudaMemcpyAsync(dump->radiance, d_L, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
+        if (dump->n_rays) CU(cudaMemcpyAsync(dump->n_rays, d_rays, dcap * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
     }
     if (!(film_out && root)) PROF();
     PROF();   // tail event 3: after the copies

@@ -224,7 +224,8 @@ struct PassState {
     float4 *sensor_w;          // sensor spectral weight
     float2 *film_pos;          // splat position
     uint64_t *rng_state, *rng_inc;   // PCG32 state (advanced bounce by bounce; NEE draws continue from the final state)
-    uint32_t *n_vertices;      // bounce records written
+    uint32_t *n_vertices;      // bounce records written (== closest-hit rays traced: one per loop iteration)
+    uint32_t *n_shadow;        // shadow rays traced per sample; nullptr unless the caller asked for pltb_sample_dump.n_rays
     // per path, carried from bounce to bounce
     float4 *p_ray_o;           // {ray.o, ray.maxt}
     float4 *p_ray_d;           // {ray.d, eta}

@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ Device
 // round trip apart (depth-major arrays), so the loads are issued four vertices at a time before the ordered sum consumes them.
 // The sum L is left in p_ray_o (dead after the last k_trace) for the splat kernels; optional per-sample dump.
 __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassState st, const __grid_constant__ PassParams pp,
-                                                float *dump_wl, float *dump_L, uint64_t dump_cap) {
+                                                float *dump_wl, float *dump_L, uint32_t *dump_rays, uint64_t dump_cap) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= pp.count) return;
     const uint32_t n = st.n_vertices[local];
@@ -268,6 +268,7 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassStat
         if (di < dump_cap) {
             if (dump_L) reinterpret_cast<float4 *>(dump_L)[di] = s4_to_f4(L);
             if (dump_wl) reinterpret_cast<float4 *>(dump_wl)[di] = st.wl[local];
+            if (dump_rays) { dump_rays[2 * di] = n; dump_rays[2 * di + 1] = st.n_shadow[local]; }
         }
     }
 }
@@ -426,8 +427,9 @@ void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int gr
     } else { k_nee_post<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
-                  float *dump_L, uint64_t dump_cap, cudaStream_t s) {
-    k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, (dump_wl || dump_L) ? dump_cap : 0);
+                  float *dump_L, uint32_t *dump_rays, uint64_t dump_cap, cudaStream_t s) {
+    k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, st.n_shadow ? dump_rays : nullptr,
+                                                    (dump_wl || dump_L || dump_rays) ? dump_cap : 0);
     PLTB_AFTER(PLTB_K_GATHER);
     if (!do_splat) return;
     // separable filters with 3x3 (tent, r = 1) or 5x5 (gaussian, r = 2) taps go through the register tiles / shared strips

@@ -105,6 +105,7 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
     st.sensor_w[local] = s4_to_f4(wgt);
     float2 fp; fp.x = pos_f.x; fp.y = pos_f.y;
     st.film_pos[local] = fp;
+    if (st.n_shadow) st.n_shadow[local] = 0;
     for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1, plt.py:65-70)
     st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
     st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
@@ -268,6 +269,9 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
     st.v_w[r] = mkf4(ds.p.x, ds.p.y, ds.p.z, ds.delta ? -ds.pdf : ds.pdf);
     if (ds.pdf != 0.f) {
         cnt[1]++;
+#if defined(__CUDA_ARCH__)
+        if (st.n_shadow) atomicAdd(st.n_shadow + local, 1u);
+#endif
         push(st.shadow_q, st.counts + kCountsNee + 3, entry);
     }
 }

@@ -1,11 +1,13 @@
-"""Procedural stand-ins for the reference's config scenes (BASELINE.json `configs`).
+"""The config scenes (BASELINE.json `configs`) by name.
 
-The reference's scene files (XML + PLY + PNG under scenes/) are not redistributed here and do not exist on the GPU box,
-so tests/, smoke() and bench.py build *equivalent* scenes from scratch: same camera, same materials and plugin
-parameters, same light, geometry regenerated procedurally with the same triangle counts and placement (32x16 UV spheres of
-960 triangles, two-triangle quads).  Files are written in Mitsuba's own formats (XML 2.1, binary PLY, PNG) into a cache
-directory and loaded through `load_file`, so the XML / PLY / bitmap loaders are exercised exactly as with the originals.
-A user who has the reference tree simply calls `mi.load_file("<ref>/scenes/cbox-grating/cbox.xml")` instead.
+`load(name)` resolves "cbox", "cbox-grating", "gratingcap" and "veach-mis" to the reference's OWN scene files (XML + PLY + PNG,
+shipped as input fixtures under tests/golden/scenes/, or wherever $PLTB_SCENES_DIR points) -- these are what bench.py, smoke()
+and the parity tests render.  The procedural writers below remain for the scenes the reference does not hold as files
+("spectrograph:*" is built by scripts/spectrograph/scene.py, "disk" lacks its envmap blob), for the ":sky" / ":envmap"
+variants, and as `load(name, procedural=True)` stand-ins whose oracle counters tests/test_host.py compares with the files':
+same camera, materials, plugin parameters and light, geometry regenerated with the same triangle counts and placement
+(32x16 UV spheres of 960 triangles, two-triangle quads), written in Mitsuba's own formats (XML 2.1, binary PLY, PNG) into a
+cache directory and loaded through `load_file`.
 
 Measured from the reference meshes (scenes/cbox*/meshes/*.ply): box = [-1,1]^3, light quad at y = 0.98624 with half-size
 0.50592, spheres centred at (-0.4782,-0.64555,-0.1665) r 0.3568, (0.1512,-0.7712,0.5576) r 0.2274,
@@ -500,6 +502,27 @@ def scene_path(name, cache_dir=None):
     return xml
 
 
-def load(name, **defaults):
+# the reference's own files for the named configs (relative to the scenes directory) and the -D defaults its scripts pass
+_REFERENCE_FILES = {"cbox": ("cbox/cbox.xml", {}), "cbox-grating": ("cbox-grating/cbox.xml", {}),
+                    "gratingcap": ("gratingcap/gratingcap.xml", {}),
+                    "veach-mis": ("veach-mis/scene.xml", {"integrator": "plt", "max_depth": 7})}
+
+
+def reference_scene_path(name):
+    """path of the reference's scene file for config scene `name`, or None when it is not shipped"""
+    if name not in _REFERENCE_FILES:
+        return None
+    root = os.environ.get("PLTB_SCENES_DIR") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                              "tests", "golden", "scenes")
+    path = os.path.join(root, _REFERENCE_FILES[name][0])
+    return path if os.path.exists(path) else None
+
+
+def load(name, procedural=False, **defaults):
     from . import load_file
+    if name.endswith(":procedural"):
+        name, procedural = name[:-len(":procedural")], True
+    ref = None if procedural else reference_scene_path(name)
+    if ref:
+        return load_file(ref, **{**_REFERENCE_FILES[name][1], **defaults})
     return load_file(scene_path(name), **defaults)

@@ -914,7 +914,7 @@ S4 tex_eval(const Scene &sc, int32_t id, const S4 &wl, V2 uv) {
  * BSDFs
  * ---------------------------------------------------------------------------------------------------------- */
 struct BSDFSample { V3 wo; float pdf = 0.f, eta = 0.f; uint32_t type = 0; };
-struct SampleOut { BSDFSample bs; S4 weight; int lobe[2] = { 0, 0 }; };
+struct SampleOut { BSDFSample bs; S4 weight; int lobe[2] = { 0, 0 }; bool lobe_valid = true; /* diffract()'s mask (unused by the reference) */ };
 
 inline Grating make_grating(const pltb_bsdf &b, V2 uv) {
     return Grating(b.f[3], V2{ b.f[4], b.f[5] }, b.f[6], b.u[2], b.u[3], b.f[7], uv);
@@ -1237,6 +1237,7 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
             float intensity = g.lobe_intensity(o.lobe[0], o.lobe[1], wi_local, wavelength); /* nm, as written (N2) */
             bool valid; V3 wo_local = g.diffract(wi_local, o.lobe[0], o.lobe[1], wavelength * 1e-3f, valid);
             o.bs.wo = nf.to_world(wo_local);
+            o.lobe_valid = valid;   /* returned as active_diffracted and never read (roughgrating.cpp:514-521); kept for the trace */
             float grating_pdf = pdf_xy.x * pdf_xy.y;
             o.bs.eta = 1.f; o.bs.type = F_GlossyReflection;
             bool active = (o.bs.pdf != 0.f) && o.bs.wo.z > 0.f;
@@ -1671,7 +1672,17 @@ struct Bounce {
     float last_nd_pdf = 0.f;
     int lobe[2] = { 0, 0 };
     bool active = false;
+    bool lobe_valid = true;   /* trace only */
 };
+
+/* Non-finite trace (tools/nan_trace.py): with PLT_ORACLE_NAN_TRACE=<file> every non-finite term of plt_solve_phase is written as
+ * one JSON line naming the factor that is not finite and the state of the path that led there (per bounce: BSDF type, |wo|,
+ * sampled lobe and whether diffract() flagged it invalid, |wi| of the vertex).  Test infrastructure, single-threaded use. */
+static FILE *nan_trace_file() {
+    static FILE *f = [] { const char *p = getenv("PLT_ORACLE_NAN_TRACE"); return p ? fopen(p, "a") : (FILE *) nullptr; }();
+    return f;
+}
+static bool s4_finite(const S4 &s) { return std::isfinite(s[0]) && std::isfinite(s[1]) && std::isfinite(s[2]) && std::isfinite(s[3]); }
 
 struct Counters { uint64_t closest = 0, shadow = 0, vertices = 0, grating = 0; };
 
@@ -1686,6 +1697,24 @@ S4 replay_path(const Scene &sc, const Bounce *bb, int bounce_idx) {
         if (b.active) alpha = wbsdf_weight(sc, b.si, b.wo) * alpha;
     }
     return alpha;
+}
+
+static void trace_nonfinite(const Scene &sc, const Bounce *bb, uint32_t n_written, uint32_t bi, const char *term, const S4 &mis,
+                            const S4 &emitter, const S4 &bsdf_val, const S4 &alpha) {
+    FILE *f = nan_trace_file();
+    const char *first = !s4_finite(emitter) ? "emitter" : !s4_finite(mis) ? "mis" : !s4_finite(bsdf_val) ? "bsdf_val"
+                        : !s4_finite(alpha) ? "replay_alpha" : "product(0*inf)";
+    fprintf(f, "{\"term\": \"%s\", \"bounce\": %u, \"first_nonfinite_factor\": \"%s\", \"emitter\": %g, \"mis\": %g, \"bsdf_val\": %g, "
+               "\"alpha\": %g, \"path\": [", term, bi, first, emitter[0], mis[0], bsdf_val[0], alpha[0]);
+    for (uint32_t j = 0; j < n_written && j <= bi; ++j) {
+        const Bounce &b = bb[j];
+        const pltb_bsdf *bs = b.si.valid() ? si_bsdf(sc, b.si) : nullptr;
+        S4 w = (b.si.valid() && j < bi) ? wbsdf_weight(sc, b.si, b.wo) : S4(0.f);
+        fprintf(f, "%s{\"bsdf\": %d, \"wi_norm\": %g, \"wo_norm\": %g, \"lobe\": [%d, %d], \"lobe_valid\": %s, \"weight\": %g}", j ? ", " : "",
+                bs ? (int) bs->type : -1, norm(b.si.wi), norm(b.wo), b.lobe[0], b.lobe[1], b.lobe_valid ? "true" : "false", w[0]);
+    }
+    fprintf(f, "]}\n");
+    fflush(f);
 }
 
 S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint32_t max_depth, uint32_t rr_depth,
@@ -1725,7 +1754,7 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
         active_next &= !rr_active || rr_continue;
         Bounce &b = bb[i];
         b.si = si; b.wo = so.bs.wo; b.flags = so.bs.type; b.last_nd_pdf = last_nd_pdf;
-        b.lobe[0] = so.lobe[0]; b.lobe[1] = so.lobe[1]; b.active = true;
+        b.lobe[0] = so.lobe[0]; b.lobe[1] = so.lobe[1]; b.active = true; b.lobe_valid = so.lobe_valid;
         if (si.valid()) {
             cnt.vertices++;
             const pltb_bsdf *bs = si_bsdf(sc, si);
@@ -1769,8 +1798,8 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                     S4 Lem = Le * mis_bsdf;
                     S4 a = replay_path(sc, bb, (int) bi);
                     L = L + a * Lem;
-                    if (getenv("PLT_ORACLE_DEBUG") && std::isnan((a * Lem)[0]))
-                        fprintf(stderr, "NaN EM bi=%u a=%g Lem=%g mis=%g lnd=%g empdf=%g\n", bi, a[0], Lem[0], mis_bsdf, b.last_nd_pdf, em_pdf);
+                    if (nan_trace_file() && !s4_finite(a * Lem))
+                        trace_nonfinite(sc, bb, n_written, bi, "emissive", S4(mis_bsdf), Le, S4(1.f), a);
                 }
             } else if (sc.env >= 0) {
                 /* the ray escaped: si.emitter(scene) is the environment (interaction.h:343-346); DirectionSample3f(scene, si,
@@ -1868,10 +1897,8 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
                 float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
                 S4 a = replay_path(sc, bb, (int) bi);
                 L = L + ((em_weight * mis_em) * bsdf_val) * a;
-                if (getenv("PLT_ORACLE_DEBUG") && std::isnan((((em_weight * mis_em) * bsdf_val) * a)[0]))
-                    fprintf(stderr, "NaN NEE bi=%u em_w=%g mis=%g bsdf=%g a=%g pdf=%g bsdf_pdf=%g wo=(%g %g %g) wi=(%g %g %g) type=%u\n", bi,
-                            em_weight[0], mis_em, bsdf_val[0], a[0], ds.pdf, bsdf_pdf, wo.x, wo.y, wo.z, si.wi.x, si.wi.y, si.wi.z,
-                            si_bsdf(sc, si)->type);
+                if (nan_trace_file() && !s4_finite(((em_weight * mis_em) * bsdf_val) * a))
+                    trace_nonfinite(sc, bb, n_written, bi, "nee", S4(mis_em), em_weight, bsdf_val, a);
             }
         }
     }

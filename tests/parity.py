@@ -18,6 +18,12 @@ def sample_agreement(a, b):
     return ok.all(axis=1).mean()
 
 
+def nonfinite_counts(a, b):
+    """(# samples non-finite in a, in b, in both)"""
+    na, nb = ~np.isfinite(np.asarray(a)).all(axis=1), ~np.isfinite(np.asarray(b)).all(axis=1)
+    return int(na.sum()), int(nb.sum()), int((na & nb).sum())
+
+
 def relative_mse(img, ref):
     """mean((img - ref)^2 / (ref^2 + 1e-2)) over the pixels finite in both images; also returns the fraction of pixels
     whose finiteness differs"""

@@ -36,6 +36,32 @@ def test_c2_crop_at_full_sample_count(mi, oracle, integ):
         assert abs(a - b) <= max(4, 1e-3 * b), (k, a, b)
 
 
+def test_c2_full_frame_one_sample_index(mi, oracle, integ):
+    """the whole 1024x1024 frame of C2 for sample indices [511, 512) of 1024 (1.05e6 samples, lane index idx = pixel * 1024 + 511):
+    per-sample radiance, per-sample ray counts and the raw film of that window against the oracle at equal spp"""
+    from mitsuba3_plt_b200 import capi, scenes
+    from parity import MAX_RMSE, nonfinite_counts, relative_mse
+    sc = scenes.load("cbox-grating", resx=1024, resy=1024)
+    ctx = mi.context()
+    n = 1024 * 1024
+    prm = capi.RenderParams(seed=0, spp=1024, spp_begin=511, spp_count=1, max_depth=7, rr_depth=50)
+    film = np.empty((1024, 1024, 4), np.float32)
+    wl, L, nr = np.zeros((n, 4), np.float32), np.zeros((n, 4), np.float32), np.zeros((n, 2), np.uint32)
+    dmp = capi.SampleDump(capi.fptr(wl), capi.fptr(L), capi.uptr(nr), n)
+    st = capi.Stats()
+    capi.check(capi.lib().pltb_render(ctx._h, sc.device(ctx), C.byref(prm), film.ctypes.data, C.byref(dmp), C.byref(st)))
+    ref = oracle.render(sc.flat, 1024, seed=0, spp_begin=511, spp_count=1, dump=True)
+    assert sample_agreement(wl, ref["wavelengths"]) == 1.0
+    frac = sample_agreement(L, ref["radiance"])
+    assert frac >= MIN_FRACTION, frac
+    assert (nr == ref["n_rays"]).all(axis=1).mean() >= MIN_FRACTION
+    nf_a, nf_b, nf_both = nonfinite_counts(L, ref["radiance"])
+    assert abs(nf_a - nf_b) <= max(2, 0.05 * nf_b) and nf_both >= min(nf_a, nf_b) - max(2, 0.05 * nf_b), (nf_a, nf_b, nf_both)
+    np.testing.assert_allclose(film[..., 3], ref["film_rgbw"][..., 3], rtol=1e-4, atol=1e-5)
+    rmse, mism = relative_mse(film[..., :3], ref["film_rgbw"][..., :3])
+    assert rmse <= MAX_RMSE and mism <= 1e-3, (rmse, mism)
+
+
 def test_c2_full_frame_linearity_and_accounting(mi, integ):
     """1024x1024 x 32 spp (2^25 samples; 4 passes when PLTB_CHUNK_LOG2=23): film([0,32)) == film([0,12)) + film([12,32)) up to the order of the float
     atomics; Gaussian W channel identical in both; counters add up."""

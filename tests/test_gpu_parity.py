@@ -2,14 +2,18 @@
 import numpy as np
 import pytest
 
-from parity import MAX_RMSE, MIN_FRACTION, max_finiteness_mismatch, relative_mse, sample_agreement
+from parity import MAX_RMSE, MIN_FRACTION, max_finiteness_mismatch, nonfinite_counts, relative_mse, sample_agreement
 
 pytestmark = pytest.mark.gpu
 
-CASES = [  # (scene, res, spp, seed)
+CASES = [  # (scene, res, spp, seed); "cbox", "cbox-grating", "gratingcap", "veach-mis" are the reference's own scene files
+    ("cbox", 256, 16, 0),                    # C1 at its configured size (BASELINE.json configs[0])
     ("cbox", 64, 8, 0),
     ("cbox-grating", 64, 8, 0),
     ("cbox-grating", 48, 16, 7),
+    ("cbox-grating", 256, 16, 1),            # C2's scene, full frame, 1.05e6 samples: the margin of the 99.9 % bar at scale
+    ("cbox-grating:procedural", 64, 8, 0),   # the procedural stand-ins (other tessellation / UVs) stay covered
+    ("cbox:procedural", 64, 8, 0),
     ("veach-mis", 64, 8, 1),                 # C4: rough conductors, sphere lights, tent filter
     ("spectrograph:bbody_3000", 1, 256, 0),  # C3: batch of 150 orthographic sensors with SRFs, directional blackbody light
     ("spectrograph:d65", 1, 64, 3),
@@ -39,6 +43,14 @@ def test_per_sample_radiance(mi, oracle, integ, name, res, spp, seed):
     assert wl_frac == 1.0, f"sampled wavelengths differ: {wl_frac}"
     frac = sample_agreement(dump["radiance"], ref["radiance"])
     assert frac >= MIN_FRACTION, f"{name}: only {frac * 100:.4f}% of samples within 1e-4"
+    # non-finite samples (invalid-lobe quirk) are counted, not waved through: same samples up to branch flips
+    nf_a, nf_b, nf_both = nonfinite_counts(dump["radiance"], ref["radiance"])
+    assert abs(nf_a - nf_b) <= max(2, 0.02 * nf_b) and nf_both >= min(nf_a, nf_b) - max(2, 0.02 * nf_b), (nf_a, nf_b, nf_both)
+    # per-sample ray counts (pltb_sample_dump.n_rays): closest-hit and shadow rays of every sample
+    same_rays = (dump["n_rays"] == ref["n_rays"]).all(axis=1).mean()
+    assert same_rays >= MIN_FRACTION, f"{name}: per-sample ray counts agree on {same_rays * 100:.4f}% of samples"
+    assert int(dump["n_rays"][:, 0].sum()) == integ.last_stats["closest_rays"]
+    assert int(dump["n_rays"][:, 1].sum()) == integ.last_stats["shadow_rays"]
     # ray counters are part of the metric (Mrays/s): must match the oracle's up to branch flips
     for k in ("closest_rays", "shadow_rays", "vertices", "grating_vertices"):
         a, b = integ.last_stats[k], ref["stats"][k]

@@ -24,7 +24,25 @@ def test_builtin_scenes_load(mi):
     g = [x for x in b.flat.bsdfs if x.type == capi.BSDF_ROUGHGRATING][0]
     assert g.u[2] == 7 and g.u[3] == 0x10 and abs(g.f[3] - 1.509) < 1e-6 and abs(g.f[7] - 10) < 1e-6
     assert abs(g.f[4] - 0.7) < 1e-6 and abs(g.f[5] - 0.4) < 1e-6 and abs(g.f[1] - 0.02) < 1e-7
-    assert b.integrator().max_depth == 7 and b.integrator().rr_depth == 50
+    # the shipped file is the reference's own: its embedded integrator is `path` (cbox.xml:11), which the scripts override
+    with pytest.raises(RuntimeError, match='Plugin "path" not found'):
+        b.integrator()
+    p = scenes.load("cbox-grating", procedural=True, resx=16, resy=16)
+    assert p.integrator().max_depth == 7 and p.integrator().rr_depth == 50
+
+
+def test_reference_files_vs_procedural_stand_ins(mi, oracle):
+    """the procedural writers (kept for the ':sky' / ':envmap' variants and as stand-ins) against the reference's files they
+    imitate, through the oracle: same work mix up to tessellation / UV differences, same image mean"""
+    from mitsuba3_plt_b200 import scenes
+    for name, tol in (("cbox", 0.05), ("cbox-grating", 0.10), ("gratingcap", 1e-6), ("veach-mis", 1e-6)):
+        assert scenes.reference_scene_path(name), name
+        a = oracle.render(scenes.load(name, resx=48, resy=48).flat, 8)
+        b = oracle.render(scenes.load(name, procedural=True, resx=48, resy=48).flat, 8)
+        for k in ("closest_rays", "shadow_rays", "vertices", "grating_vertices"):
+            assert abs(a["stats"][k] - b["stats"][k]) <= tol * max(a["stats"][k], 1), (name, k, a["stats"][k], b["stats"][k])
+        ma, mb = np.nanmean(a["image"]), np.nanmean(b["image"])
+        assert abs(ma - mb) <= max(tol, 1e-4) * ma, (name, ma, mb)
 
 
 @pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree only exists in the build container")
@@ -327,3 +345,18 @@ dist.destroy_process_group()
                           "127.0.0.1", "--master-port", "29617", "--no-python", sys.executable, "-c", code],
                          capture_output=True, text=True, env=env, timeout=300)
     assert "REDUCE_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_nonfinite_samples_all_trace_to_invalid_lobes():
+    """every non-finite radiance term of the unpolarized spectral path comes from a path that sampled an
+    invalid diffraction lobe (diffract()'s mask is returned and never read, roughgrating.cpp:514-521) and so continued with a
+    non-unit direction; the replayed throughput of such a path is exactly 0, the NaN is 0 * inf.  tools/nan_trace.py dumps the
+    oracle's trace; profiles/r02_nan_trace_*.txt are its output at larger sizes."""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "nan_trace.py"), "cbox-grating", "--res", "96", "--spp", "16",
+                          "--records", "1000"], capture_output=True, text=True, check=True).stdout
+    import json
+    recs = [json.loads(l) for l in out.splitlines() if l.startswith("{")]
+    assert len(recs) >= 3, out     # ~48 per 1e6 samples
+    for r in recs:
+        assert any(not b["lobe_valid"] and abs(b["wo_norm"] - 1) > 1e-3 for b in r["path"][:-1]), r
+        assert r["alpha"] == 0 or r["first_nonfinite_factor"] == "replay_alpha", r
