@@ -10,7 +10,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpltb200.so")
-if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu_ab.sh)
+if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu.sh ab:<suffix>)
     LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
 PLTB_ABI_VERSION = 4

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Experimental build of libpltb200 with extra nvcc flags:  tools/build_variant.sh <suffix> <flags...>  ->  mitsuba3_plt_b200/libpltb200_<suffix>.so
-# (selected at run time with PLTB200_LIB, see tools/gpu_ab.sh; variants are not tracked by git)
+# (selected at run time with PLTB200_LIB, see tools/gpu.sh ab:<suffix>; variants are not tracked by git)
 set -e
 sfx=$1; shift
 root=$(cd $(dirname $0)/.. && pwd)
