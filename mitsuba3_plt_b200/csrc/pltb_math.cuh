@@ -39,10 +39,22 @@ PLTB_HD float rcp(float x) { return __frcp_rn(x); }   // == 1.f / x (correctly r
 #else
 PLTB_HD float rcp(float x) { return 1.f / x; }
 #endif
-#if defined(__CUDA_ARCH__) && defined(PLTB_FAST_RSQRT)
-PLTB_HD float rsqrt_(float x) { return rsqrtf(x); }   // MUFU.RSQ, <= 2 ulp (what Dr.Jit's CUDA backend emits for dr::rsqrt)
+// dr::rsqrt.  Geometry and BSDF code (normalisations, microfacet sampling, the grating direction) gets the value of Dr.Jit's
+// scalar fallback 1 / sqrt(x) -- two correctly rounded IEEE operations, spelled so that no division subroutine is called: a
+// 2-ulp MUFU.RSQ there moves diffraction / microfacet branches and costs 5-10x more divergent samples than everything else
+// together (profiles/r02_ab_numerics.txt).  Smooth colour arithmetic (srgb_model_eval: 16 calls per bitmap lookup) may use
+// MUFU.RSQ (-DPLTB_FAST_RSQRT, the default; what Dr.Jit's CUDA backend emits for dr::rsqrt everywhere): no branch depends on it.
+#if defined(__CUDA_ARCH__) && defined(PLTB_FAST_RSQRT_ALL)
+PLTB_HD float rsqrt_(float x) { return rsqrtf(x); }
+#elif defined(__CUDA_ARCH__)
+PLTB_HD float rsqrt_(float x) { return __frcp_rn(__fsqrt_rn(x)); }
 #else
 PLTB_HD float rsqrt_(float x) { return 1.f / sqrtf(x); }
+#endif
+#if defined(__CUDA_ARCH__) && (defined(PLTB_FAST_RSQRT) || defined(PLTB_FAST_RSQRT_ALL))
+PLTB_HD float rsqrt_smooth(float x) { return rsqrtf(x); }
+#else
+PLTB_HD float rsqrt_smooth(float x) { return rsqrt_(x); }
 #endif
 PLTB_HD float safe_sqrt(float x) { return sqrtf(fmaxf(x, 0.f)); }
 PLTB_HD uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }

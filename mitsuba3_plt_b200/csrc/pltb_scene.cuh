@@ -248,7 +248,7 @@ PLTB_HD float srgb_model_eval(const float *c, float wl) {  // include/mitsuba/re
     float c0 = PLTB_LDG(c), c1 = PLTB_LDG(c + 1), c2 = PLTB_LDG(c + 2);
     float v = fmadd(fmadd(c0, wl, c1), wl, c2);
     if (isinf_(c2)) return fmadd(sign1(c2), .5f, .5f);
-    return fmaxf(0.f, fmadd(.5f * v, rsqrt_(fmadd(v, v, 1.f)), .5f));
+    return fmaxf(0.f, fmadd(.5f * v, rsqrt_smooth(fmadd(v, v, 1.f)), .5f));
 }
 PLTB_HD float regular_eval(const float *vals, uint32_t count, float lo, float hi, float x) {  // distr_1d.h:364-379
     if (!(x >= lo && x <= hi)) return 0.f;

@@ -226,7 +226,9 @@ struct Grating {
     }
     // the same for sample_lobe's selection weights (sinusoidal gratings: reduced-precision Bessel, see bessel_j_fast)
     PLTB_HD float axis_term_select(const BesselTables &bt, float a, int l) const {
+#ifndef PLTB_EXACT_SELECT
         if (l != 0 && (type & 0xFu) == 0) return sqr(bessel_j_fast(bt, a, l));
+#endif
         return axis_term(bt, a, l);
     }
     PLTB_HD float lobe_intensity(const BesselTables &bt, int lx, int ly, V3 wi, float wl) const {
