@@ -1,4 +1,4 @@
-// pltb_bvh.h -- host-side binned-SAH BVH builder producing the 2-wide node layout traversed by bvh_intersect()
+// pltb_bvh.h -- host-side binned-SAH BVH builder producing the 4-wide node layout traversed by Traversal / bvh_intersect()
 // (pltb_scene.cuh).  Replaces the reference's kd-tree / Embree / OptiX acceleration structures
 // (include/mitsuba/render/kdtree.h, src/render/scene_embree.inl, scene_optix.inl); the config scenes have <= 3k
 // primitives, so a host build takes well under a millisecond per thousand triangles.
@@ -15,9 +15,10 @@
 namespace pltb {
 
 struct HostBVH {
-    std::vector<float> nodes;     // 16 floats per node
+    std::vector<float> nodes;     // 32 floats per 4-wide node
     std::vector<float> tri_data;  // 12 floats per leaf-ordered primitive
     uint32_t n_nodes = 0, n_prims = 0;
+    uint32_t stack_need = 0;      // traversal-stack entries the deepest path can require (checked against kBvhStack)
 };
 
 namespace detail {
@@ -44,7 +45,11 @@ struct Builder {
 #ifndef PLTB_BVH_LEAF
 #define PLTB_BVH_LEAF 4   // primitives per leaf at which splitting stops
 #endif
-    static constexpr int kBins = 16, kLeaf = PLTB_BVH_LEAF;
+    static constexpr int kBins = 16, kLeaf = PLTB_BVH_LEAF, kMaxDepth = 48;
+
+    // binary tree of the binned-SAH build; collapsed into 4-wide nodes by emit()
+    struct TNode { Box box; int32_t left = -1, right = -1; uint32_t first = 0, count = 0; };
+    std::vector<TNode> tree;
 
     int32_t make_leaf(uint32_t first, uint32_t count) {
         uint32_t base = out->n_prims;
@@ -65,15 +70,17 @@ struct Builder {
         return (int32_t) ~(base | (count << 24));
     }
 
-    // returns child reference (>= 0 inner node index, < 0 leaf) and its bounds
-    int32_t build(uint32_t first, uint32_t count, Box &bounds) {
-        bounds = Box();
-        Box cb;
+    // binned SAH split of prims[first, first + count); past kMaxDepth (degenerate input) median splits bound the depth
+    int32_t build(uint32_t first, uint32_t count, int depth) {
+        const int32_t idx = (int32_t) tree.size();
+        tree.emplace_back();
+        Box bounds, cb;
         for (uint32_t i = first; i < first + count; ++i) { bounds.grow(boxes[prims[i]]); cb.grow(&cent[3 * prims[i]]); }
-        if (count <= (uint32_t) kLeaf) return make_leaf(first, count);
+        tree[idx].box = bounds; tree[idx].first = first; tree[idx].count = count;
+        if (count <= (uint32_t) kLeaf) return idx;
         int best_axis = -1, best_bin = -1;
         float best_cost = std::numeric_limits<float>::infinity();
-        for (int axis = 0; axis < 3; ++axis) {
+        for (int axis = 0; axis < 3 && depth < kMaxDepth; ++axis) {
             float ext = cb.hi[axis] - cb.lo[axis];
             if (!(ext > 0)) continue;
             Box bb[kBins]; uint32_t bc[kBins] = { 0 };
@@ -95,7 +102,7 @@ struct Builder {
         }
         uint32_t mid;
         if (best_axis < 0) {
-            mid = first + count / 2;   // all centroids coincide
+            mid = first + count / 2;   // all centroids coincide, or the depth bound was reached
         } else {
             float ext = cb.hi[best_axis] - cb.lo[best_axis], scale = kBins / ext, lo = cb.lo[best_axis];
             auto it = std::partition(prims.begin() + first, prims.begin() + first + count, [&](uint32_t p) {
@@ -104,24 +111,56 @@ struct Builder {
             mid = (uint32_t) (it - prims.begin());
             if (mid == first || mid == first + count) mid = first + count / 2;
         }
-        uint32_t idx = out->n_nodes++;
-        out->nodes.resize(16 * (size_t) out->n_nodes, 0.f);
-        Box b0, b1;
-        int32_t c0 = build(first, mid - first, b0);
-        int32_t c1 = build(mid, first + count - mid, b1);
-        float *n = &out->nodes[16 * (size_t) idx];
-        // pad the child boxes so that the device slab test is conservative w.r.t. the exact triangle test
-        auto pad = [](Box &b) {
-            for (int k = 0; k < 3; ++k) {
-                float e = 1e-5f * std::max(std::fabs(b.lo[k]), std::fabs(b.hi[k])) + 1e-6f * (b.hi[k] - b.lo[k]) + 1e-7f;
-                b.lo[k] -= e; b.hi[k] += e;
+        const int32_t l = build(first, mid - first, depth + 1);
+        const int32_t r = build(mid, first + count - mid, depth + 1);
+        tree[idx].left = l; tree[idx].right = r;
+        return idx;
+    }
+
+    // Collapse the binary subtree at `t` (an inner node) into one 4-wide node: the children of `t`, with the inner child of
+    // the largest surface area replaced by its own two children until there are four (or only leaves are left).
+    // Node layout (8 float4 = one 128-byte line): lo.x[4] lo.y[4] lo.z[4] hi.x[4] hi.y[4] hi.z[4] child[4] pad[4]; empty slots
+    // are far-away point boxes and reference an empty leaf.  Returns the node index; `need` receives the traversal-stack
+    // entries the subtree can require (3 pushed siblings per level).
+    int32_t emit(int32_t t, uint32_t &need) {
+        int32_t kids[4]; int n = 0;
+        kids[n++] = tree[t].left; kids[n++] = tree[t].right;
+        while (n < 4) {
+            int pick = -1; float best = -1.f;
+            for (int i = 0; i < n; ++i)
+                if (tree[kids[i]].left >= 0 && tree[kids[i]].box.area() > best) { best = tree[kids[i]].box.area(); pick = i; }
+            if (pick < 0) break;
+            const int32_t k = kids[pick];
+            kids[pick] = tree[k].left; kids[n++] = tree[k].right;
+        }
+        const uint32_t idx = out->n_nodes++;
+        out->nodes.resize(32 * (size_t) out->n_nodes, 0.f);
+        int32_t ref[4]; Box bx[4]; uint32_t sub = 0; bool empty[4];
+        for (int i = 0; i < 4; ++i) {
+            empty[i] = i >= n || (tree[kids[i]].left < 0 && tree[kids[i]].count == 0);
+            if (empty[i]) { ref[i] = (int32_t) ~0u; continue; }
+            const TNode &k = tree[kids[i]];
+            bx[i] = k.box;
+            if (k.left < 0) ref[i] = make_leaf(k.first, k.count);
+            else { uint32_t s = 0; ref[i] = emit(kids[i], s); sub = std::max(sub, s); }
+            // pad the child boxes so that the device slab test is conservative w.r.t. the exact triangle test
+            for (int a = 0; a < 3; ++a) {
+                float e = 1e-5f * std::max(std::fabs(bx[i].lo[a]), std::fabs(bx[i].hi[a])) + 1e-6f * (bx[i].hi[a] - bx[i].lo[a]) + 1e-7f;
+                bx[i].lo[a] -= e; bx[i].hi[a] += e;
             }
-        };
-        pad(b0); pad(b1);
-        n[0] = b0.lo[0]; n[1] = b0.lo[1]; n[2] = b0.lo[2]; n[3] = b0.hi[0];
-        n[4] = b0.hi[1]; n[5] = b0.hi[2]; n[6] = b1.lo[0]; n[7] = b1.lo[1];
-        n[8] = b1.lo[2]; n[9] = b1.hi[0]; n[10] = b1.hi[1]; n[11] = b1.hi[2];
-        n[12] = bitsf((uint32_t) c0); n[13] = bitsf((uint32_t) c1);
+        }
+        float *nd = &out->nodes[32 * (size_t) idx];
+        // an empty slot is a far-away point box (an infinite one would pass the slab test of rays with maxt = FLT_MAX, whose
+        // padded far distance overflows); should a ray ever aim at it, it finds an empty leaf
+        const float far_away = 1e30f;
+        for (int i = 0; i < 4; ++i) {
+            for (int a = 0; a < 3; ++a) {
+                nd[4 * a + i] = empty[i] ? far_away : bx[i].lo[a];
+                nd[12 + 4 * a + i] = empty[i] ? far_away : bx[i].hi[a];
+            }
+            nd[24 + i] = bitsf((uint32_t) ref[i]);
+        }
+        need = 3u + sub;
         return (int32_t) idx;
     }
 };
@@ -156,18 +195,14 @@ inline void build_bvh(const pltb_scene_desc *d, HostBVH &out) {
         for (int k = 0; k < 3; ++k) b.cent[3 * p + k] = 0.5f * (b.boxes[p].lo[k] + b.boxes[p].hi[k]);
     out = HostBVH();
     if (b.prims.empty()) return;
-    Box root;
-    int32_t r = b.build(0, (uint32_t) b.prims.size(), root);
-    if (r < 0) {
-        // a single leaf: wrap it in one inner node whose second child is an empty leaf
-        out.n_nodes = 1;
-        out.nodes.assign(16, 0.f);
-        float *n = out.nodes.data();
-        n[0] = root.lo[0] - 1e-4f; n[1] = root.lo[1] - 1e-4f; n[2] = root.lo[2] - 1e-4f; n[3] = root.hi[0] + 1e-4f;
-        n[4] = root.hi[1] + 1e-4f; n[5] = root.hi[2] + 1e-4f;
-        for (int k = 0; k < 6; ++k) n[6 + k] = n[k];
-        n[12] = bitsf((uint32_t) r); n[13] = bitsf(~0u);   // second child: empty leaf
+    int32_t root = b.build(0, (uint32_t) b.prims.size(), 0);
+    if (b.tree[root].left < 0) {
+        // a single leaf: wrap it in one node whose other slots are empty
+        Builder::TNode leaf = b.tree[root];
+        b.tree.push_back(leaf); b.tree.push_back(Builder::TNode());
+        b.tree[root].left = (int32_t) b.tree.size() - 2; b.tree[root].right = (int32_t) b.tree.size() - 1;
     }
+    b.emit(root, out.stack_need);
 }
 
 }  // namespace pltb

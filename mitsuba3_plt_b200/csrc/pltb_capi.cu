@@ -163,11 +163,25 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     }
     for (uint32_t i = 0; i < d->n_faces * 3; ++i)
         if (d->faces[i] >= d->n_vertices) return fail(PLTB_ERR_INVALID, "face index out of range");
+    for (uint32_t i = 0; i < d->n_emitters; ++i) {
+        const pltb_emitter &e = d->emitters[i];
+        if (e.type > PLTB_EMITTER_ENVMAP) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
+        if (e.type == PLTB_EMITTER_ENVMAP &&
+            (e.env_res[0] < 3 || e.env_res[1] < 3 || (uint64_t) e.env_data + 4ull * e.env_res[0] * e.env_res[1] > d->n_tex_data ||
+             e.env_warp >= d->n_tex_data))
+            return fail(PLTB_ERR_INVALID, "envmap: data / warp blocks outside tex_data");
+    }
+    // leaf references hold the first primitive in 24 bits; the traversal stack has kBvhStack entries
+    if ((uint64_t) d->n_faces + d->n_shapes >= (1u << 24))
+        return fail(PLTB_ERR_UNSUPPORTED, "scenes with 2^24 or more primitives are not supported by the BVH leaf encoding");
+    HostBVH bvh;
+    build_bvh(d, bvh);
+    if (bvh.stack_need > (uint32_t) kBvhStack)
+        return fail(PLTB_ERR_UNSUPPORTED, "BVH too deep for the traversal stack (" + std::to_string(bvh.stack_need) + " > " +
+                                          std::to_string(kBvhStack) + " entries)");
     CU(cudaSetDevice(ctx->device));
     pltb_scene *s = new pltb_scene();
     s->ctx = ctx;
-    HostBVH bvh;
-    build_bvh(d, bvh);
     DeviceScene &ds = s->dev;
     int rc = 0;
     const float *nodes = nullptr, *tris = nullptr;
@@ -195,15 +209,8 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     ds.n_faces = d->n_faces; ds.n_shapes = d->n_shapes; ds.n_emitters = d->n_emitters; ds.n_sensors = d->n_sensors;
     ds.emitter_pmf = d->n_emitters ? 1.f / (float) d->n_emitters : 0.f;
     ds.env = -1;
-    for (uint32_t i = 0; i < d->n_emitters; ++i) {
-        const pltb_emitter &e = d->emitters[i];
-        if (e.type > PLTB_EMITTER_ENVMAP) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
-        if (e.type == PLTB_EMITTER_CONSTANT || e.type == PLTB_EMITTER_ENVMAP) ds.env = (int32_t) i;
-        if (e.type == PLTB_EMITTER_ENVMAP &&
-            (e.env_res[0] < 3 || e.env_res[1] < 3 || (uint64_t) e.env_data + 4ull * e.env_res[0] * e.env_res[1] > d->n_tex_data ||
-             e.env_warp >= d->n_tex_data))
-            return fail(PLTB_ERR_INVALID, "envmap: data / warp blocks outside tex_data");
-    }
+    for (uint32_t i = 0; i < d->n_emitters; ++i)
+        if (d->emitters[i].type == PLTB_EMITTER_CONSTANT || d->emitters[i].type == PLTB_EMITTER_ENVMAP) ds.env = (int32_t) i;
     // Simpson nodes of math::bessel_j_small (include/mitsuba/core/math.h:204-223, 316-322), float ops as the reference
     {
         const float a = 0.f, b = kPi, h = (b - a) / (float) (20 - 1);

@@ -63,6 +63,8 @@ PLTB_HD bool signbit_(float b) { return (f2u(b) >> 31) != 0; }
 PLTB_HD float mulsign(float a, float b) { return u2f(f2u(a) ^ (f2u(b) & 0x80000000u)); }
 PLTB_HD float mulsign_neg(float a, float b) { return u2f(f2u(a) ^ (~f2u(b) & 0x80000000u)); }
 PLTB_HD float sign1(float v) { return u2f(0x3f800000u | (f2u(v) & 0x80000000u)); }
+PLTB_HD uint32_t umin_(uint32_t a, uint32_t b) { return a < b ? a : b; }
+PLTB_HD uint32_t umax_(uint32_t a, uint32_t b) { return a > b ? a : b; }
 PLTB_HD bool finite_(float x) { return (f2u(x) & 0x7f800000u) != 0x7f800000u; }
 PLTB_HD bool isnan_(float x) { return x != x; }
 PLTB_HD bool isinf_(float x) { return (f2u(x) & 0x7fffffffu) == 0x7f800000u; }

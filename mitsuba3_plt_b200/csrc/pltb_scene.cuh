@@ -1,6 +1,6 @@
-// pltb_scene.cuh -- device-resident flattened scene: geometry SoA, 2-wide BVH, plugin tables, texture evaluation.
+// pltb_scene.cuh -- device-resident flattened scene: geometry SoA, 4-wide BVH, plugin tables, texture evaluation.
 // Layout in HBM (all tables are small and stay L1/L2-resident for the config scenes):
-//   bvh_nodes : float4[4] per node  {lo0.xyz,hi0.x}{hi0.yz,lo1.xy}{lo1.z,hi1.xyz}{child0,child1 as int bits}
+//   bvh_nodes : float4[8] per 4-wide node  lo.x[4] lo.y[4] lo.z[4] hi.x[4] hi.y[4] hi.z[4] child[4] (int bits) pad[4]
 //   tri_data  : float4[3] per leaf-ordered primitive {p0.xyz,e1.x}{e1.yz,e2.xy}{e2.z, prim id, shape id, -}
 //   vertex arrays / faces as uploaded from pltb_scene_desc; plugin tables as arrays of the ABI structs.
 #pragma once
@@ -75,10 +75,14 @@ PLTB_HD bool rectangle_intersect(const pltb_shape &sh, const Ray &ray, float &t_
     return true;
 }
 
-// Scene::ray_intersect / ray_test (src/render/scene.cpp:176-205) over our own BVH: short-stack traversal, ordered
-// descent, Moeller-Trumbore exactly as Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:460-481).
-// The traversal is a resumable state machine (one inner node or one leaf per step) so that k_trace can keep the lanes of
-// a warp busy by handing finished lanes a new ray while the others are still walking the tree.
+// Scene::ray_intersect / ray_test (src/render/scene.cpp:176-205) over our own 4-wide BVH: ordered descent with a small stack of
+// (entry distance, child) pairs so that subtrees behind the closest hit found so far are dropped when they are popped, without
+// fetching their node; Moeller-Trumbore exactly as Mesh::moeller_trumbore (include/mitsuba/render/mesh.h:460-481).
+// A node is one 128-byte line (pltb_bvh.h): seven 16-byte loads, four slab tests, a 5-exchange sorting network on keys
+// (distance bits | child slot).  The traversal is a resumable state machine (one inner node or one leaf per step) so that
+// k_trace can keep the lanes of a warp busy by handing finished lanes a new ray while the others are still walking the tree.
+constexpr int kBvhStack = 64;   // entries; pltb_scene_create refuses scenes whose tree could need more (HostBVH::stack_need)
+
 struct Traversal {
     Ray ray;
     float ix, iy, iz;
@@ -86,7 +90,7 @@ struct Traversal {
     int sp;
     bool done;
     Hit best;
-    int32_t stack[32];
+    unsigned long long stack[kBvhStack];   // key << 32 | child reference
 
     PLTB_HD void begin(const DeviceScene &sc, const Ray &r) {
         ray = r;
@@ -99,33 +103,48 @@ struct Traversal {
         ix = 1.f / r.d.x; iy = 1.f / r.d.y; iz = 1.f / r.d.z;
     }
     PLTB_HD void pop() {
-        if (sp == 0) done = true;
-        else node = stack[--sp];
+        while (sp > 0) {
+            const unsigned long long e = stack[--sp];
+            // the key holds the entry distance rounded down: a subtree that starts behind the closest hit cannot improve it
+            if (u2f((uint32_t) (e >> 32) & ~3u) <= ray.maxt) { node = (int32_t) (uint32_t) e; return; }
+        }
+        done = true;
+    }
+    PLTB_HD static uint32_t slab_key(float lox, float loy, float loz, float hix, float hiy, float hiz, float ox, float oy, float oz,
+                                     float ix, float iy, float iz, float maxt, uint32_t slot) {
+        const float t0x = (lox - ox) * ix, t1x = (hix - ox) * ix;
+        const float t0y = (loy - oy) * iy, t1y = (hiy - oy) * iy;
+        const float t0z = (loz - oz) * iz, t1z = (hiz - oz) * iz;
+        const float n = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+        const float f = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), maxt));
+        // boxes are padded at build time; the 1 + 4 ulp factor keeps the slab test conservative
+        return n <= f * 1.0000005f ? ((f2u(n) & ~3u) | slot) : 0xFFFFFFFFu;
     }
     PLTB_HD void inner_step(const DeviceScene &sc) {
-        const float4 *n = sc.bvh_nodes + 4 * (size_t) node;
-        float4 a = PLTB_LDG(n), b = PLTB_LDG(n + 1), c = PLTB_LDG(n + 2), d = PLTB_LDG(n + 3);
-        // child 0: lo (a.x a.y a.z) hi (a.w b.x b.y); child 1: lo (b.z b.w c.x) hi (c.y c.z c.w)
-        float t0x = (a.x - ray.o.x) * ix, t1x = (a.w - ray.o.x) * ix;
-        float t0y = (a.y - ray.o.y) * iy, t1y = (b.x - ray.o.y) * iy;
-        float t0z = (a.z - ray.o.z) * iz, t1z = (b.y - ray.o.z) * iz;
-        float n0 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
-        float f0 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
-        t0x = (b.z - ray.o.x) * ix; t1x = (c.y - ray.o.x) * ix;
-        t0y = (b.w - ray.o.y) * iy; t1y = (c.z - ray.o.y) * iy;
-        t0z = (c.x - ray.o.z) * iz; t1z = (c.w - ray.o.z) * iz;
-        float n1 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
-        float f1 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
-        // boxes are padded at build time; the 1 + 4 ulp factor keeps the slab test conservative
-        bool h0 = n0 <= f0 * 1.0000005f, h1 = n1 <= f1 * 1.0000005f;
-        int32_t c0 = (int32_t) f2u(d.x), c1 = (int32_t) f2u(d.y);
-        if (h0 && h1) {
-            if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
-            stack[sp++] = c1;
-            node = c0;
-        } else if (h0) node = c0;
-        else if (h1) node = c1;
-        else pop();
+        const float4 *n = sc.bvh_nodes + 8 * (size_t) node;
+        const float4 lx = PLTB_LDG(n), ly = PLTB_LDG(n + 1), lz = PLTB_LDG(n + 2), hx = PLTB_LDG(n + 3), hy = PLTB_LDG(n + 4),
+                     hz = PLTB_LDG(n + 5), ch = PLTB_LDG(n + 6);
+        const float ox = ray.o.x, oy = ray.o.y, oz = ray.o.z, mt = ray.maxt;
+        uint32_t k0 = slab_key(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, ox, oy, oz, ix, iy, iz, mt, 0u);
+        uint32_t k1 = slab_key(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, ox, oy, oz, ix, iy, iz, mt, 1u);
+        uint32_t k2 = slab_key(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, ox, oy, oz, ix, iy, iz, mt, 2u);
+        uint32_t k3 = slab_key(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, ox, oy, oz, ix, iy, iz, mt, 3u);
+        // sorting network (0,1)(2,3)(0,2)(1,3)(1,2): ascending entry distance, misses (0xFFFFFFFF) last
+        uint32_t t;
+        t = umin_(k0, k1); k1 = umax_(k0, k1); k0 = t;
+        t = umin_(k2, k3); k3 = umax_(k2, k3); k2 = t;
+        t = umin_(k0, k2); k2 = umax_(k0, k2); k0 = t;
+        t = umin_(k1, k3); k3 = umax_(k1, k3); k1 = t;
+        t = umin_(k1, k2); k2 = umax_(k1, k2); k1 = t;
+        if (k0 == 0xFFFFFFFFu) { pop(); return; }
+        if (k3 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k3 << 32) | child_ref(ch, k3);
+        if (k2 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k2 << 32) | child_ref(ch, k2);
+        if (k1 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k1 << 32) | child_ref(ch, k1);
+        node = (int32_t) child_ref(ch, k0);
+    }
+    PLTB_HD static uint32_t child_ref(const float4 &ch, uint32_t key) {
+        const uint32_t s = key & 3u;
+        return f2u(s == 0 ? ch.x : s == 1 ? ch.y : s == 2 ? ch.z : ch.w);
     }
     template <bool AnyHit> PLTB_HD void leaf_step(const DeviceScene &sc) {
         uint32_t leaf = ~(uint32_t) node, first = leaf & 0xFFFFFFu, count = leaf >> 24;
@@ -167,80 +186,12 @@ struct Traversal {
     }
 };
 
-// one-ray-per-thread form (coherent primary rays in k_raygen, shadow rays in k_nee): same steps as Traversal, state in registers
+// one-ray-per-thread form (coherent primary rays in k_raygen): the same steps, run to completion
 template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
-    Hit best; best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
-    if (sc.n_nodes == 0) return best;
-    // A ray with a NaN component (the reference lets paths continue with alpha = inf * 0, SURVEY/DESIGN "quirks") fails every
-    // triangle / shape test (NaN comparisons are false) but would pass every slab test and walk the whole tree: report the
-    // miss right away.
-    if (isnan_(ray.o.x + ray.o.y + ray.o.z + ray.d.x + ray.d.y + ray.d.z)) return best;
-    const float ix = 1.f / ray.d.x, iy = 1.f / ray.d.y, iz = 1.f / ray.d.z;
-    int32_t stack[32];
-    int sp = 0;
-    int32_t node = 0;  // >= 0: inner node index; < 0: leaf ~(first | count << 24)
-    for (;;) {
-        if (node >= 0) {
-            const float4 *n = sc.bvh_nodes + 4 * (size_t) node;
-            float4 a = PLTB_LDG(n), b = PLTB_LDG(n + 1), c = PLTB_LDG(n + 2), d = PLTB_LDG(n + 3);
-            // child 0: lo (a.x a.y a.z) hi (a.w b.x b.y); child 1: lo (b.z b.w c.x) hi (c.y c.z c.w)
-            float t0x = (a.x - ray.o.x) * ix, t1x = (a.w - ray.o.x) * ix;
-            float t0y = (a.y - ray.o.y) * iy, t1y = (b.x - ray.o.y) * iy;
-            float t0z = (a.z - ray.o.z) * iz, t1z = (b.y - ray.o.z) * iz;
-            float n0 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
-            float f0 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
-            t0x = (b.z - ray.o.x) * ix; t1x = (c.y - ray.o.x) * ix;
-            t0y = (b.w - ray.o.y) * iy; t1y = (c.z - ray.o.y) * iy;
-            t0z = (c.x - ray.o.z) * iz; t1z = (c.w - ray.o.z) * iz;
-            float n1 = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
-            float f1 = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), ray.maxt));
-            // boxes are padded at build time; the 1 + 4 ulp factor keeps the slab test conservative
-            bool h0 = n0 <= f0 * 1.0000005f, h1 = n1 <= f1 * 1.0000005f;
-            int32_t c0 = (int32_t) f2u(d.x), c1 = (int32_t) f2u(d.y);
-            if (h0 && h1) {
-                if (n1 < n0) { int32_t t = c0; c0 = c1; c1 = t; }
-                stack[sp++] = c1;
-                node = c0;
-                continue;
-            } else if (h0) { node = c0; continue; }
-            else if (h1) { node = c1; continue; }
-        } else {
-            uint32_t leaf = ~(uint32_t) node, first = leaf & 0xFFFFFFu, count = leaf >> 24;
-            for (uint32_t i = first; i < first + count; ++i) {
-                const float4 *tp = sc.tri_data + 3 * (size_t) i;
-                float4 q0 = PLTB_LDG(tp), q1 = PLTB_LDG(tp + 1), q2 = PLTB_LDG(tp + 2);
-                uint32_t prim = f2u(q2.y);
-                int32_t shape = (int32_t) f2u(q2.z);
-                float t, u = 0.f, v = 0.f;
-                bool hit;
-                if (prim < sc.n_faces) {
-                    V3 p0 = mk3(q0.x, q0.y, q0.z), e1 = mk3(q0.w, q1.x, q1.y), e2 = mk3(q1.z, q1.w, q2.x);
-                    V3 pvec = cross(ray.d, e2);
-                    float inv_det = rcp(dot(e1, pvec));
-                    V3 tvec = ray.o - p0;
-                    u = dot(tvec, pvec) * inv_det;
-                    hit = u >= 0.f && u <= 1.f;
-                    V3 qvec = cross(tvec, e1);
-                    v = dot(ray.d, qvec) * inv_det;
-                    hit &= v >= 0.f && u + v <= 1.f;
-                    t = dot(e2, qvec) * inv_det;
-                    hit &= t >= 0.f && t <= ray.maxt;
-                } else {
-                    const pltb_shape &sh = sc.shapes[shape];
-                    if (sh.type == PLTB_SHAPE_SPHERE) hit = sphere_intersect(sh, ray, t);
-                    else hit = rectangle_intersect(sh, ray, t, u, v);
-                }
-                if (hit && t < best.t) {
-                    best.t = t; best.u = u; best.v = v; best.prim = prim; best.shape = shape;
-                    if (AnyHit) return best;
-                    ray.maxt = t;
-                }
-            }
-        }
-        if (sp == 0) break;
-        node = stack[--sp];
-    }
-    return best;
+    Traversal tr;
+    tr.begin(sc, ray);
+    while (!tr.done) tr.template step<AnyHit>(sc);
+    return tr.best;
 }
 
 // ---- textures / spectra -------------------------------------------------------------------------------------------------

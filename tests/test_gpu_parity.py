@@ -26,6 +26,20 @@ CASES = [  # (scene, res, spp, seed); "cbox", "cbox-grating", "gratingcap", "vea
 ]
 
 
+def ray_count_agreement(name, a, b):
+    """Closest-hit rays per sample must agree like the radiance does.  Shadow rays are counted when `ds.pdf != 0`
+    (scene.cpp:330-340), and for a vertex that lies ON a flat area light (paths continue through emitters, N8) the sampled
+    direction is in the light's plane: |dot(d, n)| is 0 or one ulp, so pdf is 0 or huge -- with zero radiance either way
+    (`dot(d, n) < 0` fails, area.cpp:198-208).  Device sinf / cosf differ from glibc by an ulp often enough to flip that test on
+    ~1.5 % of the samples of the closed procedural box: those counts may differ by one, everything else must be equal."""
+    a, b = a.astype(np.int64), b.astype(np.int64)
+    same_closest = (a[:, 0] == b[:, 0]).mean()
+    assert same_closest >= MIN_FRACTION, f"{name}: closest-hit ray counts agree on {same_closest * 100:.4f}% of samples"
+    d = np.abs(a[:, 1] - b[:, 1])
+    assert (d <= 1).mean() >= MIN_FRACTION and (d == 0).mean() >= 0.97, (name, (d == 0).mean(), (d <= 1).mean())
+    assert abs(int(a[:, 1].sum()) - int(b[:, 1].sum())) <= max(4, 2e-3 * b[:, 1].sum()), name
+
+
 @pytest.fixture(scope="module")
 def integ(mi):
     return mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
@@ -47,8 +61,7 @@ def test_per_sample_radiance(mi, oracle, integ, name, res, spp, seed):
     nf_a, nf_b, nf_both = nonfinite_counts(dump["radiance"], ref["radiance"])
     assert abs(nf_a - nf_b) <= max(2, 0.02 * nf_b) and nf_both >= min(nf_a, nf_b) - max(2, 0.02 * nf_b), (nf_a, nf_b, nf_both)
     # per-sample ray counts (pltb_sample_dump.n_rays): closest-hit and shadow rays of every sample
-    same_rays = (dump["n_rays"] == ref["n_rays"]).all(axis=1).mean()
-    assert same_rays >= MIN_FRACTION, f"{name}: per-sample ray counts agree on {same_rays * 100:.4f}% of samples"
+    ray_count_agreement(name, dump["n_rays"], ref["n_rays"])
     assert int(dump["n_rays"][:, 0].sum()) == integ.last_stats["closest_rays"]
     assert int(dump["n_rays"][:, 1].sum()) == integ.last_stats["shadow_rays"]
     # ray counters are part of the metric (Mrays/s): must match the oracle's up to branch flips
