@@ -35,6 +35,7 @@ struct Box {
 };
 inline uint32_t fbits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 inline float bitsf(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline uint32_t f2u_(float f) { return fbits(f); }
 
 struct Builder {
     const pltb_scene_desc *d;
@@ -64,6 +65,9 @@ struct Builder {
             } else {
                 rec[9] = bitsf(p); rec[10] = bitsf(p - d->n_faces);
             }
+            // material class of the owning shape (shade queue the hit is routed to): 1 = roughgrating, 0 = everything else
+            const int32_t bid = d->shapes[f2u_(rec[10])].bsdf;
+            rec[11] = bitsf((bid >= 0 && d->bsdfs[bid].type == PLTB_BSDF_ROUGHGRATING) ? 1u : 0u);
             out->tri_data.insert(out->tri_data.end(), rec, rec + 12);
             out->n_prims++;
         }

@@ -122,27 +122,37 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
             }
             // results are written in place; k_classify walks the live list in order afterwards so that the shade / NEE work
             // lists stay (nearly) sorted by sample id and the per-sample state accesses of later kernels stay coalesced
-            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? 0xFFFFFFFFu : tr.best.prim));
+            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? kHitMiss : (tr.best.prim | (tr.best.cls << 30))));
             active = false;
         }
     }
     flush_counters(cnt, st.counters);
 }
 
-// Routes the results of k_trace: hits to the shade queue of their material class, misses finalised in place.
+// Routes the results of k_trace: hits to the shade queue of their material class (carried in the hit record), misses finalised in
+// place.  The kernel is a chain of two dependent DRAM reads per entry (list entry -> hit record) followed by a list append, so a
+// warp takes 128 consecutive entries at a time: four independent load chains in flight per lane, appended in list order.
 __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                   uint32_t bounce) {
     const uint32_t n = st.counts[4 * bounce];
+    const uint32_t lane = threadIdx.x & 31u, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     DevPush push;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
-        const uint32_t local = st.live[e];
-        const float4 h4 = st.p_hit[local];
-        Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w); h.shape = -1;
-        PCG32 rng; rng.state = 0; rng.inc = 0;
-        if (h.prim != 0xFFFFFFFFu)
-            h.shape = h.prim < sc.n_faces ? (int32_t) __ldg(sc.face_shape + h.prim) : (int32_t) (h.prim - sc.n_faces);
-        else { rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local]; }
-        route_hit(sc, st, local, bounce, h, rng, false, push);
+    for (uint32_t base = warp * 128u; base < n; base += n_warps * 128u) {
+        uint32_t local[4]; float4 h4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { const uint32_t e = base + 32u * j + lane; local[j] = e < n ? st.live[e] : 0u; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) if (base + 32u * j + lane < n) h4[j] = st.p_hit[local[j]];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (base + 32u * j + lane >= n) continue;
+            const uint32_t w = f2u(h4[j].w);
+            Hit h; h.t = h4[j].x; h.u = h4[j].y; h.v = h4[j].z; h.prim = w & kHitPrimMask; h.cls = (w >> 30) & 1u; h.shape = -1;
+            PCG32 rng; rng.state = 0; rng.inc = 0;
+            if (w != kHitMiss) h.shape = 0;   // any valid shape: route_hit only needs hit / miss and the class here
+            else { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
+            route_hit(sc, st, local[j], bounce, h, rng, false, push);
+        }
     }
 }
 

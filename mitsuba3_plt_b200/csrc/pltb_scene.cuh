@@ -1,7 +1,7 @@
 // pltb_scene.cuh -- device-resident flattened scene: geometry SoA, 4-wide BVH, plugin tables, texture evaluation.
 // Layout in HBM (all tables are small and stay L1/L2-resident for the config scenes):
 //   bvh_nodes : float4[8] per 4-wide node  lo.x[4] lo.y[4] lo.z[4] hi.x[4] hi.y[4] hi.z[4] child[4] (int bits) pad[4]
-//   tri_data  : float4[3] per leaf-ordered primitive {p0.xyz,e1.x}{e1.yz,e2.xy}{e2.z, prim id, shape id, -}
+//   tri_data  : float4[3] per leaf-ordered primitive {p0.xyz,e1.x}{e1.yz,e2.xy}{e2.z, prim id, shape id, material class}
 //   vertex arrays / faces as uploaded from pltb_scene_desc; plugin tables as arrays of the ABI structs.
 #pragma once
 #include "../../include/pltb.h"
@@ -41,7 +41,9 @@ struct DeviceScene {
 };
 
 struct Ray { V3 o, d; float maxt; };
-struct Hit { float t, u, v; uint32_t prim; int32_t shape; };
+struct Hit { float t, u, v; uint32_t prim; int32_t shape; uint32_t cls; };   // cls: material class of the shape (tri_data)
+// closest hit as stored per path: {t, u, v, prim | cls << 30}; prim < 2^24 (pltb_scene_create); 0xFFFFFFFF = miss
+constexpr uint32_t kHitPrimMask = 0x00FFFFFFu, kHitMiss = 0xFFFFFFFFu;
 
 PLTB_HD V3 ld3(const float *p, uint32_t i) { return mk3(PLTB_LDG(p + 3 * i), PLTB_LDG(p + 3 * i + 1), PLTB_LDG(p + 3 * i + 2)); }
 PLTB_HD V2 ld2(const float *p, uint32_t i) { return mk2(PLTB_LDG(p + 2 * i), PLTB_LDG(p + 2 * i + 1)); }
@@ -94,7 +96,7 @@ struct Traversal {
 
     PLTB_HD void begin(const DeviceScene &sc, const Ray &r) {
         ray = r;
-        best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1;
+        best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1; best.cls = 0;
         sp = 0; node = 0;
         // A ray with a NaN component (the reference lets paths continue with alpha = inf * 0, DESIGN.md "quirks") fails every
         // triangle / shape test (NaN comparisons are false) but would pass every slab test and walk the whole tree: report
@@ -173,7 +175,7 @@ struct Traversal {
                 else hit = rectangle_intersect(sh, ray, t, u, v);
             }
             if (hit && t < best.t) {
-                best.t = t; best.u = u; best.v = v; best.prim = prim; best.shape = shape;
+                best.t = t; best.u = u; best.v = v; best.prim = prim; best.shape = shape; best.cls = f2u(q2.w);
                 if (AnyHit) { done = true; return; }
                 ray.maxt = t;
             }

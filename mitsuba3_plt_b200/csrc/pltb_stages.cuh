@@ -66,11 +66,11 @@ template <class Push>
 PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, const Hit &h, PCG32 &rng,
                        bool rng_dirty, Push &push) {
     if (h.shape >= 0) {
-        st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim));
-        if (rng_dirty) { st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc; }
-        const int32_t bid = sc.shapes[h.shape].bsdf;
-        const int cls = (bid >= 0 && sc.bsdfs[bid].type == PLTB_BSDF_ROUGHGRATING) ? 1 : 0;
-        push(st.shade_q[cls], st.counts + 4 * i + 1 + cls, local);
+        if (rng_dirty) {   // bounce 0 (k_raygen); k_trace has already written the record
+            st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim | (h.cls << 30)));
+            st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
+        }
+        push(st.shade_q[h.cls], st.counts + 4 * i + 1 + h.cls, local);
     } else {
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
         st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
@@ -120,7 +120,7 @@ template <int Class, class Push>
 PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
     const float4 o4 = st.p_ray_o[local], d4 = st.p_ray_d[local], h4 = st.p_hit[local];
     Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
-    Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w);
+    Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w) & kHitPrimMask; h.cls = (uint32_t) Class;
     h.shape = h.prim < sc.n_faces ? (int32_t) PLTB_LDG(sc.face_shape + h.prim) : (int32_t) (h.prim - sc.n_faces);
     const S4 wl = f4_to_s4(st.wl[local]);
     PCG32 rng; rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local];

@@ -23,7 +23,7 @@ int main(int argc, char **argv) {
         face_shape.push_back(0);
     }
     pltb_shape shapes[2] = {};
-    shapes[0].type = PLTB_SHAPE_MESH; shapes[0].n_faces = n_tris;
+    shapes[0].type = PLTB_SHAPE_MESH; shapes[0].n_faces = n_tris; shapes[0].bsdf = shapes[1].bsdf = -1;
     shapes[1].type = PLTB_SHAPE_SPHERE; shapes[1].center[0] = 0.2f; shapes[1].center[1] = -0.1f; shapes[1].center[2] = 0.3f; shapes[1].radius = 0.25f;
     pltb_scene_desc d = {};
     d.n_vertices = 3 * n_tris; d.n_faces = n_tris; d.n_shapes = 2;
