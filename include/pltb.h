@@ -15,6 +15,8 @@
  *   pltb_render            <- Integrator::render (include/mitsuba/render/integrator.h:77,
  *                             src/python/python/ad/integrators/common.py:46-110) with
  *                             PLTIntegrator.sample (scripts/rendering/integrators/plt.py:492-529) inlined
+ *                             PLTB_RENDER_POLARIZED | PLTB_RENDER_STOKES: StokesIntegrator::sample (src/integrators/stokes.cpp:
+ *                             88-138) around it, driven by SamplingIntegrator::render (src/render/integrator.cpp:121-367,419-491)
  *   pltb_cancel            <- Integrator::cancel (src/render/integrator.cpp:91-93)
  *   pltb_last_error        <- Throw(...) -> std::runtime_error (include/mitsuba/core/logger.h:133-160)
  *
@@ -32,7 +34,7 @@
 extern "C" {
 #endif
 
-#define PLTB_ABI_VERSION 4
+#define PLTB_ABI_VERSION 5
 #define PLTB_MAX_DEPTH 16      /* upper bound on the `max_depth` plugin parameter (plt.py:37) */
 #define PLTB_MAX_LOBES 9       /* diffractionGratingsMaxLobes (include/mitsuba/plt/diffractiongrating.h:24) */
 
@@ -209,8 +211,13 @@ enum {
     PLTB_RENDER_DEVICE_OUT = 4,   /* film_out is a device pointer */
     PLTB_RENDER_ACCUMULATE = 8,   /* do not clear the accumulator first (multi-pass renders) */
     PLTB_RENDER_NO_SPLAT = 16,    /* skip the film (per-sample dump only) */
-    PLTB_RENDER_PROFILE = 32      /* bracket every kernel with CUDA events and fill the per-kernel ms_* fields of pltb_stats */
+    PLTB_RENDER_PROFILE = 32,     /* bracket every kernel with CUDA events and fill the per-kernel ms_* fields of pltb_stats */
+    PLTB_RENDER_POLARIZED = 64,   /* the `*_spectral_polarized` variants: Spectrum = 4x4 Mueller matrix of 4 wavelengths
+                                     (include/mitsuba/core/spectrum.h:60-95); the film still receives unpolarized_spectrum(L) */
+    PLTB_RENDER_STOKES = 128      /* with POLARIZED: the `stokes` wrapper integrator (src/integrators/stokes.cpp:88-138): 12 more film
+                                     channels S0.R S0.G S0.B ... S3.B after R G B W (raw film H*W*16, developed H*W*15) */
 };
+#define PLTB_FILM_CHANNELS(flags) (((flags) & PLTB_RENDER_STOKES) ? 16 : 4)   /* raw accumulator channels per pixel */
 
 typedef struct pltb_render_params {
     uint32_t seed;             /* mi.render(seed=) */
@@ -231,6 +238,8 @@ typedef struct pltb_sample_dump {
     float *radiance;      /* 4 per sample (PLTIntegrator.sample result, before the sensor weight), may be NULL */
     uint32_t *n_rays;     /* 2 per sample: closest-hit rays, shadow rays; may be NULL */
     uint64_t capacity;    /* number of samples the arrays can hold */
+    float *stokes;        /* PLTB_RENDER_POLARIZED only, 16 per sample, may be NULL: first column of the result Mueller matrix,
+                             [component S0..S3][wavelength] (after the sensor-frame rotation when PLTB_RENDER_STOKES is set) */
 } pltb_sample_dump;
 
 /* kernels of one wavefront pass, in launch order (csrc/pltb_kernels.cu) */

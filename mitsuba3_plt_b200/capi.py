@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libpltb200.so")
 if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu.sh ab:<suffix>)
     LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
-PLTB_ABI_VERSION = 4
+PLTB_ABI_VERSION = 5
 PLTB_MAX_DEPTH = 16
 
 # enums (include/pltb.h)
@@ -29,6 +29,12 @@ EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2, 3
 SENSOR_PERSPECTIVE, SENSOR_ORTHOGRAPHIC = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = range(3)
 RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT, RENDER_PROFILE = 1, 2, 4, 8, 16, 32
+RENDER_POLARIZED, RENDER_STOKES = 64, 128
+
+
+def film_channels(flags):
+    """raw accumulator channels per pixel (PLTB_FILM_CHANNELS)"""
+    return 16 if flags & RENDER_STOKES else 4
 
 f32, u32, i32, u64 = C.c_float, C.c_uint32, C.c_int32, C.c_uint64
 PF, PU = C.POINTER(f32), C.POINTER(u32)
@@ -84,7 +90,7 @@ KERNEL_NAMES = ["k_raygen", "k_shade<grating>", "k_shade<other>", "k_trace", "k_
 
 
 class SampleDump(C.Structure):
-    _fields_ = [("wavelengths", PF), ("radiance", PF), ("n_rays", PU), ("capacity", u64)]
+    _fields_ = [("wavelengths", PF), ("radiance", PF), ("n_rays", PU), ("capacity", u64), ("stokes", PF)]
 
 
 class Stats(C.Structure):

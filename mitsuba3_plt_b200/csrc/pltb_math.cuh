@@ -77,7 +77,8 @@ PLTB_HD V3 operator+(V3 a, V3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); 
 PLTB_HD V3 operator-(V3 a, V3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
 PLTB_HD V3 operator-(V3 a) { return mk3(-a.x, -a.y, -a.z); }
 PLTB_HD V3 operator*(V3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
-PLTB_HD V3 operator/(V3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// Dr.Jit: array / scalar is array * rcp(scalar) (ext/drjit/include/drjit/array_router.h:218-232)
+PLTB_HD V3 operator/(V3 a, float s) { const float r = rcp(s); return mk3(a.x * r, a.y * r, a.z * r); }
 PLTB_HD float dot(V3 a, V3 b) { return fmadd(a.z, b.z, fmadd(a.y, b.y, a.x * b.x)); }
 PLTB_HD float sqnorm(V3 a) { return fmadd(a.z, a.z, fmadd(a.y, a.y, a.x * a.x)); }
 PLTB_HD float norm(V3 a) { return sqrtf(sqnorm(a)); }
@@ -93,7 +94,7 @@ PLTB_HD S4 s4(float a) { S4 r; r.v[0] = r.v[1] = r.v[2] = r.v[3] = a; return r; 
 PLTB_HD S4 operator*(S4 a, S4 b) { S4 r; for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] * b.v[i]; return r; }
 PLTB_HD S4 operator*(S4 a, float b) { S4 r; for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] * b; return r; }
 PLTB_HD S4 operator+(S4 a, S4 b) { S4 r; for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] + b.v[i]; return r; }
-PLTB_HD S4 operator/(S4 a, float b) { S4 r; for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] / b; return r; }
+PLTB_HD S4 operator/(S4 a, float b) { S4 r; const float rb = rcp(b); for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] * rb; return r; }
 PLTB_HD float smax(S4 a) { return fmaxf(fmaxf(a.v[0], a.v[1]), fmaxf(a.v[2], a.v[3])); }
 
 // include/mitsuba/core/vector.h:116-136

@@ -77,7 +77,9 @@ inline V3 operator+(V3 a, V3 b) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
 inline V3 operator-(V3 a, V3 b) { return { a.x - b.x, a.y - b.y, a.z - b.z }; }
 inline V3 operator-(V3 a) { return { -a.x, -a.y, -a.z }; }
 inline V3 operator*(V3 a, float s) { return { a.x * s, a.y * s, a.z * s }; }
-inline V3 operator/(V3 a, float s) { return { a.x / s, a.y / s, a.z / s }; }
+/* Dr.Jit: array / scalar is array * rcp(scalar) ("reciprocal approximation", ext/drjit/include/drjit/array_router.h:218-232;
+ * Python: src/python/base.cpp:220-237); rcp of a scalar float is 1 / x.  Pinned by tests/golden/ref_kat_pol.json. */
+inline V3 operator/(V3 a, float s) { const float r = 1.f / s; return { a.x * r, a.y * r, a.z * r }; }
 inline float dot(V3 a, V3 b) { return fmadd(a.z, b.z, fmadd(a.y, b.y, a.x * b.x)); }
 inline float sqnorm(V3 a) { return fmadd(a.z, a.z, fmadd(a.y, a.y, a.x * a.x)); }
 inline float norm(V3 a) { return std::sqrt(sqnorm(a)); }
@@ -97,7 +99,7 @@ struct S4 {
 inline S4 operator*(S4 a, S4 b) { S4 r; for (int i = 0; i < 4; ++i) r[i] = a[i] * b[i]; return r; }
 inline S4 operator*(S4 a, float b) { S4 r; for (int i = 0; i < 4; ++i) r[i] = a[i] * b; return r; }
 inline S4 operator+(S4 a, S4 b) { S4 r; for (int i = 0; i < 4; ++i) r[i] = a[i] + b[i]; return r; }
-inline S4 operator/(S4 a, float b) { S4 r; for (int i = 0; i < 4; ++i) r[i] = a[i] / b; return r; }
+inline S4 operator/(S4 a, float b) { S4 r; const float rb = 1.f / b; for (int i = 0; i < 4; ++i) r[i] = a[i] * rb; return r; }
 inline float smax(S4 a) { return std::max(std::max(a[0], a[1]), std::max(a[2], a[3])); }
 
 /* include/mitsuba/core/vector.h:116-136 */
@@ -1275,6 +1277,46 @@ void rough_eval_pdf(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo, bo
     if (active) { value = F * v; pdf = p; }
 }
 
+/* Coherence(diffusivity, opl).inv_coherence_det(k) (include/mitsuba/plt/plt.h:27-59): det((k / (2 pi opl 1e3)) * diag(diffusivity)) */
+inline float inv_coherence_det(float k, float diffusivity, float opl) {
+    float rmm = opl * 1e+3f, s = k / (kTwoPi * rmm);
+    float d00 = s * diffusivity, d11 = s * diffusivity, d01 = s * 0.f, d10 = s * 0.f;
+    return fmsub(d00, d11, d01 * d10);
+}
+
+/* The exhaustive lobe search of RoughGrating::wbsdf_eval (roughgrating.cpp:845-896): sum over (lx, ly, wavelength) of the lobe
+ * intensities whose window contains wo, before the Fresnel factor (a Spectrum in unpolarized, a Mueller matrix in polarized
+ * variants) and specular_reflectance are applied. */
+S4 grating_lobe_sum(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
+    (void) sc;
+    Grating g = make_grating(b, si.uv);
+    V3 reflection_dir = reflect(si.wi);
+    S4 result(0.f);
+    float a = 2 * std::sqrt(b.f[1] * b.f[2]); /* texture eval_1 of alpha_u/alpha_v: unclamped */
+    int half = (int) b.u[2] / 2;
+    for (int lx = -half; lx < half + 1; lx++) {
+        for (int ly = -half; ly < half + 1; ly++) {
+            for (int i = 0; i < 4; i++) {
+                float wl = si.wavelengths[i];
+                float k = kTwoPi / (wl * 1e-3f);
+                float lobe_intensity = g.lobe_intensity(lx, ly, si.wi, wl * 1e-3f);
+                bool lobe_active; V3 center_dir = g.diffract(si.wi, lx, ly, wl * 1e-3f, lobe_active);
+                if (lx == 0 && ly == 0) {
+                    result[i] += (lobe_active && std::fabs(unit_angle(center_dir, wo)) < a) ? lobe_intensity : 0.0f;
+                } else {
+                    float det = inv_coherence_det(k, b.f[8], 1.0f);   /* Coherence3f coh(m_coherence, 1.0f), roughgrating.cpp:879 */
+                    float angle_offset = std::fabs(unit_angle(reflection_dir, wo));
+                    float inv_det = std::isnan(det) ? 0.0f : det;
+                    float angular_coh = std::exp(-0.5f * angle_offset * inv_det * angle_offset);
+                    if (std::isnan(angular_coh)) angular_coh = 0.0f;
+                    result[i] += (lobe_active && std::fabs(unit_angle(center_dir, wo)) < a) ? lobe_intensity * angular_coh : 0.0f;
+                }
+            }
+        }
+    }
+    return result;
+}
+
 /* wbsdf_eval: base -> eval (src/render/bsdf.cpp:59-71) */
 S4 bsdf_eval_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
@@ -1299,35 +1341,7 @@ S4 bsdf_eval_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
         case PLTB_BSDF_ROUGHGRATING: { /* roughgrating.cpp:676-970, spectral branch :841-969 (JIT semantics: the
                                           cos_theta tests do not mask the returned value) */
             V3 H = normalize(wo + si.wi);
-            Grating g = make_grating(b, si.uv);
-            V3 reflection_dir = reflect(si.wi);
-            S4 result(0.f);
-            Microfacet distr(b.u[0], b.f[1], b.f[2], b.u[1] != 0);
-            float a = 2 * std::sqrt(b.f[1] * b.f[2]); /* texture eval_1 of alpha_u/alpha_v: unclamped */
-            int half = (int) b.u[2] / 2;
-            for (int lx = -half; lx < half + 1; lx++) {
-                for (int ly = -half; ly < half + 1; ly++) {
-                    for (int i = 0; i < 4; i++) {
-                        float wl = si.wavelengths[i];
-                        float k = kTwoPi / (wl * 1e-3f);
-                        float lobe_intensity = g.lobe_intensity(lx, ly, si.wi, wl * 1e-3f);
-                        bool lobe_active; V3 center_dir = g.diffract(si.wi, lx, ly, wl * 1e-3f, lobe_active);
-                        if (lx == 0 && ly == 0) {
-                            result[i] += (lobe_active && std::fabs(unit_angle(center_dir, wo)) < a) ? lobe_intensity : 0.0f;
-                        } else {
-                            /* Coherence(m_coherence, 1.0).inv_coherence_det(k), include/mitsuba/plt/plt.h:57-100 */
-                            float rmm = 1.0f * 1e+3f, s = k / (kTwoPi * rmm);
-                            float d00 = s * b.f[8], d11 = s * b.f[8], d01 = s * 0.f, d10 = s * 0.f;
-                            float det = fmsub(d00, d11, d01 * d10);
-                            float angle_offset = std::fabs(unit_angle(reflection_dir, wo));
-                            float inv_det = std::isnan(det) ? 0.0f : det;
-                            float angular_coh = std::exp(-0.5f * angle_offset * inv_det * angle_offset);
-                            if (std::isnan(angular_coh)) angular_coh = 0.0f;
-                            result[i] += (lobe_active && std::fabs(unit_angle(center_dir, wo)) < a) ? lobe_intensity * angular_coh : 0.0f;
-                        }
-                    }
-                }
-            }
+            S4 result = grating_lobe_sum(sc, b, si, wo);
             S4 F = conductor_F(sc, b, si, dot(si.wi, H));
             if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], si.wavelengths, si.uv);
             return F * result;
@@ -1699,6 +1713,129 @@ S4 replay_path(const Scene &sc, const Bounce *bb, int bounce_idx) {
     return alpha;
 }
 
+/* MIS-weighted emitted radiance seen at bounce `bi` (solve_replay_emissive, plt.py:315-405, before the replayed throughput is
+ * applied): mis_weight(last_nd_pdf, pdf_emitter_direction) * emitter.eval.  False when the vertex sees no emitter. */
+bool emissive_term(const Scene &sc, const Bounce *bb, uint32_t bi, S4 &Lem) {
+    const pltb_scene_desc *d = sc.d;
+    const Bounce &b = bb[bi];
+    if (b.si.valid()) {
+        int32_t em_id = d->shapes[b.si.shape].emitter;
+        if (em_id < 0) return false;
+        const pltb_emitter &em = d->emitters[em_id];
+        bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
+        V3 prev_p = bi > 0 ? bb[bi - 1].si.p : V3(0, 0, 0);
+        /* DirectionSample3f(scene, si, prev_si), records.h:173-180 */
+        DirectionSample ds;
+        ds.p = b.si.p; ds.n = b.si.sh.n; ds.uv = b.si.uv;
+        V3 rel = b.si.p - prev_p;
+        ds.dist = norm(rel);
+        ds.d = rel / ds.dist;
+        /* Scene::pdf_emitter_direction (scene.cpp:350-361) -> AreaLight::pdf_direction (area.cpp:170-196) */
+        float em_pdf = 0.f;
+        if (!prev_delta) {
+            float dp = dot(ds.d, ds.n);
+            if (dp < 0.f) em_pdf = shape_pdf_direction(d->shapes[em.shape], prev_p, ds);
+            em_pdf *= sc.emitter_pmf;
+        }
+        float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
+        /* AreaLight::eval, area.cpp:82-89 */
+        S4 Le = b.si.wi.z > 0.f ? emitter_radiance(sc, em, b.si.wavelengths, b.si.uv) : S4(0.f);
+        Lem = Le * mis_bsdf;
+        return true;
+    }
+    if (sc.env < 0) return false;
+    /* the ray escaped: si.emitter(scene) is the environment (interaction.h:343-346); DirectionSample3f(scene, si, prev_si)
+     * takes d = -si.wi (records.h:173-180) */
+    const pltb_emitter &em = d->emitters[sc.env];
+    bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
+    /* ConstantBackgroundEmitter::pdf_direction (constant.cpp:152-157) / EnvironmentMapEmitter (envmap.cpp:468-484) */
+    float em_pdf = 0.f;
+    if (!prev_delta)
+        em_pdf = (em.type == PLTB_EMITTER_ENVMAP ? envmap_pdf_direction(sc, em, -b.si.wi) : kInvFourPi) * sc.emitter_pmf;
+    float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
+    S4 Le;
+    if (em.type == PLTB_EMITTER_ENVMAP) /* ::eval, envmap.cpp:343-353 */
+        Le = envmap_eval_spectrum(sc, em, envmap_dir_to_uv(xf_vector(em.to_local, -b.si.wi)), b.si.wavelengths);
+    else
+        Le = emitter_radiance(sc, em, b.si.wavelengths, V2{ 0.f, 0.f }); /* ::eval, constant.cpp:92-96 */
+    Lem = Le * mis_bsdf;
+    return true;
+}
+
+/* The emitter half of solve_replay_NEE (plt.py:221-269) for one recorded bounce: Scene::sample_emitter_direction with its
+ * shadow ray, the re-evaluated emitter value and em_weight = em_val / ds.pdf.  False when NEE is inactive for the vertex. */
+struct NeeSample { S4 em_weight; V3 wo; float pdf = 0.f; bool delta = false; };
+bool nee_light_sample(const Scene &sc, const Bounce &b, V2 u2, Counters &cnt, NeeSample &out) {
+    const pltb_scene_desc *d = sc.d;
+    bool active_em = b.active && (b.flags & F_Smooth) != 0;
+    if (!(active_em && d->n_emitters > 0)) return false;
+    const SI &si = b.si;
+    /* Scene::sample_emitter_direction (scene.cpp:294-348) + sample_emitter (:222-245) */
+    uint32_t index = 0;
+    V2 sample = u2;
+    if (d->n_emitters > 1) {
+        float cf = (float) d->n_emitters, scaled = sample.x * cf;
+        index = std::min((uint32_t) scaled, d->n_emitters - 1u);
+        sample.x = scaled - (float) index;
+    }
+    const pltb_emitter &em = d->emitters[index];
+    DirectionSample ds;
+    if (em.type == PLTB_EMITTER_AREA) {
+        ds = shape_sample_direction(sc, d->shapes[em.shape], si.p, sample); /* area.cpp:116-168 */
+    } else if (em.type == PLTB_EMITTER_CONSTANT) { /* ::sample_direction, constant.cpp:121-150 */
+        V3 dir = square_to_uniform_sphere(sample);
+        V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+        float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
+        ds.p = fmadd(dir, dist, si.p);
+        ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
+    } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::sample_direction, envmap.cpp:421-466 */
+        Hier2D warp(d->tex_data + em.env_warp);
+        V2 uv; float pdf;
+        warp.sample(sample, uv, pdf);
+        uv.x += .5f / (float) (em.env_res[0] - 1u);
+        bool act_s = pdf > 0.f;
+        float theta = uv.y * kPi, phi = uv.x * (2.f * kPi);
+        float st = std::sin(theta), ct = std::cos(theta), sp = std::sin(phi), cp = std::cos(phi);
+        V3 sd(cp * st, sp * st, ct); /* dr::sphdir */
+        V3 dl(sd.y, sd.z, -sd.x);
+        V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+        float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
+        float inv_sin_theta = envmap_inv_sin_theta(dl);
+        V3 dw = xf_vector(em.to_world, dl);
+        ds.p = si.p + dw * dist;
+        ds.n = -dw; ds.uv = uv; ds.delta = false; ds.d = dw; ds.dist = dist;
+        ds.pdf = act_s ? pdf * inv_sin_theta * (1.f / (2.f * sqr(kPi))) : 0.f;
+    } else { /* DirectionalEmitter::sample_direction, src/emitters/directional.cpp:149-176 */
+        V3 dirn(em.direction[0], em.direction[1], em.direction[2]);
+        ds.d = -dirn;
+        float dist = 2.f * em.bsphere_radius;
+        ds.p = fmadd(ds.d, dist, si.p);
+        ds.n = dirn; ds.pdf = 1.f; ds.delta = true; ds.dist = dist;
+    }
+    ds.emitter = (int32_t) index;
+    ds.pdf *= sc.emitter_pmf;
+    if (ds.pdf != 0.f) {
+        cnt.shadow++;
+        Ray sr = si.spawn_ray_to(ds.p);
+        Hit sh = intersect(sc, sr, true);
+        if (sh.shape >= 0) ds.pdf = 0.f;
+    }
+    /* back in plt.py:264-269 */
+    ds.d = normalize(ds.p - si.p);
+    S4 em_val(0.f);
+    if (em.type == PLTB_EMITTER_AREA) { /* AreaLight::eval_direction, area.cpp:198-208 */
+        if (dot(ds.d, ds.n) < 0.f) em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
+    } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::eval_direction, envmap.cpp:486-491 */
+        em_val = envmap_eval_spectrum(sc, em, ds.uv, si.wavelengths);
+    } else { /* DirectionalEmitter / ConstantBackgroundEmitter::eval_direction (directional.cpp:189-195) */
+        em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
+    }
+    out.em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : S4(0.f);
+    out.wo = si.to_local(ds.d);
+    out.pdf = ds.pdf; out.delta = ds.delta;
+    return true;
+}
+
 static void trace_nonfinite(const Scene &sc, const Bounce *bb, uint32_t n_written, uint32_t bi, const char *term, const S4 &mis,
                             const S4 &emitter, const S4 &bsdf_val, const S4 &alpha) {
     FILE *f = nan_trace_file();
@@ -1719,7 +1856,6 @@ static void trace_nonfinite(const Scene &sc, const Bounce *bb, uint32_t n_writte
 
 S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint32_t max_depth, uint32_t rr_depth,
               Counters &cnt) {
-    const pltb_scene_desc *d = sc.d;
     Bounce bb[PLTB_MAX_DEPTH];
 
     /* ---- plt_sample_phase, plt.py:50-171 ---- */
@@ -1771,139 +1907,32 @@ S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint3
     for (uint32_t bi = 0; bi < max_depth; ++bi) {
         bool written = bi < n_written; /* unwritten slots: all-zero, active = false (N4) */
         /* solve_replay_emissive, :315-405 */
-        if (written) {
-            const Bounce &b = bb[bi];
-            if (b.si.valid()) {
-                int32_t em_id = d->shapes[b.si.shape].emitter;
-                if (em_id >= 0) {
-                    const pltb_emitter &em = d->emitters[em_id];
-                    bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
-                    V3 prev_p = bi > 0 ? bb[bi - 1].si.p : V3(0, 0, 0);
-                    /* DirectionSample3f(scene, si, prev_si), records.h:173-180 */
-                    DirectionSample ds;
-                    ds.p = b.si.p; ds.n = b.si.sh.n; ds.uv = b.si.uv;
-                    V3 rel = b.si.p - prev_p;
-                    ds.dist = norm(rel);
-                    ds.d = rel / ds.dist;
-                    /* Scene::pdf_emitter_direction (scene.cpp:350-361) -> AreaLight::pdf_direction (area.cpp:170-196) */
-                    float em_pdf = 0.f;
-                    if (!prev_delta) {
-                        float dp = dot(ds.d, ds.n);
-                        if (dp < 0.f) em_pdf = shape_pdf_direction(d->shapes[em.shape], prev_p, ds);
-                        em_pdf *= sc.emitter_pmf;
-                    }
-                    float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
-                    /* AreaLight::eval, area.cpp:82-89 */
-                    S4 Le = b.si.wi.z > 0.f ? emitter_radiance(sc, em, b.si.wavelengths, b.si.uv) : S4(0.f);
-                    S4 Lem = Le * mis_bsdf;
-                    S4 a = replay_path(sc, bb, (int) bi);
-                    L = L + a * Lem;
-                    if (nan_trace_file() && !s4_finite(a * Lem))
-                        trace_nonfinite(sc, bb, n_written, bi, "emissive", S4(mis_bsdf), Le, S4(1.f), a);
-                }
-            } else if (sc.env >= 0) {
-                /* the ray escaped: si.emitter(scene) is the environment (interaction.h:343-346); DirectionSample3f(scene, si,
-                 * prev_si) takes d = -si.wi (records.h:173-180) */
-                const pltb_emitter &em = d->emitters[sc.env];
-                bool prev_delta = bi > 0 ? (bb[bi - 1].flags & F_Delta) != 0 : true;
-                /* ConstantBackgroundEmitter::pdf_direction (constant.cpp:152-157) / EnvironmentMapEmitter (envmap.cpp:468-484) */
-                float em_pdf = 0.f;
-                if (!prev_delta)
-                    em_pdf = (em.type == PLTB_EMITTER_ENVMAP ? envmap_pdf_direction(sc, em, -b.si.wi) : kInvFourPi) * sc.emitter_pmf;
-                float mis_bsdf = mis_weight(b.last_nd_pdf, em_pdf);
-                S4 Le;
-                if (em.type == PLTB_EMITTER_ENVMAP) /* ::eval, envmap.cpp:343-353 */
-                    Le = envmap_eval_spectrum(sc, em, envmap_dir_to_uv(xf_vector(em.to_local, -b.si.wi)), b.si.wavelengths);
-                else
-                    Le = emitter_radiance(sc, em, b.si.wavelengths, V2{ 0.f, 0.f }); /* ::eval, constant.cpp:92-96 */
-                S4 a = replay_path(sc, bb, (int) bi);
-                L = L + a * (Le * mis_bsdf);
-            }
+        S4 Lem;
+        if (written && emissive_term(sc, bb, bi, Lem)) {
+            S4 a = replay_path(sc, bb, (int) bi);
+            L = L + a * Lem;
+            if (nan_trace_file() && !s4_finite(a * Lem))
+                trace_nonfinite(sc, bb, n_written, bi, "emissive", S4(1.f), Lem, S4(1.f), a);
         }
         /* solve_replay_NEE, :221-300 */
         V2 u2; u2.x = rng.next_float32(); u2.y = rng.next_float32(); /* drawn for every i, every lane */
-        if (written) {
-            const Bounce &b = bb[bi];
-            bool active_em = b.active && (b.flags & F_Smooth) != 0;
-            if (active_em && d->n_emitters > 0) {
-                const SI &si = b.si;
-                /* Scene::sample_emitter_direction (scene.cpp:294-348) + sample_emitter (:222-245) */
-                uint32_t index = 0; float emitter_weight = 1.f;
-                V2 sample = u2;
-                if (d->n_emitters > 1) {
-                    float cf = (float) d->n_emitters, scaled = sample.x * cf;
-                    index = std::min((uint32_t) scaled, d->n_emitters - 1u);
-                    emitter_weight = cf;
-                    sample.x = scaled - (float) index;
-                }
-                const pltb_emitter &em = d->emitters[index];
-                DirectionSample ds;
-                if (em.type == PLTB_EMITTER_AREA) {
-                    ds = shape_sample_direction(sc, d->shapes[em.shape], si.p, sample); /* area.cpp:116-168 */
-                } else if (em.type == PLTB_EMITTER_CONSTANT) { /* ::sample_direction, constant.cpp:121-150 */
-                    V3 dir = square_to_uniform_sphere(sample);
-                    V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
-                    float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
-                    ds.p = fmadd(dir, dist, si.p);
-                    ds.n = -dir; ds.uv = sample; ds.pdf = kInvFourPi; ds.delta = false; ds.d = dir; ds.dist = dist;
-                } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::sample_direction, envmap.cpp:421-466 */
-                    Hier2D warp(d->tex_data + em.env_warp);
-                    V2 uv; float pdf;
-                    warp.sample(sample, uv, pdf);
-                    uv.x += .5f / (float) (em.env_res[0] - 1u);
-                    bool act_s = pdf > 0.f;
-                    float theta = uv.y * kPi, phi = uv.x * (2.f * kPi);
-                    float st = std::sin(theta), ct = std::cos(theta), sp = std::sin(phi), cp = std::cos(phi);
-                    V3 sd(cp * st, sp * st, ct); /* dr::sphdir */
-                    V3 dl(sd.y, sd.z, -sd.x);
-                    V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
-                    float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
-                    float inv_sin_theta = envmap_inv_sin_theta(dl);
-                    V3 dw = xf_vector(em.to_world, dl);
-                    ds.p = si.p + dw * dist;
-                    ds.n = -dw; ds.uv = uv; ds.delta = false; ds.d = dw; ds.dist = dist;
-                    ds.pdf = act_s ? pdf * inv_sin_theta * (1.f / (2.f * sqr(kPi))) : 0.f;
-                } else { /* DirectionalEmitter::sample_direction, src/emitters/directional.cpp:149-176 */
-                    V3 dirn(em.direction[0], em.direction[1], em.direction[2]);
-                    ds.d = -dirn;
-                    float dist = 2.f * em.bsphere_radius;
-                    ds.p = fmadd(ds.d, dist, si.p);
-                    ds.n = dirn; ds.pdf = 1.f; ds.delta = true; ds.dist = dist;
-                }
-                ds.emitter = (int32_t) index;
-                ds.pdf *= sc.emitter_pmf;
-                (void) emitter_weight;
-                bool act = ds.pdf != 0.f;
-                if (act) {
-                    cnt.shadow++;
-                    Ray sr = si.spawn_ray_to(ds.p);
-                    Hit sh = intersect(sc, sr, true);
-                    if (sh.shape >= 0) ds.pdf = 0.f;
-                }
-                /* back in plt.py:264-269 */
-                ds.d = normalize(ds.p - si.p);
-                S4 em_val(0.f);
-                if (em.type == PLTB_EMITTER_AREA) { /* AreaLight::eval_direction, area.cpp:198-208 */
-                    if (dot(ds.d, ds.n) < 0.f) em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
-                } else if (em.type == PLTB_EMITTER_ENVMAP) { /* ::eval_direction, envmap.cpp:486-491 */
-                    em_val = envmap_eval_spectrum(sc, em, ds.uv, si.wavelengths);
-                } else { /* DirectionalEmitter / ConstantBackgroundEmitter::eval_direction (directional.cpp:189-195) */
-                    em_val = emitter_radiance(sc, em, si.wavelengths, ds.uv);
-                }
-                S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : S4(0.f);
-                V3 wo = si.to_local(ds.d);
-                S4 bsdf_val = wbsdf_eval(sc, si, wo);
-                float bsdf_pdf = wbsdf_pdf(sc, si, wo);
-                float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-                S4 a = replay_path(sc, bb, (int) bi);
-                L = L + ((em_weight * mis_em) * bsdf_val) * a;
-                if (nan_trace_file() && !s4_finite(((em_weight * mis_em) * bsdf_val) * a))
-                    trace_nonfinite(sc, bb, n_written, bi, "nee", S4(mis_em), em_weight, bsdf_val, a);
-            }
+        NeeSample ns;
+        if (written && nee_light_sample(sc, bb[bi], u2, cnt, ns)) {
+            const SI &si = bb[bi].si;
+            S4 bsdf_val = wbsdf_eval(sc, si, ns.wo);
+            float bsdf_pdf = wbsdf_pdf(sc, si, ns.wo);
+            float mis_em = ns.delta ? 1.0f : mis_weight(ns.pdf, bsdf_pdf);
+            S4 a = replay_path(sc, bb, (int) bi);
+            L = L + ((ns.em_weight * mis_em) * bsdf_val) * a;
+            if (nan_trace_file() && !s4_finite(((ns.em_weight * mis_em) * bsdf_val) * a))
+                trace_nonfinite(sc, bb, n_written, bi, "nee", S4(mis_em), ns.em_weight, bsdf_val, a);
         }
     }
     return L;
 }
+
+void spectrum_to_srgb(const float *cie_srgb, const S4 &value, const S4 &wl, float rgb[3]);
+#include "plt_oracle_pol.inc"
 
 /* ------------------------------------------------------------------------------------------------------------
  * Sensor + film
@@ -2000,11 +2029,11 @@ inline float rfilter_eval(const pltb_film &f, float x) {
 }
 
 /* ImageBlock::put, coalesced path (src/render/imageblock.cpp:429-500); film has no border. */
-void splat(const pltb_film &f, uint32_t W, uint32_t H, float *film, V2 pos, const float values[4]) {
+void splat(const pltb_film &f, uint32_t W, uint32_t H, float *film, V2 pos, const float *values, int nch = 4) {
     if (f.rfilter == PLTB_RFILTER_BOX) {
         int x = (int) std::floor(pos.x), y = (int) std::floor(pos.y);
         if (x < 0 || y < 0 || x >= (int) W || y >= (int) H) return;
-        for (int k = 0; k < 4; ++k) film[4 * ((size_t) y * W + x) + k] += values[k];
+        for (int k = 0; k < nch; ++k) film[nch * ((size_t) y * W + x) + k] += values[k];
         return;
     }
     int n = (int) std::ceil(f.radius - .5f), count = 2 * n + 1;
@@ -2022,8 +2051,8 @@ void splat(const pltb_film &f, uint32_t W, uint32_t H, float *film, V2 pos, cons
             int x = px + xs;
             if (x < 0 || x >= (int) W) continue;
             float w = wy[ys] * wx[xs];
-            float *dst = film + 4 * ((size_t) y * W + x);
-            for (int k = 0; k < 4; ++k) dst[k] += values[k] * w;
+            float *dst = film + nch * ((size_t) y * W + x);
+            for (int k = 0; k < nch; ++k) dst[k] += values[k] * w;
         }
     }
 }
@@ -2065,7 +2094,9 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
     if (n_threads <= 0) n_threads = 1;
     const uint32_t max_depth = std::min<uint32_t>(prm->max_depth, PLTB_MAX_DEPTH);
     std::vector<std::vector<float>> films;
-    if (film_rgbw && !(prm->flags & PLTB_RENDER_NO_SPLAT)) films.assign(n_threads, std::vector<float>((size_t) W * H * 4, 0.f));
+    const bool polarized = (prm->flags & PLTB_RENDER_POLARIZED) != 0, stokes = polarized && (prm->flags & PLTB_RENDER_STOKES) != 0;
+    const int nch = PLTB_FILM_CHANNELS(stokes ? PLTB_RENDER_STOKES : 0);
+    if (film_rgbw && !(prm->flags & PLTB_RENDER_NO_SPLAT)) films.assign(n_threads, std::vector<float>((size_t) W * H * nch, 0.f));
     std::vector<Counters> counters(n_threads);
     std::atomic<uint32_t> next_row{ 0 };
     auto t0 = std::chrono::steady_clock::now();
@@ -2093,7 +2124,23 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
                     sample_wavelengths(sc, sn, wav_sample, wl, wgt);
                     Ray ray = sensor_ray(sn, pos_adj);
                     Counters c0 = cnt;
-                    S4 L = plt_sample(sc, rng, ray, wl, max_depth, prm->rr_depth, cnt);
+                    S4 L;
+                    float values[16];
+                    if (polarized) {
+                        M4 Lm = plt_sample_pol(sc, rng, ray, wl, max_depth, prm->rr_depth, cnt);
+                        /* scene->sensors()[0]->world_transform() (stokes.cpp:100-102); a `batch` sensor's own transform is the
+                         * identity in every config that uses one */
+                        static const float ident[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+                        if (stokes) Lm = stokes_aovs(sc, Lm, ray, wl, desc->n_sensors > 1 ? ident : desc->sensors[0].to_world, values + 4);
+                        L = Lm.e[0][0];   /* unpolarized_spectrum(spec), integrator.cpp:456 */
+                        if (dump && dump->stokes) {
+                            uint64_t di = ((uint64_t) row * cw + (x - cx)) * prm->spp_count + (s - prm->spp_begin);
+                            if (di < dump->capacity)
+                                for (int c = 0; c < 4; ++c) for (int k = 0; k < 4; ++k) dump->stokes[16 * di + 4 * c + k] = Lm.e[c][0][k];
+                        }
+                    } else {
+                        L = plt_sample(sc, rng, ray, wl, max_depth, prm->rr_depth, cnt);
+                    }
                     if (dump) {
                         uint64_t di = ((uint64_t) row * cw + (x - cx)) * prm->spp_count + (s - prm->spp_begin);
                         if (di < dump->capacity) {
@@ -2106,10 +2153,9 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
                         }
                     }
                     if (!films.empty()) {
-                        float values[4];
                         spectrum_to_srgb(desc->cie_srgb, L * wgt, wl, values);
                         values[3] = 1.f;
-                        splat(desc->film, W, H, films[tid].data(), pos_f, values);
+                        splat(desc->film, W, H, films[tid].data(), pos_f, values, nch);
                     }
                 }
             }
@@ -2122,7 +2168,7 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
     double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (!films.empty()) {
         bool accumulate = (prm->flags & PLTB_RENDER_ACCUMULATE) != 0;
-        for (size_t i = 0; i < (size_t) W * H * 4; ++i) {
+        for (size_t i = 0; i < (size_t) W * H * nch; ++i) {
             float acc = accumulate ? film_rgbw[i] : 0.f;
             for (int t = 0; t < n_threads; ++t) acc += films[t][i];
             film_rgbw[i] = acc;
@@ -2138,6 +2184,16 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
         stats->ms_total = (float) (secs * 1e3);
     }
     return secs;
+}
+
+/* HDRFilm::develop (src/films/hdrfilm.cpp:304-400) with AOV channels: every channel / (w == 0 ? 1 : w), W dropped */
+void plt_oracle_develop_n(const float *raw, uint64_t n_pixels, int nch, float *out) {
+    for (uint64_t i = 0; i < n_pixels; ++i) {
+        float w = raw[nch * i + 3];
+        float d = w == 0.f ? 1.f : w;
+        int o = 0;
+        for (int c = 0; c < nch; ++c) if (c != 3) out[(nch - 1) * i + o++] = raw[nch * i + c] / d;
+    }
 }
 
 /* HDRFilm::develop (src/films/hdrfilm.cpp:304-400): rgb / (w == 0 ? 1 : w) */
@@ -2242,6 +2298,49 @@ void plt_oracle_envmap_probe(const pltb_scene_desc *d, const float *u, const flo
     out[3] = envmap_eval_spectrum(sc, em, uv, wl)[0];
     out[4] = dw.x; out[5] = dw.y; out[6] = dw.z;
 }
+/* ---- polarized building blocks and further header-level functions (pinned on tests/golden/ref_kat_pol.json) ---- */
+static void m4_store(const M4 &m, float *out) { for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) for (int k = 0; k < 4; ++k) out[16 * i + 4 * j + k] = m.e[i][j][k]; }
+static M4 m4_load(const float *in) { M4 m; for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) for (int k = 0; k < 4; ++k) m.e[i][j][k] = in[16 * i + 4 * j + k]; return m; }
+void plt_oracle_array_div(const float *v3, const float *s4v, float s, float *out) {
+    V3 v = V3(v3[0], v3[1], v3[2]) / s; S4 sp; for (int k = 0; k < 4; ++k) sp[k] = s4v[k]; sp = sp / s;
+    out[0] = v.x; out[1] = v.y; out[2] = v.z; for (int k = 0; k < 4; ++k) out[3 + k] = sp[k];
+}
+void plt_oracle_m4_ops(const float *a, const float *b, const float *s4v, float f, float *out) {   /* out: 7 matrices of 64 floats */
+    M4 A = m4_load(a), B = m4_load(b); S4 s; for (int k = 0; k < 4; ++k) s[k] = s4v[k];
+    m4_store(A * B, out); m4_store(m4_diag(s), out + 64); m4_store(m4_scale(A, s), out + 128); m4_store(m4_div(A, f), out + 192);
+    m4_store(m4_depolarizer(s), out + 256); m4_store(A * m4_absorber(s), out + 320); m4_store(m4_transpose(A), out + 384);
+}
+void plt_oracle_fresnel_polarized_real(float c, float eta, float *out) {
+    FresnelPol f = fresnel_polarized(c, eta);
+    out[0] = f.a_s.re; out[1] = f.a_s.im; out[2] = f.a_p.re; out[3] = f.a_p.im; out[4] = f.cos_theta_t; out[5] = f.eta_it; out[6] = f.eta_ti;
+}
+void plt_oracle_fresnel_polarized_complex(float c, float eta, float k, float *out) {
+    FresnelPol f = fresnel_polarized(c, cx(eta, k));
+    out[0] = f.a_s.re; out[1] = f.a_s.im; out[2] = f.a_p.re; out[3] = f.a_p.im; out[4] = f.cos_theta_t;
+}
+void plt_oracle_specular_reflection_complex(float c, float eta, float k, float *out) { m4_store(specular_reflection(S4(c), S4(eta), S4(k)), out); }
+void plt_oracle_specular_reflection_real(float c, float eta, float *out) { m4_store(specular_reflection(c, eta), out); }
+void plt_oracle_specular_transmission(float c, float eta, float *out) { m4_store(specular_transmission(c, eta), out); }
+void plt_oracle_stokes_basis(const float *d, float *out) { V3 b = stokes_basis(V3(d[0], d[1], d[2])); out[0] = b.x; out[1] = b.y; out[2] = b.z; }
+void plt_oracle_rotate_stokes_basis(const float *f, const float *c, const float *t, float *out) {
+    m4_store(rotate_stokes_basis(V3(f[0], f[1], f[2]), V3(c[0], c[1], c[2]), V3(t[0], t[1], t[2])), out);
+}
+void plt_oracle_align_stokes_frames(const float *m, const float *n, const float *wo_hat, const float *wi_hat, float *out) {
+    m4_store(align_stokes_frames(m4_load(m), V3(n[0], n[1], n[2]), V3(wo_hat[0], wo_hat[1], wo_hat[2]), V3(wi_hat[0], wi_hat[1], wi_hat[2])), out);
+}
+float plt_oracle_pdf_rgb_spectrum(float wl) { return pdf_rgb_spectrum(wl); }
+void plt_oracle_warp(const float *u, float *out) {   /* disk_concentric[2] cosine_hemisphere[3] uniform_sphere[3] uniform_triangle[2] */
+    V2 s{ u[0], u[1] };
+    V2 d = square_to_uniform_disk_concentric(s); V3 c = square_to_cosine_hemisphere(s), sp = square_to_uniform_sphere(s); V2 t = square_to_uniform_triangle(s);
+    out[0] = d.x; out[1] = d.y; out[2] = c.x; out[3] = c.y; out[4] = c.z; out[5] = sp.x; out[6] = sp.y; out[7] = sp.z; out[8] = t.x; out[9] = t.y;
+}
+void plt_oracle_coordinate_system(const float *n, float *out) {
+    V3 s, t; coordinate_system(V3(n[0], n[1], n[2]), s, t);
+    out[0] = s.x; out[1] = s.y; out[2] = s.z; out[3] = t.x; out[4] = t.y; out[5] = t.z;
+}
+float plt_oracle_unit_angle(const float *a, const float *b) { return unit_angle(V3(a[0], a[1], a[2]), V3(b[0], b[1], b[2])); }
+float plt_oracle_inv_coherence_det(float k, float diffusivity, float opl) { return inv_coherence_det(k, diffusivity, opl); }
+
 float plt_oracle_rfilter_eval(uint32_t type, float radius, float stddev, float x) {
     pltb_film f{}; f.rfilter = type; f.radius = radius; f.stddev = stddev;
     return rfilter_eval(f, x);

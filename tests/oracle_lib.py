@@ -28,6 +28,7 @@ def lib():
         L.plt_oracle_render.argtypes = [C.POINTER(capi.SceneDesc), C.POINTER(capi.RenderParams), C.c_void_p,
                                         C.POINTER(capi.SampleDump), C.POINTER(capi.Stats), C.c_int]
         L.plt_oracle_develop.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.plt_oracle_develop_n.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
         f, i, u = C.c_float, C.c_int, C.c_uint32
         PF = C.POINTER(C.c_float)
         for name, res, args in [
@@ -58,8 +59,10 @@ def farr(*v):
 
 
 def render(flat, spp, seed=0, max_depth=7, rr_depth=50, spp_begin=0, spp_count=None, crop=None, dump=False,
-           film=True, n_threads=0):
-    """Run the oracle on a FlatScene.  Returns dict(film_rgbw, image, wavelengths, radiance, n_rays, stats, seconds)."""
+           film=True, n_threads=0, polarized=False, stokes=False):
+    """Run the oracle on a FlatScene.  Returns dict(film_rgbw, image, wavelengths, radiance, n_rays, stats, seconds).
+    polarized: the `*_spectral_polarized` variant (Mueller-matrix Spectrum); stokes: the `stokes` wrapper integrator around it
+    (film_rgbw then has 16 channels R G B W S0.RGB .. S3.RGB, image 15, and the dump gains 'stokes' (n, 4, 4))."""
     from mitsuba3_plt_b200 import capi
     L = lib()
     d = flat.desc
@@ -70,6 +73,9 @@ def render(flat, spp, seed=0, max_depth=7, rr_depth=50, spp_begin=0, spp_count=N
     prm.max_depth, prm.rr_depth = max_depth, rr_depth
     cx, cy, cw, ch = crop if crop else (0, 0, W, H)
     prm.crop_x, prm.crop_y, prm.crop_w, prm.crop_h = cx, cy, cw, ch
+    if polarized:
+        prm.flags |= capi.RENDER_POLARIZED | (capi.RENDER_STOKES if stokes else 0)
+    nch = capi.film_channels(prm.flags)
     out = {}
     dmp = None
     if dump:
@@ -77,7 +83,10 @@ def render(flat, spp, seed=0, max_depth=7, rr_depth=50, spp_begin=0, spp_count=N
         out["wavelengths"] = np.zeros((n, 4), np.float32); out["radiance"] = np.zeros((n, 4), np.float32)
         out["n_rays"] = np.zeros((n, 2), np.uint32)
         dmp = capi.SampleDump(capi.fptr(out["wavelengths"]), capi.fptr(out["radiance"]), capi.uptr(out["n_rays"]), n)
-    fbuf = np.zeros((H, W, 4), np.float32) if film else None
+        if polarized:
+            out["stokes"] = np.zeros((n, 4, 4), np.float32)
+            dmp.stokes = capi.fptr(out["stokes"])
+    fbuf = np.zeros((H, W, nch), np.float32) if film else None
     if not film:
         prm.flags |= capi.RENDER_NO_SPLAT
     st = capi.Stats()
@@ -85,7 +94,7 @@ def render(flat, spp, seed=0, max_depth=7, rr_depth=50, spp_begin=0, spp_count=N
                                C.byref(dmp) if dmp else None, C.byref(st), n_threads)
     out["seconds"], out["stats"] = secs, st.as_dict()
     if film:
-        img = np.zeros((H, W, 3), np.float32)
-        L.plt_oracle_develop(fbuf.ctypes.data, W * H, img.ctypes.data)
+        img = np.zeros((H, W, nch - 1), np.float32)
+        L.plt_oracle_develop_n(fbuf.ctypes.data, W * H, nch, img.ctypes.data)
         out["film_rgbw"], out["image"] = fbuf, img
     return out
