@@ -360,3 +360,23 @@ def test_nonfinite_samples_all_trace_to_invalid_lobes():
     for r in recs:
         assert any(not b["lobe_valid"] and abs(b["wo_norm"] - 1) > 1e-3 for b in r["path"][:-1]), r
         assert r["alpha"] == 0 or r["first_nonfinite_factor"] == "replay_alpha", r
+
+
+def test_disk_scene_polarized_variant_has_no_nonfinite_samples(mi, oracle, tmp_path):
+    """the reference's only linear-float grating fixture, results/disk/result_s3.exr (polarized CUDA
+    variant, 1.97e9 samples), has 0 non-finite pixels.  The reference's scenes/disk/disk.xml (procedural sky for the missing EXR
+    blob) through the oracle: the polarized variant -- what that fixture was rendered with -- produces none, the unpolarized
+    variant produces the fresnel_conductor(cos > 1) 0 * inf samples DESIGN.md section 5 accounts for."""
+    import shutil
+    from mitsuba3_plt_b200 import imageio, scenes
+    d = tmp_path / "disk"
+    shutil.copytree(os.path.join(ROOT, "tests", "golden", "scenes", "disk"), d)
+    imageio.write_exr(str(d / "textures" / "empty_play_room.exr"), scenes.procedural_sky(64, 32), compression="zip")
+    sc = mi.load_file(str(d / "disk.xml"), resx=200, resy=150)
+    pol = oracle.render(sc.flat, 64, seed=0, dump=True, polarized=True, stokes=True)
+    assert np.isfinite(pol["radiance"]).all() and np.isfinite(pol["stokes"]).all() and np.isfinite(pol["image"]).all()
+    assert pol["image"].shape == (150, 200, 15)
+    unp = oracle.render(sc.flat, 64, seed=0, dump=True)
+    assert 1 <= (~np.isfinite(unp["radiance"])).any(axis=1).sum() <= 10
+    # the same paths were traced: the Spectrum type does not enter any sampling decision of this scene
+    assert (pol["n_rays"] == unp["n_rays"]).all()
