@@ -31,22 +31,26 @@ from .xmlscene import Color, Properties, SpectrumValue, Transform, dict_to_tree,
 
 __all__ = ["set_variant", "variant", "load_file", "load_dict", "render", "traverse", "register_integrator",
            "PLTIntegrator", "Scene", "Properties", "ScalarTransform4f", "Transform4f", "Context", "context",
-           "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized"]
+           "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized", "StokesIntegrator"]
 
 ScalarTransform4f = Transform4f = Transform
 
-_SUPPORTED_VARIANTS = ("cuda_spectral", "cuda_ad_spectral", "llvm_spectral", "llvm_ad_spectral", "scalar_spectral")
+_SUPPORTED_VARIANTS = ("cuda_spectral", "cuda_ad_spectral", "llvm_spectral", "llvm_ad_spectral", "scalar_spectral",
+                       "cuda_spectral_polarized", "cuda_ad_spectral_polarized", "llvm_spectral_polarized",
+                       "llvm_ad_spectral_polarized", "scalar_spectral_polarized")
 _variant = "cuda_spectral"
 is_spectral, is_polarized = True, False
 
 
 def set_variant(*names):
-    """mi.set_variant: the build implements the unpolarized 4-wavelength spectral variants only (SURVEY.md fact 2);
-    every accepted name runs the same CUDA path."""
-    global _variant
+    """mi.set_variant: the 4-wavelength spectral variants, unpolarized and polarized (Spectrum = Mueller matrix; what
+    scripts/rendering/main-headless.py:128-130 selects); every accepted name runs the same CUDA path, the `_polarized`
+    suffix switches the kernels to Mueller arithmetic (PLTB_RENDER_POLARIZED)."""
+    global _variant, is_polarized
     for n in names:
         if n in _SUPPORTED_VARIANTS:
             _variant = n
+            is_polarized = n.endswith("_polarized")
             return
     raise ImportError(f"Requested an unsupported variant {names!r}. The following variants are available: "
                       f"{', '.join(_SUPPORTED_VARIANTS)}.")
@@ -264,7 +268,7 @@ class PLTIntegrator:
             capi.lib().pltb_cancel(self._cancel_ctx._h)
 
     def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, *, ctx=None, dump=None, crop=None,
-               reduce=True, profile=False, download=True, out=None):
+               reduce=True, profile=False, download=True, out=None, _stokes=False):
         """Returns the developed image (H, W, 3) float32, or the raw RGBW accumulator (H, W, 4) if develop=False.
         `dump`: optional dict that receives per-sample 'wavelengths', 'radiance' and 'n_rays' arrays (parity mode).
         Multi-GPU: the spp range is sharded over the ranks of `ctx`; rank 0 returns the image, the others None."""
@@ -283,7 +287,9 @@ class PLTIntegrator:
         # wavefront limit of the reference (common.py:358-363); larger renders are split into sub-renders with
         # consecutive seeds whose raw accumulators are summed (SURVEY.md 8b "Seed/pass convention")
         n_sub, sub_spp = split_subrenders(W, H, spp)
-        shape = (H, W, 3 if develop else 4)
+        mode = (capi.RENDER_POLARIZED if is_polarized else 0) | (capi.RENDER_STOKES if _stokes else 0)
+        nch = capi.film_channels(mode)
+        shape = (H, W, nch - 1 if develop else nch)
         if out is not None:
             if out.shape != shape or out.dtype != np.float32 or not out.flags.c_contiguous:
                 raise RuntimeError(f"render(): `out` must be a C-contiguous float32 array of shape {shape}")
@@ -302,7 +308,7 @@ class PLTIntegrator:
                 if crop:
                     prm.crop_x, prm.crop_y, prm.crop_w, prm.crop_h = crop
                 last = k == n_sub - 1
-                flags = 0
+                flags = mode
                 if k > 0:
                     flags |= capi.RENDER_ACCUMULATE
                 if last and reduce and ctx.world > 1:
@@ -320,6 +326,9 @@ class PLTIntegrator:
                     dump["radiance"] = np.zeros((n, 4), np.float32)
                     dump["n_rays"] = np.zeros((n, 2), np.uint32)     # closest-hit rays, shadow rays per sample
                     dmp = capi.SampleDump(capi.fptr(dump["wavelengths"]), capi.fptr(dump["radiance"]), capi.uptr(dump["n_rays"]), n)
+                    if is_polarized:   # first column of the result Mueller matrix: (n, Stokes component, wavelength)
+                        dump["stokes"] = np.zeros((n, 4, 4), np.float32)
+                        dmp.stokes = capi.fptr(dump["stokes"])
                 st = capi.Stats()
                 dst = out.ctypes.data if (last and out is not None and download) else None
                 capi.check(L.pltb_render(ctx._h, dev, C.byref(prm), dst, C.byref(dmp) if dmp else None, C.byref(st)))
@@ -349,11 +358,38 @@ class PLTIntegrator:
 register_integrator("plt", lambda props: PLTIntegrator(props))
 
 
-def _make_integrator(props):
+class StokesIntegrator:
+    """The `stokes` plugin (src/integrators/stokes.cpp:66-138) around a nested `plt` integrator -- what
+    scripts/rendering/utils/render.py:17-30 builds: the result gains 12 channels S0.R S0.G S0.B ... S3.B after R G B
+    (`aov_names`), i.e. render() returns (H, W, 15)."""
+
+    def __init__(self, nested):
+        if not is_polarized:
+            raise RuntimeError("This integrator should only be used in polarized mode!")   # stokes.cpp:73-74
+        if nested is None:
+            raise RuntimeError("Must specify a sub-integrator!")                           # stokes.cpp:84-85
+        if not isinstance(nested, PLTIntegrator):
+            raise RuntimeError("Child objects must be of type 'SamplingIntegrator'!")       # stokes.cpp:77-78
+        self.nested = nested
+
+    def aov_names(self):
+        return [f"S{i}.{c}" for i in range(4) for c in "RGB"]
+
+    def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, **kw):
+        return self.nested.render(scene, sensor=sensor, seed=seed, spp=spp, develop=develop, evaluate=evaluate, _stokes=True, **kw)
+
+    def cancel(self):
+        self.nested.cancel()
+
+    @property
+    def last_stats(self):
+        return self.nested.last_stats
+
+
+def _make_integrator(props, nested=None):
     t = props.plugin_name
     if t == "stokes":
-        # src/integrators/stokes.cpp:73-74: throws in unpolarized variants (the only ones built)
-        raise RuntimeError("This integrator should only be used in polarized mode!")
+        return StokesIntegrator(nested)
     if t not in _integrator_registry:
         raise RuntimeError(f'Plugin "{t}" not found (only the `plt` integrator is on the B200 hot path)')
     return _integrator_registry[t](props)
@@ -379,7 +415,10 @@ def load_dict(d):
         return Scene(flatten(tree), tree)
     if d["type"] in _integrator_registry or d["type"] == "stokes":
         p = Properties(d["type"], **{k: v for k, v in d.items() if k != "type" and not isinstance(v, dict)})
-        return _make_integrator(p)
+        children = [load_dict(v) for v in d.values() if isinstance(v, dict)]
+        if d["type"] == "stokes" and len(children) > 1:
+            raise RuntimeError("More than one sub-integrator specified!")                   # stokes.cpp:79-80
+        return _make_integrator(p, children[0] if children else None)
     raise RuntimeError(f'load_dict(): top-level plugin "{d["type"]}" is not on the plt hot path')
 
 

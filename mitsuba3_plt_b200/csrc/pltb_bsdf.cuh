@@ -6,7 +6,7 @@
 
 namespace pltb {
 
-struct BSDFSampleOut { V3 wo; float pdf, eta; uint32_t type; S4 weight; };
+struct BSDFSampleOut { V3 wo; float pdf, eta; uint32_t type; S4 weight; float aux; /* roughgrating: sampled lobe intensity */ };
 
 PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, V2 uv, float cos_theta) {
     S4 eta = tex_eval(sc, b.tex[0], wl, uv), k = tex_eval(sc, b.tex[1], wl, uv), F;
@@ -23,7 +23,7 @@ PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, 
 PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl,
                                         float s1, V2 s2, V2 lobe_s2) {
     BSDFSampleOut o;
-    o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f);
+    o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f); o.aux = 0.f;
     const float cos_theta_i = wi.z;
     switch (type) {
         case PLTB_BSDF_DIFFUSE: {  // src/bsdfs/diffuse.cpp:101-125
@@ -101,6 +101,7 @@ PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &
             S4 w = s4(weight);
             if (b.tex[2] >= 0) w = w * tex_eval(sc, b.tex[2], wl, uv);
             if (active) o.weight = ((F * w) * intensity) * b.f[7];
+            o.aux = intensity;
             return o;
         }
         default: return o;
@@ -236,8 +237,9 @@ PLTB_HD void grating_scan(const GratingLoop &gl, V3 wo, GratingHits &h) {
     });
 }
 
-PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const GratingLoop &gl, V3 wi, V2 uv, const S4 &wl, V3 wo,
-                          const GratingHits &h) {
+// the lobe sum of grating_finish without the Fresnel factor and specular_reflectance (the polarized variants multiply it with a
+// Mueller matrix instead, roughgrating.cpp:924-968)
+PLTB_HD S4 grating_lobe_sum(const DeviceScene &sc, const pltb_bsdf &b, const GratingLoop &gl, V3 wi, V3 wo, const GratingHits &h) {
     const Grating &g = gl.g;
     S4 result = s4(0.f);
     if (h.n > 0) {
@@ -269,6 +271,12 @@ PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const Grati
         else
             for (int k = 0; k < h.n; ++k) add((int) (h.hit[k] & 15) - 4, (int) ((h.hit[k] >> 4) & 15) - 4, (int) (h.hit[k] >> 8));
     }
+    return result;
+}
+
+PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const GratingLoop &gl, V3 wi, V2 uv, const S4 &wl, V3 wo,
+                          const GratingHits &h) {
+    S4 result = grating_lobe_sum(sc, b, gl, wi, wo, h);
     V3 H = normalize(wo + wi);
     S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
     if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
@@ -300,6 +308,33 @@ PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t t
             return D != 0.f ? F * result : s4(0.f);
         }
         case PLTB_BSDF_ROUGHGRATING: return grating_eval(sc, b, wi, uv, wl, wo);
+        default: return s4(0.f);
+    }
+}
+
+// wbsdf_eval without its Fresnel factor (wi / wo already twosided-flipped): what the polarized variants scale a Mueller matrix
+// with -- the whole value for the depolarizing BSDFs (diffuse, principled), D G / (4 cos) [* specular_reflectance] for the rough
+// conductor (0 where the unpolarized eval is masked), the lobe sum [* specular_reflectance] for the grating
+PLTB_HD S4 bsdf_eval_nofresnel(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    switch (type) {
+        case PLTB_BSDF_DIFFUSE:
+        case PLTB_BSDF_PRINCIPLED: return bsdf_eval_inner(sc, b, type, wi, uv, wl, wo);
+        case PLTB_BSDF_ROUGHCONDUCTOR: {
+            if (!(wi.z > 0.f && wo.z > 0.f)) return s4(0.f);
+            V3 H = normalize(wo + wi);
+            Microfacet distr = make_mf(b);
+            float D = distr.eval(H), G = distr.G(wi, wo, H);
+            S4 result = s4(D * G / (4.f * wi.z));
+            if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+            return D != 0.f ? result : s4(0.f);
+        }
+        case PLTB_BSDF_ROUGHGRATING: {
+            GratingLoop gl; gl.init(b, wi, uv, wl, wo);
+            GratingHits h; grating_scan(gl, wo, h);
+            S4 result = grating_lobe_sum(sc, b, gl, wi, wo, h);
+            if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+            return result;
+        }
         default: return s4(0.f);
     }
 }
@@ -368,7 +403,7 @@ template <int Class> PLTB_HD uint32_t class_type(const pltb_bsdf *b) {
 template <int Class = -1>
 PLTB_HD BSDFSampleOut wbsdf_sample(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
                                    V2 lobe_s2) {
-    if (!b) { BSDFSampleOut o; o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f); return o; }
+    if (!b) { BSDFSampleOut o; o.wo = mk3(0, 0, 0); o.pdf = 0.f; o.eta = 0.f; o.type = 0; o.weight = s4(0.f); o.aux = 0.f; return o; }
     const uint32_t type = class_type<Class>(b);
     if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) {
         float wz = wi.z;

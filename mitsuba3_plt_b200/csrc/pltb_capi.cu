@@ -63,9 +63,10 @@ struct pltb_context {
     // pass state
     PassState st{};
     uint32_t st_chunk = 0, st_depth = 0;
+    bool st_polarized = false;
     std::vector<void *> st_allocs;
     unsigned long long *counters = nullptr;
-    float *dump_wl = nullptr, *dump_L = nullptr; uint32_t *dump_rays = nullptr; uint64_t dump_cap = 0;
+    float *dump_wl = nullptr, *dump_L = nullptr, *dump_stokes = nullptr; uint32_t *dump_rays = nullptr; uint64_t dump_cap = 0;
     uint32_t *n_shadow = nullptr; uint32_t n_shadow_cap = 0;   // per-sample shadow-ray counts (only for pltb_sample_dump.n_rays)
     int sm_count = 148;
     cudaEvent_t ev[2] = { nullptr, nullptr };
@@ -134,7 +135,7 @@ int pltb_context_create(int device, int rank, int world, const void *nccl_unique
 
 static void free_state(pltb_context *c) {
     for (void *p : c->st_allocs) cudaFree(p);
-    c->st_allocs.clear(); c->st_chunk = 0; c->st_depth = 0;
+    c->st_allocs.clear(); c->st_chunk = 0; c->st_depth = 0; c->st_polarized = false;
 }
 
 void pltb_context_destroy(pltb_context *c) {
@@ -144,7 +145,7 @@ void pltb_context_destroy(pltb_context *c) {
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     free_state(c);
     cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
-    cudaFree(c->dump_rays); cudaFree(c->n_shadow);
+    cudaFree(c->dump_rays); cudaFree(c->n_shadow); cudaFree(c->dump_stokes);
     cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
     for (cudaEvent_t e : c->prof) cudaEventDestroy(e);
     for (cudaEvent_t e : c->kprof) cudaEventDestroy(e);
@@ -255,8 +256,8 @@ int pltb_film_device_ptr(pltb_context *c, float **accum, uint64_t *n) {
     return 0;
 }
 
-static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
-    if (c->st_chunk >= chunk && c->st_depth >= depth) return 0;
+static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool polarized) {
+    if (c->st_chunk >= chunk && c->st_depth >= depth && (c->st_polarized || !polarized)) return 0;
     free_state(c);
     auto alloc = [&](void **p, size_t bytes) -> int {
         CU(cudaMalloc(p, bytes));
@@ -295,7 +296,17 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth) {
     rc |= alloc((void **) &st.queue_eval, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.shadow_q, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.counts, kCountsTotal * sizeof(uint32_t));
+    st.pp_alpha = st.pv_w = st.pv_alpha = st.pv_em = nullptr; st.stokes_theta = nullptr;
+    if (polarized) {
+        rc |= alloc((void **) &st.pp_alpha, 4 * (size_t) chunk * sizeof(float4));
+        rc |= alloc((void **) &st.pv_w, 16 * nv * sizeof(float4));
+        rc |= alloc((void **) &st.pv_alpha, 4 * nv * sizeof(float4));
+        rc |= alloc((void **) &st.pv_em, 4 * nv * sizeof(float4));
+        rc |= alloc((void **) &st.stokes_theta, (size_t) chunk * sizeof(float));
+    }
+    st.nv = nv;
     if (rc) { free_state(c); return rc; }
+    c->st_polarized = polarized;
     st.chunk = chunk;
     st.counters = c->counters;
     c->st_chunk = chunk; c->st_depth = depth;
@@ -319,7 +330,11 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     const uint32_t cw = prm->crop_w ? prm->crop_w : W, ch = prm->crop_h ? prm->crop_h : H;
     if (prm->crop_x + cw > W || prm->crop_y + ch > H) return fail(PLTB_ERR_INVALID, "crop window outside the film");
     const uint64_t total = (uint64_t) cw * ch * prm->spp_count;
-    const uint64_t n_acc = (uint64_t) W * H * 4;
+    const bool polarized = (prm->flags & PLTB_RENDER_POLARIZED) != 0, stokes = polarized && (prm->flags & PLTB_RENDER_STOKES) != 0;
+    if ((prm->flags & PLTB_RENDER_STOKES) && !polarized)
+        return fail(PLTB_ERR_INVALID, "This integrator should only be used in polarized mode!");   // stokes.cpp:73-74
+    const int nch = PLTB_FILM_CHANNELS(stokes ? PLTB_RENDER_STOKES : 0);
+    const uint64_t n_acc = (uint64_t) W * H * nch;
     if (c->accum_floats != n_acc) {
         cudaFree(c->accum); c->accum = nullptr;
         CU(cudaMalloc(&c->accum, n_acc * sizeof(float)));
@@ -331,32 +346,40 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     // 2^25 1666 Msamples/s.  State is 156 B per sample + 152 B per vertex slot (1.2 KB at max_depth 7): 2^25 samples = 41 GB of
     // the B200's 180 GB; the pass shrinks when that would exceed 30 % of the device memory.
     uint32_t chunk_log2 = 25;
-    const bool state_fits = c->st_chunk && c->st_depth >= prm->max_depth && (total <= c->st_chunk || c->st_chunk >= (1u << 25));
+    const bool state_fits = c->st_chunk && c->st_depth >= prm->max_depth && (total <= c->st_chunk || c->st_chunk >= (1u << 25)) &&
+                            (c->st_polarized || !polarized);
+    if (polarized && !c->st_polarized && c->st_chunk) free_state(c);   // the polarized arrays need a (smaller) pass of their own
     if (!state_fits) {   // (cudaMemGetInfo is a driver round trip: only when the state has to be (re)allocated)
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b) {
-            const uint64_t per_sample = 156ull + 152ull * prm->max_depth;
+            // polarized: + 64 B per sample (throughput column) + 384 B per vertex slot (16-float4 weight, two 4-float4 columns)
+            const uint64_t per_sample = 156ull + 152ull * prm->max_depth + (polarized ? 68ull + 384ull * prm->max_depth : 0ull);
             while (chunk_log2 > 20 && (per_sample << chunk_log2) > (uint64_t) (0.3 * (double) total_b)) --chunk_log2;
         }
     }
     if (const char *e = getenv("PLTB_CHUNK_LOG2")) chunk_log2 = (uint32_t) std::min(26, std::max(10, atoi(e)));
     uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(total, 1), 1ull << chunk_log2);
-    if (int rc = ensure_state(c, chunk, prm->max_depth)) return rc;
+    if (int rc = ensure_state(c, chunk, prm->max_depth, polarized)) return rc;
     PassState st = c->st;
+    if (!polarized) { st.pp_alpha = st.pv_w = st.pv_alpha = st.pv_em = nullptr; st.stokes_theta = nullptr; }
+    else if (!stokes) st.stokes_theta = nullptr;
+    st.nv = (size_t) c->st_chunk * c->st_depth;
     st.chunk = c->st_chunk; st.max_depth = prm->max_depth; st.rr_depth = prm->rr_depth;
-    float *d_wl = nullptr, *d_L = nullptr; uint32_t *d_rays = nullptr; uint64_t dcap = 0;
+    float *d_wl = nullptr, *d_L = nullptr, *d_stokes = nullptr; uint32_t *d_rays = nullptr; uint64_t dcap = 0;
     st.n_shadow = nullptr;
-    if (dump && (dump->wavelengths || dump->radiance || dump->n_rays)) {
+    if (dump && (dump->wavelengths || dump->radiance || dump->n_rays || (polarized && dump->stokes))) {
         dcap = std::min<uint64_t>(dump->capacity, total);
         if (c->dump_cap < dcap) {
-            cudaFree(c->dump_wl); cudaFree(c->dump_L); cudaFree(c->dump_rays);
-            c->dump_wl = c->dump_L = nullptr; c->dump_rays = nullptr; c->dump_cap = 0;
+            cudaFree(c->dump_wl); cudaFree(c->dump_L); cudaFree(c->dump_rays); cudaFree(c->dump_stokes);
+            c->dump_wl = c->dump_L = c->dump_stokes = nullptr; c->dump_rays = nullptr; c->dump_cap = 0;
             CU(cudaMalloc(&c->dump_wl, dcap * 4 * sizeof(float)));
             CU(cudaMalloc(&c->dump_L, dcap * 4 * sizeof(float)));
             CU(cudaMalloc(&c->dump_rays, dcap * 2 * sizeof(uint32_t)));
+            CU(cudaMalloc(&c->dump_stokes, dcap * 16 * sizeof(float)));
             c->dump_cap = dcap;
         }
         d_wl = c->dump_wl; d_L = c->dump_L;
+        if (polarized && dump->stokes) d_stokes = c->dump_stokes;
         if (dump->n_rays) {
             if (c->n_shadow_cap < st.chunk) {
                 cudaFree(c->n_shadow); c->n_shadow = nullptr; c->n_shadow_cap = 0;
@@ -423,7 +446,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         PROF();
         launch_nee_post(scene->dev, st, 1, nee_grid, s);
         PROF();
-        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, dcap, s);
+        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         launches += do_splat ? 9 : 8;   // raygen, 3 x nee_light, 3 x nee_post, gather (+ splat)
     }
@@ -439,13 +462,13 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (film_out && root) {
         const float *src = c->accum; uint64_t n_out = n_acc;
         if (prm->flags & PLTB_RENDER_DEVELOP) {
-            const uint64_t n_rgb = (uint64_t) W * H * 3;
+            const uint64_t n_rgb = (uint64_t) W * H * (nch - 1);
             if (c->rgb_floats != n_rgb) {
                 cudaFree(c->rgb); c->rgb = nullptr;
                 CU(cudaMalloc(&c->rgb, n_rgb * sizeof(float)));
                 c->rgb_floats = n_rgb;
             }
-            launch_develop(c->accum, c->rgb, (uint64_t) W * H, s);
+            launch_develop(c->accum, c->rgb, (uint64_t) W * H, nch, s);
             launches++;
             src = c->rgb; n_out = n_rgb;
         }
@@ -457,6 +480,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         if (dump->wavelengths) CU(cudaMemcpyAsync(dump->wavelengths, d_wl, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
         if (dump->radiance) CU(cudaMemcpyAsync(dump->radiance, d_L, dcap * 4 * sizeof(float), cudaMemcpyDeviceToHost, s));
         if (dump->n_rays) CU(cudaMemcpyAsync(dump->n_rays, d_rays, dcap * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        if (d_stokes) CU(cudaMemcpyAsync(dump->stokes, d_stokes, dcap * 16 * sizeof(float), cudaMemcpyDeviceToHost, s));
     }
     if (!(film_out && root)) PROF();
     PROF();   // tail event 3: after the copies

@@ -240,6 +240,13 @@ struct PassState {
     float4 *v_em;              // MIS-weighted emissive contribution alpha_i * Lem_i
     float4 *v_nee;             // NEE contribution (k_nee)
     float2 *v_wiz_shape;       // {wi.z, shape id bits}
+    // polarized variants only (PLTB_RENDER_POLARIZED; nullptr otherwise).  Component-major: [c][...] with c = Stokes component.
+    float4 *pp_alpha;          // [4][chunk]   first column of the sample-phase throughput matrix
+    float4 *pv_w;              // [16][nv]     replay weight W_i as 4 rows x 4 wavelengths: index (4 * wavelength + row) * nv + r
+    float4 *pv_alpha;          // [4][nv]      first column of the replayed throughput alpha_i (the NEE step reads it)
+    float4 *pv_em;             // [4][nv]      first column of alpha_i * Lem_i
+    float *stokes_theta;       // [chunk]      angle of the final Stokes-frame rotation to the sensor's x axis (stokes.cpp:100-106)
+    size_t nv;                 // chunk * max_depth slots
     // work lists (path ids), filled with warp-aggregated atomics
     uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
     uint32_t *shade_q[2];      // hits of the current bounce by material class: 0 everything else, 1 roughgrating

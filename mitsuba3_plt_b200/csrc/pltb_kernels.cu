@@ -10,7 +10,7 @@
 #include <cuda_runtime.h>
 #include <cstdlib>
 
-#include "pltb_stages.cuh"
+#include "pltb_stages_pol.cuh"
 #include "pltb_launch.h"
 
 namespace pltb {
@@ -410,6 +410,99 @@ __global__ void k_develop(const float4 *accum, float *rgb, uint64_t n_pixels) {
     rgb[3 * i] = a.x / d; rgb[3 * i + 1] = a.y / d; rgb[3 * i + 2] = a.z / d;
 }
 
+// ---- polarized variants (PLTB_RENDER_POLARIZED): same queues and launch order, Mueller arithmetic in the shading / NEE kernels ----
+template <int Class>
+__global__ void __launch_bounds__(128) k_shade_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                                   uint32_t bounce) {
+    const uint32_t n = st.counts[4 * bounce + 1 + Class];
+    const uint32_t *list = st.shade_q[Class];
+    uint32_t cnt[4] = { 0, 0, 0, 0 };
+    DevPush push;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_shade_pol<Class>(sc, st, list[e], bounce, push, cnt);
+    flush_counters(cnt, st.counters);
+}
+
+template <int Class>
+__global__ void __launch_bounds__(128) k_nee_post_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+    const uint32_t n = st.counts[kCountsNee + Class];
+    const uint32_t *queue = st.queue[Class];
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_nee_post_pol<Class>(sc, st, queue[e]);
+}
+
+// plt_solve_phase accumulation for the first column of L, then StokesIntegrator::sample's rotation to the sensor frame
+// (stokes.cpp:97-106) when `stokes`.  The four components are left in p_ray_o / p_ray_d / p_hit / p_prev (dead by now).
+__global__ void __launch_bounds__(256) k_gather_pol(const __grid_constant__ PassState st, const __grid_constant__ PassParams pp, int stokes,
+                                                    float *dump_wl, float *dump_L, uint32_t *dump_rays, float *dump_stokes, uint64_t dump_cap) {
+    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= pp.count) return;
+    const uint32_t n = st.n_vertices[local];
+    S4 L[4] = { s4(0.f), s4(0.f), s4(0.f), s4(0.f) };
+    for (uint32_t i = 0; i < n; ++i) {
+        const size_t r = (size_t) i * st.chunk + local;
+        for (int c = 0; c < 4; ++c) L[c] = L[c] + f4_to_s4(st.pv_em[(size_t) c * st.nv + r]);
+        L[0] = L[0] + f4_to_s4(st.v_nee[r]);
+    }
+    if (stokes) {
+        const float theta = st.stokes_theta[local];
+        const F44 R = StokesFrames::rotator(sinf(2.f * theta), cosf(2.f * theta));
+        for (int k = 0; k < 4; ++k) {
+            C4 x; for (int c = 0; c < 4; ++c) x.v[c] = L[c].v[k];
+            x = f44_apply(R, x);
+            for (int c = 0; c < 4; ++c) L[c].v[k] = x.v[c];
+        }
+    }
+    st.p_ray_o[local] = s4_to_f4(L[0]); st.p_ray_d[local] = s4_to_f4(L[1]); st.p_hit[local] = s4_to_f4(L[2]); st.p_prev[local] = s4_to_f4(L[3]);
+    if (dump_cap) {
+        uint32_t pix, s_rel;
+        split_work(pp, pp.first + local, pix, s_rel);
+        const uint64_t di = (uint64_t) pix * pp.spp_count + s_rel;
+        if (di < dump_cap) {
+            if (dump_L) reinterpret_cast<float4 *>(dump_L)[di] = s4_to_f4(L[0]);
+            if (dump_wl) reinterpret_cast<float4 *>(dump_wl)[di] = st.wl[local];
+            if (dump_rays) { dump_rays[2 * di] = n; dump_rays[2 * di + 1] = st.n_shadow[local]; }
+            if (dump_stokes) for (int c = 0; c < 4; ++c) reinterpret_cast<float4 *>(dump_stokes)[4 * di + c] = s4_to_f4(L[c]);
+        }
+    }
+}
+
+// film splat with the 12 Stokes AOVs (16 channels per pixel: R G B W S0.RGB .. S3.RGB): one thread per sample, four vector
+// atomics per tap.  AOV i = spectrum_to_srgb(S_i / pdf_rgb_spectrum(wavelengths)) (stokes.cpp:108-121); the main channels are
+// spectrum_to_srgb(ray_weight * S_0) (integrator.cpp:456-470).
+__global__ void __launch_bounds__(256) k_splat_stokes(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+                                                      const __grid_constant__ PassParams pp, float *accum) {
+    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= pp.count) return;
+    const S4 wl = f4_to_s4(st.wl[local]);
+    const S4 comp[4] = { f4_to_s4(st.p_ray_o[local]), f4_to_s4(st.p_ray_d[local]), f4_to_s4(st.p_hit[local]), f4_to_s4(st.p_prev[local]) };
+    float values[16];
+    splat_values(sc, comp[0], wl, f4_to_s4(st.sensor_w[local]), values);
+    for (int i = 0; i < 4; ++i) {
+        S4 v;
+        for (int k = 0; k < 4; ++k) { const float pdf = pdf_rgb_spectrum(wl.v[k]); v.v[k] = comp[i].v[k] * (pdf != 0.f ? rcp(pdf) : 0.f); }
+        spectrum_to_srgb(sc.cie_srgb, v, wl, values + 4 + 3 * i);
+    }
+    struct Film16 {
+        float *accum;
+        __device__ __forceinline__ void add(size_t pixel, const float *v, float w) {
+            float4 *dst = reinterpret_cast<float4 *>(accum) + 4 * pixel;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) atomicAdd(dst + q, make_float4(v[4 * q] * w, v[4 * q + 1] * w, v[4 * q + 2] * w, v[4 * q + 3] * w));
+        }
+    } film{ accum };
+    splat_taps(sc, pp, values, st.film_pos[local], film);
+}
+
+// HDRFilm::develop with AOV channels: every channel but W divided by (w == 0 ? 1 : w)
+__global__ void k_develop_n(const float *accum, float *out, uint64_t n_pixels, int nch) {
+    uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pixels) return;
+    const float w = accum[nch * i + 3], d = w == 0.f ? 1.f : w;
+    int o = 0;
+    for (int c = 0; c < nch; ++c) if (c != 3) out[(nch - 1) * i + o++] = accum[nch * i + c] / d;
+}
+
 thread_local LaunchHook g_launch_hook;
 #define PLTB_AFTER(k) do { if (g_launch_hook.fn) g_launch_hook.fn((k), g_launch_hook.user); } while (0)
 
@@ -421,6 +514,11 @@ void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, i
     k_classify<<<grid, 256, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_CLASSIFY);
 }
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
+    if (st.pv_w) {   // polarized variant
+        if (cls) { k_shade_pol<1><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_GRATING); }
+        else { k_shade_pol<0><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_OTHER); }
+        return;
+    }
     if (cls) { k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_GRATING); }
     else { k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_OTHER); }
 }
@@ -431,17 +529,30 @@ void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cuda
     k_trace<true><<<grid, 128, 0, s>>>(sc, st, 0); PLTB_AFTER(PLTB_K_TRACE_SHADOW);
 }
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
+    if (st.pv_w) {   // polarized variant: scan and evaluation of the grating in one kernel
+        if (cls) { k_nee_post_pol<1><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING); }
+        else { k_nee_post_pol<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
+        return;
+    }
     if (cls) {
         k_nee_post<1><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING);
         k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL);
     } else { k_nee_post<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
-                  float *dump_L, uint32_t *dump_rays, uint64_t dump_cap, cudaStream_t s) {
-    k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, st.n_shadow ? dump_rays : nullptr,
-                                                    (dump_wl || dump_L || dump_rays) ? dump_cap : 0);
+                  float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s) {
+    if (st.pv_w)
+        k_gather_pol<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, stokes, dump_wl, dump_L, st.n_shadow ? dump_rays : nullptr, dump_stokes,
+                                                            (dump_wl || dump_L || dump_rays || dump_stokes) ? dump_cap : 0);
+    else
+        k_gather<<<(pp.count + 255) / 256, 256, 0, s>>>(st, pp, dump_wl, dump_L, st.n_shadow ? dump_rays : nullptr,
+                                                        (dump_wl || dump_L || dump_rays) ? dump_cap : 0);
     PLTB_AFTER(PLTB_K_GATHER);
     if (!do_splat) return;
+    if (stokes) {
+        k_splat_stokes<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
+        return;
+    }
     // separable filters with 3x3 (tent, r = 1) or 5x5 (gaussian, r = 2) taps go through the register tiles / shared strips
     const int nr = sc.film.rfilter == PLTB_RFILTER_BOX ? 0 : (int) ceilf(sc.film.radius - .5f);
     if ((nr == 1 || nr == 2) && !getenv("PLTB_SPLAT_DIRECT")) {
@@ -455,8 +566,9 @@ void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &
     }
     k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
 }
-void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, cudaStream_t s) {
-    k_develop<<<(unsigned) ((n_pixels + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4 *>(accum), rgb, n_pixels);
+void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, int nch, cudaStream_t s) {
+    if (nch == 4) k_develop<<<(unsigned) ((n_pixels + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4 *>(accum), rgb, n_pixels);
+    else k_develop_n<<<(unsigned) ((n_pixels + 255) / 256), 256, 0, s>>>(accum, rgb, n_pixels, nch);
 }
 
 }  // namespace pltb

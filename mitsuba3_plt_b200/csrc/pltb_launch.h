@@ -14,6 +14,6 @@ void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, i
 void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s);
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s);
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
-                  float *dump_L, uint32_t *dump_rays, uint64_t dump_cap, cudaStream_t s);
-void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, cudaStream_t s);
+                  float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s);
+void launch_develop(const float *accum, float *rgb, uint64_t n_pixels, int nch, cudaStream_t s);
 }  // namespace pltb

@@ -29,6 +29,10 @@ PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32
     idx = (y * pp.film_w + x) * pp.spp + s;
 }
 
+PLTB_HD float stokes_rotation_angle(const pltb_sensor &sn, V3 ray_d, bool batch);   // pltb_stages_pol.cuh
+struct PassState;
+PLTB_NI void pol_miss_record(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i);   // pltb_stages_pol.cuh
+
 // Closest-hit bookkeeping shared by k_raygen (bounce 0) and k_trace (bounce >= 1): a hit is routed to the shade queue of
 // its material class; a miss finalises the path in place (plt.py:93-168 with si invalid: the five BSDF draws and the RR
 // draw are still consumed, the bounce record contributes nothing, the loop ends).
@@ -36,7 +40,8 @@ PLTB_HD void decode_sample(const PassParams &pp, uint64_t w, uint32_t &x, uint32
 // si.emitter(scene) of the invalid interaction is the environment (interaction.h:343-346), DirectionSample3f(scene, si, prev_si)
 // takes d = -si.wi = ray.d (records.h:173-180).  Constant background: pdf_direction = 1 / (4 pi) (constant.cpp:152-157),
 // eval = radiance (:92-96).  The replayed throughput is the prefix product of the recorded weights, as in stage_shade.
-PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
+// the MIS-weighted environment radiance mis_bsdf * Le seen by the escaped ray (before the replayed throughput)
+PLTB_NI S4 env_miss_lem(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
     const pltb_emitter &e = sc.emitters[sc.env];
     const S4 wl = f4_to_s4(st.wl[local]);
     float last_nd_pdf = 1.f;
@@ -45,8 +50,6 @@ PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_
         last_nd_pdf = st.p_prev[local].w;
         prev_bsdf_delta = (st.p_flags[local] & 1u) != 0;
     }
-    S4 ai = s4(1.f);
-    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
     float em_pdf = 0.f;
     S4 Le;
     if (e.type == PLTB_EMITTER_ENVMAP) {   // EnvironmentMapEmitter::pdf_direction / ::eval (envmap.cpp:468-484, 343-353)
@@ -59,7 +62,12 @@ PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_
         Le = tex_eval(sc, e.radiance, wl, mk2(0.f, 0.f));
     }
     const float mis_bsdf = mis_weight(last_nd_pdf, em_pdf);
-    return ai * (Le * mis_bsdf);
+    return Le * mis_bsdf;
+}
+PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
+    S4 ai = s4(1.f);
+    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
+    return ai * env_miss_lem(sc, st, local, i);
 }
 
 template <class Push>
@@ -75,7 +83,8 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
         st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
         const size_t r = (size_t) i * st.chunk + local;
-        st.v_em[r] = sc.env >= 0 ? s4_to_f4(env_miss_emission(sc, st, local, i)) : mkf4(0.f, 0.f, 0.f, 0.f);
+        if (st.pv_em) pol_miss_record(sc, st, local, i);
+        else st.v_em[r] = sc.env >= 0 ? s4_to_f4(env_miss_emission(sc, st, local, i)) : mkf4(0.f, 0.f, 0.f, 0.f);
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
         st.n_vertices[local] = i + 1;
     }
@@ -106,6 +115,7 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
     float2 fp; fp.x = pos_f.x; fp.y = pos_f.y;
     st.film_pos[local] = fp;
     if (st.n_shadow) st.n_shadow[local] = 0;
+    if (st.stokes_theta) st.stokes_theta[local] = stokes_rotation_angle(sc.sensors[0], ray.d, sc.n_sensors > 1);
     for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1, plt.py:65-70)
     st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
     st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);

@@ -1,0 +1,80 @@
+"""GPU parity of the polarized spectral variant + `stokes` wrapper against the polarized oracle: per-sample
+Stokes vectors (first column of the result Mueller matrix, rotated to the sensor frame), per-sample ray counts, and the
+15-channel image (R G B, S0.RGB .. S3.RGB)."""
+import numpy as np
+import pytest
+
+from parity import MAX_RMSE, MIN_FRACTION, relative_mse, sample_agreement
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("cbox", 64, 8, 0), ("cbox-grating", 64, 8, 0), ("cbox-grating", 128, 16, 3), ("veach-mis", 64, 8, 1), ("gratingcap", 96, 8, 0),
+         ("cbox-grating:envmap", 48, 8, 5), ("spectrograph:d65", 1, 64, 3), ("disk", 64, 8, 2)]
+
+
+@pytest.fixture()
+def polarized(mi):
+    mi.set_variant("cuda_ad_spectral_polarized")
+    yield mi.load_dict({"type": "stokes", "nested": {"type": "plt", "max_depth": 7, "rr_depth": 50}})
+    mi.set_variant("cuda_spectral")
+
+
+def stokes_agreement(a, b):
+    """fraction of samples whose 16 values (4 Stokes components x 4 wavelengths) all agree: relative to the sample's intensity
+    scale, since S1..S3 are differences of like-sized terms and can be arbitrarily small next to S0"""
+    a, b = np.asarray(a, np.float64).reshape(len(a), 16), np.asarray(b, np.float64).reshape(len(b), 16)
+    scale = np.maximum(np.abs(b[:, :4]).max(axis=1, keepdims=True), 1e-6)
+    both_nan = np.isnan(a) & np.isnan(b)
+    with np.errstate(invalid="ignore"):
+        ok = (np.abs(a - b) <= 1e-4 * scale) | both_nan
+    return ok.all(axis=1).mean()
+
+
+@pytest.mark.parametrize("name,res,spp,seed", CASES)
+def test_stokes_per_sample(mi, oracle, polarized, name, res, spp, seed):
+    from mitsuba3_plt_b200 import scenes
+    from test_gpu_parity import ray_count_agreement
+    sc = scenes.load(name, resx=res, resy=res)
+    dump = {}
+    img = polarized.render(sc, spp=spp, seed=seed, dump=dump)
+    ref = oracle.render(sc.flat, spp, seed=seed, dump=True, polarized=True, stokes=True)
+    assert img.shape == ref["image"].shape and img.shape[-1] == 15
+    assert sample_agreement(dump["wavelengths"], ref["wavelengths"]) == 1.0
+    frac = sample_agreement(dump["radiance"], ref["radiance"])          # S0: unpolarized_spectrum(L)
+    assert frac >= MIN_FRACTION, f"{name}: S0 agrees on {frac * 100:.4f}% of samples"
+    sfrac = stokes_agreement(dump["stokes"], ref["stokes"])
+    assert sfrac >= MIN_FRACTION, f"{name}: Stokes vectors agree on {sfrac * 100:.4f}% of samples"
+    ray_count_agreement(name, dump["n_rays"], ref["n_rays"])
+    assert np.isfinite(dump["stokes"]).all() == np.isfinite(ref["stokes"]).all()
+    rmse, mism = relative_mse(img[..., :3], ref["image"][..., :3])
+    assert rmse <= MAX_RMSE and mism <= 0.01, (rmse, mism)
+    # the Stokes AOV channels: S0.RGB like the image; S1..S3 are signed, compare against the S0 scale
+    s0 = np.abs(ref["image"][..., 3:6]).mean()
+    for c in range(3, 15):
+        d = np.nanmean(np.abs(img[..., c] - ref["image"][..., c]))
+        assert d <= 0.01 * max(s0, 1e-6), (c, d, s0)
+
+
+def test_polarized_without_stokes_and_variant_switch(mi, oracle):
+    """the polarized variant with the bare `plt` integrator returns 3 channels (unpolarized_spectrum of the Mueller result);
+    switching back to the unpolarized variant on the same context re-uses the state"""
+    from mitsuba3_plt_b200 import scenes
+    sc = scenes.load("cbox", resx=48, resy=48)
+    it = mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
+    try:
+        mi.set_variant("cuda_spectral_polarized")
+        dump = {}
+        img = it.render(sc, spp=8, seed=1, dump=dump)
+        assert img.shape == (48, 48, 3)
+        ref = oracle.render(sc.flat, 8, seed=1, dump=True, polarized=True)
+        assert sample_agreement(dump["radiance"], ref["radiance"]) >= MIN_FRACTION
+        rmse, _ = relative_mse(img, ref["image"])
+        assert rmse <= MAX_RMSE
+    finally:
+        mi.set_variant("cuda_spectral")
+    dump = {}
+    it.render(sc, spp=8, seed=1, dump=dump)
+    ref = oracle.render(sc.flat, 8, seed=1, dump=True)
+    assert sample_agreement(dump["radiance"], ref["radiance"]) >= MIN_FRACTION
+    with pytest.raises(RuntimeError, match="polarized"):
+        mi.load_dict({"type": "stokes", "nested": {"type": "plt"}})

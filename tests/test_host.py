@@ -208,9 +208,20 @@ def test_plugin_parameters_and_errors(mi):
     with pytest.raises(RuntimeError):
         mi.load_dict({"type": "volpath"})
     with pytest.raises(ImportError):
+        mi.set_variant("cuda_ad_rgb_polarized")          # the RGB variants are not built
+    mi.set_variant("cuda_ad_rgb_polarized", "llvm_spectral")
+    assert mi.variant() == "llvm_spectral" and not mi.is_polarized
+    try:   # the polarized spectral variants: Spectrum = Mueller matrix; `stokes` needs one of them and one nested integrator
         mi.set_variant("cuda_ad_spectral_polarized")
-    mi.set_variant("cuda_ad_spectral_polarized", "llvm_spectral")
-    assert mi.variant() == "llvm_spectral"
+        assert mi.is_polarized
+        st = mi.load_dict({"type": "stokes", "nested": {"type": "plt", "max_depth": 7, "rr_depth": 50, "samples_per_pass": 512}})
+        assert st.nested.max_depth == 7 and st.aov_names()[0] == "S0.R" and len(st.aov_names()) == 12
+        with pytest.raises(RuntimeError, match="sub-integrator"):
+            mi.load_dict({"type": "stokes"})
+        with pytest.raises(RuntimeError, match="More than one"):
+            mi.load_dict({"type": "stokes", "a": {"type": "plt"}, "b": {"type": "plt"}})
+    finally:
+        mi.set_variant("cuda_spectral")
     mi.register_integrator("myplt", lambda p: mi.PLTIntegrator(p))
     assert mi.load_dict({"type": "myplt", "max_depth": 3}).max_depth == 3
 
