@@ -205,7 +205,7 @@ PLTB_HD F44 pol_sample_weight(const PolVertex &p, int k) {
 }
 
 // wbsdf_weight for wavelength k (diffuse.cpp:182-200: a *scaled identity*; conductor.cpp:320-376; dielectric.cpp:522-565 with its
-// swapped directions and the elementwise "nan check"; base class: eval_pdf ratio, bsdf.cpp:85-97)
+// swapped directions and the "nan check" select against the identity; base class: eval_pdf ratio, bsdf.cpp:85-97)
 PLTB_HD F44 pol_replay_weight(const PolVertex &p, int k) {
     switch (p.type) {
         case PLTB_BSDF_DIFFUSE: return f44_diag(p.refl.v[k]);
@@ -215,7 +215,8 @@ PLTB_HD F44 pol_replay_weight(const PolVertex &p, int k) {
         case PLTB_BSDF_DIELECTRIC: {
             F44 w = p.wo.z > 0.0f ? mueller_reflection(fresnel_polarized(p.cos_w, p.eta.v[0])) : mueller_transmission(p.cos_w, p.eta.v[0]);
             w = f44_scale(w, rcp(p.wpdf));
-            for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w.m[i][j] = w.m[i][j] > 1.0f ? w.m[i][j] : 1.0f;
+            // dr::select(weight > 1.0f, weight, 1.0): both scalars convert to the identity matrix (matrix.h:68-73)
+            for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { const float id = i == j ? 1.0f : 0.0f; w.m[i][j] = w.m[i][j] > id ? w.m[i][j] : id; }
             w = p.fw.align(w);
             return f44_mul(w, f44_diag(p.wo.z > 0.0f ? p.refl.v[k] : p.trans.v[k]));
         }

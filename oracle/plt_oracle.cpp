@@ -2305,10 +2305,11 @@ void plt_oracle_array_div(const float *v3, const float *s4v, float s, float *out
     V3 v = V3(v3[0], v3[1], v3[2]) / s; S4 sp; for (int k = 0; k < 4; ++k) sp[k] = s4v[k]; sp = sp / s;
     out[0] = v.x; out[1] = v.y; out[2] = v.z; for (int k = 0; k < 4; ++k) out[3 + k] = sp[k];
 }
-void plt_oracle_m4_ops(const float *a, const float *b, const float *s4v, float f, float *out) {   /* out: 7 matrices of 64 floats */
+void plt_oracle_m4_ops(const float *a, const float *b, const float *s4v, float f, float *out) {   /* out: 8 matrices of 64 floats */
     M4 A = m4_load(a), B = m4_load(b); S4 s; for (int k = 0; k < 4; ++k) s[k] = s4v[k];
     m4_store(A * B, out); m4_store(m4_diag(s), out + 64); m4_store(m4_scale(A, s), out + 128); m4_store(m4_div(A, f), out + 192);
     m4_store(m4_depolarizer(s), out + 256); m4_store(A * m4_absorber(s), out + 320); m4_store(m4_transpose(A), out + 384);
+    m4_store(m4_select_gt_one(m4_scale(A, 3.f)), out + 448);
 }
 void plt_oracle_fresnel_polarized_real(float c, float eta, float *out) {
     FresnelPol f = fresnel_polarized(c, eta);

@@ -71,6 +71,9 @@ int main() {
         printf(", \"depolarizer\": "); print_mueller(mueller::depolarizer<Spec>(Spec(0.5f, 0.25f, 2.f, 3.f)));
         printf(", \"A_times_absorber\": "); print_mueller(A * mueller::absorber<Spec>(Spec(0.5f, 0.25f, 2.f, 3.f)));
         printf(", \"transpose\": "); print_mueller(dr::transpose(A));
+        // dielectric.cpp:533-536 "hacky nan check": dr::select(weight > 1.0f, weight, 1.0) on a Mueller matrix
+        Mueller W = A * 3.f;
+        printf(", \"select_gt_one\": "); print_mueller(dr::select(W > 1.0f, W, 1.0));
         printf("}");
         first_item = false;
     }
