@@ -422,3 +422,17 @@ def test_polarized_oracle_matches_the_reference_published_render(mi, oracle):
         x, y = blk(img[..., 3 + 3 * i]), np.array(G[f"S{i}"])
         assert np.corrcoef(x.ravel(), y.ravel())[0, 1] >= min_corr, i
         assert abs(x.mean() - y.mean()) <= 0.25 * abs(y.mean()) + 2e-5, (i, x.mean(), y.mean())
+
+
+def test_polarized_oracle_converges_to_the_reference_published_spectrograph(mi, oracle):
+    """the oracle half of tests/test_gpu_polarized.py::test_converges_to_the_reference_published_spectrograph: the roughgrating
+    path against results/spectrograph-bbody-3000/result.exr at 16384 spp (median difference 1.7 %, total within 1 %)"""
+    from mitsuba3_plt_b200 import imageio
+    d = os.path.join(ROOT, "tests", "golden", "scenes", "spectrograph-bbody-3000")
+    want, _ = imageio.read_exr(os.path.join(d, "result.exr"))
+    want = want[0, :, :3]
+    sc = mi.load_file(os.path.join(d, "scene.xml"), resx=150, resy=1)
+    r = oracle.render(sc.flat, 16384, seed=0, polarized=True, stokes=True)
+    s0 = r["image"][0, :, 3:6]
+    assert np.median(np.abs(s0 - want) / np.maximum(np.abs(want), 1e-6)) <= 0.03
+    assert abs(s0[:, 2].sum() / want[:, 2].sum() - 1) <= 0.015
