@@ -15,8 +15,12 @@ ap.add_argument("--cpu-seconds", type=float, default=6.0)
 ap.add_argument("--only", default="")
 args = ap.parse_args()
 
-CONFIGS = [  # id, builtin scene, resx, resy, spp, note
+CONFIGS = [  # id, builtin scene, resx, resy, spp, note    (ids ending in "pol": polarized spectral variant + `stokes` wrapper, 8f f1)
     ("C1", "cbox", 256, 256, 16, "scenes/cbox, 256x256, 16 spp"),
+    ("C1L", "cbox", 1024, 1024, 64, "scenes/cbox, 1024x1024, 64 spp (C1's scene at a size that fills the GPU)"),
+    ("C1pol", "cbox", 500, 500, 1024, "scenes/cbox 500x500, 1024 spp, stokes{plt}, polarized: the reference's published results/cbox-plt "
+                                    "(params.json: 1.654 min on the authors' GPU, JIT included)"),
+    ("C2pol", "cbox-grating", 1024, 1024, 128, "scenes/cbox-grating 1024x1024, 128 spp, stokes{plt}, polarized"),
     ("C2", "cbox-grating", 1024, 1024, 1024, "scenes/cbox-grating 1024x1024, 1024 spp"),
     ("C3", "spectrograph:bbody_3000", 1, 1, 1 << 20, "spectrograph, 150 sensors x 2^20 spp (largest row of synthetic-times.csv)"),
     ("C3p", "spectrograph:bbody_3000", 1, 1, 10_000_000, "spectrograph prior pass, 150 sensors x 1e7 spp"),
@@ -26,12 +30,13 @@ it = mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
 only = set(filter(None, args.only.split(",")))
 
 
-def oracle_rate(sc, spp, W, H):
-    probe = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=1, film=False) if W * H > 4096 else \
-        oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=min(spp, 256), film=False)
+def oracle_rate(sc, spp, W, H, pol=False):
+    kw = {"polarized": pol, "stokes": pol}
+    probe = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=1, film=False, **kw) if W * H > 4096 else \
+        oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=min(spp, 256), film=False, **kw)
     rate = probe["stats"]["samples"] / max(probe["seconds"], 1e-9)
     n = int(max(1, min(spp, args.cpu_seconds * rate / (W * H))))
-    r = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=n)
+    r = oracle_lib.render(sc.flat, spp, spp_begin=0, spp_count=n, **kw)
     st = r["stats"]
     return st["samples"] / r["seconds"] / 1e6, (st["closest_rays"] + st["shadow_rays"]) / r["seconds"] / 1e6, n
 
@@ -39,6 +44,10 @@ def oracle_rate(sc, spp, W, H):
 for cid, name, rx, ry, spp, note in CONFIGS:
     if only and cid not in only:
         continue
+    pol = cid.endswith("pol")
+    mi.set_variant("cuda_ad_spectral_polarized" if pol else "cuda_spectral")
+    it = mi.load_dict({"type": "stokes", "nested": {"type": "plt", "max_depth": 7, "rr_depth": 50}} if pol else
+                      {"type": "plt", "max_depth": 7, "rr_depth": 50})
     sc = scenes.load(name, resx=rx, resy=ry)
     W, H = sc.film_size()
     warm = min(spp, max(1, (1 << 24) // (W * H)))
@@ -48,7 +57,7 @@ for cid, name, rx, ry, spp, note in CONFIGS:
     wall = time.perf_counter() - t0
     st = it.last_stats
     ms = st["ms_total"]
-    cpu_ms, cpu_mr, n = oracle_rate(sc, spp, W, H)
+    cpu_ms, cpu_mr, n = oracle_rate(sc, spp, W, H, pol)
     print(json.dumps({"config": cid, "workload": note, "film": [W, H], "spp": spp, "samples": st["samples"],
                       "gpu_ms": round(ms, 3), "gpu_wall_ms": round(wall * 1e3, 3),
                       "gpu_msamples_per_s": round(st["samples"] / ms / 1e3, 2),
@@ -60,6 +69,8 @@ for cid, name, rx, ry, spp, note in CONFIGS:
                       "cpu_oracle_msamples_per_s": round(cpu_ms, 4), "cpu_oracle_mrays_per_s": round(cpu_mr, 4),
                       "cpu_cores": os.cpu_count(), "cpu_sample": f"spp indices [0,{n}) of {spp}, full frame"}), flush=True)
 
+mi.set_variant("cuda_spectral")
+it = mi.load_dict({"type": "plt", "max_depth": 7, "rr_depth": 50})
 for c5_id, c5_scene in (("C5", "gratingcap"), ("C5d", "disk")):
     if only and c5_id not in only:
         continue
