@@ -392,13 +392,20 @@ PLTB_HD const pltb_bsdf *si_bsdf(const DeviceScene &sc, int32_t shape) {
     int32_t id = sc.shapes[shape].bsdf;
     return id < 0 ? nullptr : sc.bsdfs + id;
 }
+// the material class of a queue is the BSDF plugin type (one exception below): a compile-time constant inside k_shade<Class> / k_nee_post<Class>, so the
+// switch statements of the *_inner functions keep one case; Class < 0: generic (type read from the record)
 template <int Class> PLTB_HD uint32_t class_type(const pltb_bsdf *b) {
-    if (Class == 1) return PLTB_BSDF_ROUGHGRATING;
-    uint32_t t = b->type;
+#ifndef PLTB_CLASS_PER_TYPE
+    if (Class == PLTB_BSDF_CONDUCTOR) {   // the shared class of the delta BSDFs (pltb_bvh.h: material_class)
+        const uint32_t t = b->type;
 #if defined(__CUDA_ARCH__)
-    if (Class == 0 && t == PLTB_BSDF_ROUGHGRATING) __builtin_unreachable();
+        if (t != PLTB_BSDF_CONDUCTOR && t != PLTB_BSDF_DIELECTRIC) __builtin_unreachable();
 #endif
-    return t;
+        return t;
+    }
+#endif
+    if (Class >= 0) return (uint32_t) Class;
+    return b->type;
 }
 template <int Class = -1>
 PLTB_HD BSDFSampleOut wbsdf_sample(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,

@@ -64,6 +64,7 @@ struct pltb_context {
     PassState st{};
     uint32_t st_chunk = 0, st_depth = 0;
     bool st_polarized = false;
+    uint32_t st_class_mask = 0;   // classes whose queues are allocated
     std::vector<void *> st_allocs;
     unsigned long long *counters = nullptr;
     float *dump_wl = nullptr, *dump_L = nullptr, *dump_stokes = nullptr; uint32_t *dump_rays = nullptr; uint64_t dump_cap = 0;
@@ -83,6 +84,7 @@ struct pltb_scene {
     std::vector<pltb_sensor> sensors;
     pltb_sensor *d_sensors = nullptr;
     uint32_t film_w = 0, film_h = 0;
+    uint32_t class_mask = 0;   // material classes (BSDF plugin types) present: bit c <=> some shape uses a BSDF of type c
 };
 
 template <class T> static int upload(std::vector<void *> &allocs, const T *host, size_t n, const T **dev) {
@@ -135,7 +137,7 @@ int pltb_context_create(int device, int rank, int world, const void *nccl_unique
 
 static void free_state(pltb_context *c) {
     for (void *p : c->st_allocs) cudaFree(p);
-    c->st_allocs.clear(); c->st_chunk = 0; c->st_depth = 0; c->st_polarized = false;
+    c->st_allocs.clear(); c->st_chunk = 0; c->st_depth = 0; c->st_polarized = false; c->st_class_mask = 0;
 }
 
 void pltb_context_destroy(pltb_context *c) {
@@ -220,6 +222,8 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
         ds.bessel.h_over_3 = h / 3.0f;
     }
     s->film_w = d->film.width * d->n_sensors; s->film_h = d->film.height;
+    for (uint32_t i = 0; i < d->n_shapes; ++i)
+        s->class_mask |= 1u << material_class(d->shapes[i].bsdf >= 0 ? d->bsdfs[d->shapes[i].bsdf].type : 0u);
     *out = s;
     return 0;
 }
@@ -256,8 +260,10 @@ int pltb_film_device_ptr(pltb_context *c, float **accum, uint64_t *n) {
     return 0;
 }
 
-static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool polarized) {
-    if (c->st_chunk >= chunk && c->st_depth >= depth && (c->st_polarized || !polarized)) return 0;
+static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool polarized, uint32_t class_mask) {
+    if (c->st_chunk >= chunk && c->st_depth >= depth && (c->st_polarized || !polarized) && (class_mask & ~c->st_class_mask) == 0) return 0;
+    class_mask |= c->st_class_mask;
+    chunk = std::max(chunk, c->st_chunk); depth = std::max(depth, c->st_depth); polarized = polarized || c->st_polarized;
     free_state(c);
     auto alloc = [&](void **p, size_t bytes) -> int {
         CU(cudaMalloc(p, bytes));
@@ -281,8 +287,12 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.v_w, nv * sizeof(float4));
     rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
-    rc |= alloc((void **) &st.shade_q[0], chunk * sizeof(uint32_t));
-    rc |= alloc((void **) &st.shade_q[1], chunk * sizeof(uint32_t));
+    for (int k = 0; k < kClasses; ++k) {
+        st.shade_q[k] = st.queue[k] = nullptr;
+        if (!(class_mask >> k & 1u)) continue;
+        rc |= alloc((void **) &st.shade_q[k], chunk * sizeof(uint32_t));
+        rc |= alloc((void **) &st.queue[k], nv * sizeof(uint32_t));
+    }
     rc |= alloc((void **) &st.v_p_u, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_n_v, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_s_wix, nv * sizeof(float4));
@@ -291,8 +301,6 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.v_em, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_nee, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_wiz_shape, nv * sizeof(float2));
-    rc |= alloc((void **) &st.queue[0], nv * sizeof(uint32_t));
-    rc |= alloc((void **) &st.queue[1], nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.queue_eval, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.shadow_q, nv * sizeof(uint32_t));
     rc |= alloc((void **) &st.counts, kCountsTotal * sizeof(uint32_t));
@@ -306,7 +314,7 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     }
     st.nv = nv;
     if (rc) { free_state(c); return rc; }
-    c->st_polarized = polarized;
+    c->st_polarized = polarized; c->st_class_mask = class_mask;
     st.chunk = chunk;
     st.counters = c->counters;
     c->st_chunk = chunk; c->st_depth = depth;
@@ -359,7 +367,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     }
     if (const char *e = getenv("PLTB_CHUNK_LOG2")) chunk_log2 = (uint32_t) std::min(26, std::max(10, atoi(e)));
     uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(total, 1), 1ull << chunk_log2);
-    if (int rc = ensure_state(c, chunk, prm->max_depth, polarized)) return rc;
+    if (int rc = ensure_state(c, chunk, prm->max_depth, polarized, scene->class_mask)) return rc;
     PassState st = c->st;
     if (!polarized) { st.pp_alpha = st.pv_w = st.pv_alpha = st.pv_em = nullptr; st.stokes_theta = nullptr; }
     else if (!stokes) st.stokes_theta = nullptr;
@@ -434,21 +442,26 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         if (profile) KHook::mark(-1, c);
         // sample phase as dense per-bounce wavefronts: raygen + trace(0), then shade(i) / trace(i + 1)
         launch_raygen(scene->dev, st, pp, s);
+        // one k_shade / k_nee_post launch per material class the scene contains (roughgrating first: the longest kernel)
+        const uint32_t cm = scene->class_mask;
+        const int n_cls = __builtin_popcount(cm), has_grating = (cm >> PLTB_BSDF_ROUGHGRATING) & 1;
         for (uint32_t b = 0; b < prm->max_depth; ++b) {
-            launch_shade(scene->dev, st, b, 1, wf_grid, s);
-            launch_shade(scene->dev, st, b, 0, wf_grid, s);
-            launches += 2;
+            for (int cls = kClasses - 1; cls >= 0; --cls)
+                if (cm >> cls & 1u) launch_shade(scene->dev, st, b, cls, wf_grid, s);
+            launches += n_cls;
             if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches += 2; }
         }
         PROF();
-        launch_nee_light(scene->dev, st, nee_grid, s);
-        launch_nee_post(scene->dev, st, 0, nee_grid, s);
+        launch_nee_light(scene->dev, st, cm, nee_grid, s);
+        for (int cls = kClasses - 1; cls >= 0; --cls)
+            if ((cm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(scene->dev, st, cls, nee_grid, s);
         PROF();
-        launch_nee_post(scene->dev, st, 1, nee_grid, s);
+        if (has_grating) launch_nee_post(scene->dev, st, PLTB_BSDF_ROUGHGRATING, nee_grid, s);
         PROF();
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
-        launches += do_splat ? 9 : 8;   // raygen, 3 x nee_light, 3 x nee_post, gather (+ splat)
+        // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
+        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized ? 1 : 0) + 1 + (do_splat ? 1 : 0);
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0

@@ -216,6 +216,12 @@ PLTB_HD float rfilter_eval(const pltb_film &f, float x) {  // gaussian.cpp:94-10
 // ---- wavefront state ------------------------------------------------------------------------------------------------------------
 // All arrays are SoA.  Per-sample and per-path arrays are indexed by the sample's local id in the pass; vertex records are
 // depth-major (index = depth * chunk + sample_local) so that accesses of a warp are coalesced float4s.
+// Material classes: one shade / NEE queue per BSDF plugin type (indexed by PLTB_BSDF_*; conductor, dielectric and "no BSDF" share
+// one, pltb_bvh.h: material_class), so that a warp of k_shade / k_nee_post runs one plugin's code (the class is a template
+// parameter).  With two classes (grating / everything else) the "everything else" kernel ran at 14-17 of 32 lanes on cbox and
+// veach-mis and missed the instruction cache (profiles/r02_ncu_kernels_c{1,4}_2class.txt).
+constexpr int kClasses = 7;
+
 struct PassState {
     uint32_t chunk;            // samples per pass (capacity of every per-sample array)
     uint32_t max_depth, rr_depth;
@@ -249,18 +255,26 @@ struct PassState {
     size_t nv;                 // chunk * max_depth slots
     // work lists (path ids), filled with warp-aggregated atomics
     uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
-    uint32_t *shade_q[2];      // hits of the current bounce by material class: 0 everything else, 1 roughgrating
-    uint32_t *queue[2];        // NEE work items of the whole pass: entry = sample_local | depth << 27
+    uint32_t *shade_q[kClasses];   // hits of the current bounce by material class (== BSDF plugin type, PLTB_BSDF_*); nullptr for
+                                   // classes the scene does not contain
+    uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: entry = sample_local | depth << 27
     uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee_post<1> -> k_nee_eval)
     uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>)
-    // counters, zeroed once per pass: [4 * i + 0] live count of bounce i, [4 * i + 1 + c] shade_q[c] count of bounce i;
-    // the NEE queue counts sit at [kCountsNee + c], then the queue_eval count, the shadow_q count and the shadow-ray cursor
+    // counters, zeroed once per pass (cnt_* below index them)
     uint32_t *counts;
     // statistics
     unsigned long long *counters;  // closest, shadow, vertices, grating vertices, nee_other, nee_grating
 };
-constexpr int kCountsNee = 4 * PLTB_MAX_DEPTH + 4;
-constexpr int kCountsTotal = kCountsNee + 5;
+// layout of PassState::counts: per bounce i a block of kCountsStride words {live count, trace cursor, shade_q[c] counts}; then the NEE
+// queue counts per class, the queue_eval count, the shadow_q count and the shadow-ray cursor
+constexpr int kCountsStride = 2 + kClasses + 3;   // 12
+constexpr int kCountsNee = kCountsStride * (PLTB_MAX_DEPTH + 1);
+constexpr int kCountsTotal = kCountsNee + kClasses + 5;
+PLTB_HD int cnt_live(uint32_t i) { return kCountsStride * (int) i; }
+PLTB_HD int cnt_cursor(uint32_t i) { return kCountsStride * (int) i + 1; }
+PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCountsStride * (int) i + 2 + (int) c; }
+PLTB_HD int cnt_nee(uint32_t c) { return kCountsNee + (int) c; }
+constexpr int kCntEval = kCountsNee + kClasses, kCntShadow = kCountsNee + kClasses + 1, kCntShadowCursor = kCountsNee + kClasses + 2;
 
 struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;

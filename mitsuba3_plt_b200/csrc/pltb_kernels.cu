@@ -73,8 +73,8 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
 template <bool Shadow>
 __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
-    const uint32_t n = Shadow ? st.counts[kCountsNee + 3] : st.counts[4 * bounce];
-    uint32_t *cursor = Shadow ? st.counts + kCountsNee + 4 : st.counts + 4 * bounce + 3;
+    const uint32_t n = Shadow ? st.counts[kCntShadow] : st.counts[cnt_live(bounce)];
+    uint32_t *cursor = Shadow ? st.counts + kCntShadowCursor : st.counts + cnt_cursor(bounce);
     const unsigned lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     Traversal tr;
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
             }
             // results are written in place; k_classify walks the live list in order afterwards so that the shade / NEE work
             // lists stay (nearly) sorted by sample id and the per-sample state accesses of later kernels stay coalesced
-            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? kHitMiss : (tr.best.prim | (tr.best.cls << 30))));
+            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? kHitMiss : (tr.best.prim | (tr.best.cls << kHitClsShift))));
             active = false;
         }
     }
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
 // warp takes 128 consecutive entries at a time: four independent load chains in flight per lane, appended in list order.
 __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                   uint32_t bounce) {
-    const uint32_t n = st.counts[4 * bounce];
+    const uint32_t n = st.counts[cnt_live(bounce)];
     const uint32_t lane = threadIdx.x & 31u, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     DevPush push;
     for (uint32_t base = warp * 128u; base < n; base += n_warps * 128u) {
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
         for (int j = 0; j < 4; ++j) {
             if (base + 32u * j + lane >= n) continue;
             const uint32_t w = f2u(h4[j].w);
-            Hit h; h.t = h4[j].x; h.u = h4[j].y; h.v = h4[j].z; h.prim = w & kHitPrimMask; h.cls = (w >> 30) & 1u; h.shape = -1;
+            Hit h; h.t = h4[j].x; h.u = h4[j].y; h.v = h4[j].z; h.prim = w & kHitPrimMask; h.cls = (w >> kHitClsShift) & 7u; h.shape = -1;
             PCG32 rng; rng.state = 0; rng.inc = 0;
             if (w != kHitMiss) h.shape = 0;   // any valid shape: route_hit only needs hit / miss and the class here
             else { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
 template <int Class>
 __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
-    const uint32_t n = st.counts[4 * bounce + 1 + Class];
+    const uint32_t n = st.counts[cnt_shade(bounce, Class)];
     const uint32_t *list = st.shade_q[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     DevPush push;
@@ -173,10 +173,11 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceSce
 // NEE step 1 for the queue of one material class (the stage itself is class-independent)
 __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                    int cls) {
-    const uint32_t n = st.counts[kCountsNee + cls];
+    const uint32_t n = st.counts[cnt_nee(cls)];
     const uint32_t *queue = st.queue[cls];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 4 + cls, (unsigned long long) n);   // queue sizes
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n)   // queue sizes: roughgrating / everything else
+        atomicAdd(st.counters + (cls == PLTB_BSDF_ROUGHGRATING ? 5 : 4), (unsigned long long) n);
     DevPush push;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_nee_light(sc, st, queue[e], push, cnt);
@@ -221,11 +222,11 @@ struct GratingInsideBlock {
 template <int Class>
 __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc,
                                                                       const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[kCountsNee + Class];
+    const uint32_t n = st.counts[cnt_nee(Class)];
     const uint32_t *queue = st.queue[Class];
     DevPush push;
 #ifndef PLTB_NEEPOST_DIRECT
-    if (Class == 1) {
+    if (Class == PLTB_BSDF_ROUGHGRATING) {
         __shared__ ScanItem items[128];
         __shared__ uint32_t n_items;
         __shared__ uint8_t flag[128];
@@ -233,17 +234,17 @@ __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ Device
         for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
             const uint32_t e = base + threadIdx.x;
             const bool valid = e < n;
-            stage_nee_post_rb<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
+            stage_nee_post<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
         }
         return;
     }
 #endif
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post<Class>(sc, st, queue[e], push);
+        stage_nee_post<Class>(sc, st, queue[e], true, push, GratingInsideDirect());
 }
 
 __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[kCountsNee + 2];
+    const uint32_t n = st.counts[kCntEval];
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 6, (unsigned long long) n);
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_nee_eval(sc, st, st.queue_eval[e]);
@@ -414,7 +415,7 @@ __global__ void k_develop(const float4 *accum, float *rgb, uint64_t n_pixels) {
 template <int Class>
 __global__ void __launch_bounds__(128) k_shade_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                    uint32_t bounce) {
-    const uint32_t n = st.counts[4 * bounce + 1 + Class];
+    const uint32_t n = st.counts[cnt_shade(bounce, Class)];
     const uint32_t *list = st.shade_q[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     DevPush push;
@@ -425,7 +426,7 @@ __global__ void __launch_bounds__(128) k_shade_pol(const __grid_constant__ Devic
 
 template <int Class>
 __global__ void __launch_bounds__(128) k_nee_post_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[kCountsNee + Class];
+    const uint32_t n = st.counts[cnt_nee(Class)];
     const uint32_t *queue = st.queue[Class];
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_nee_post_pol<Class>(sc, st, queue[e]);
@@ -513,31 +514,45 @@ void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, i
     k_trace<false><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_TRACE);
     k_classify<<<grid, 256, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_CLASSIFY);
 }
-void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
-    if (st.pv_w) {   // polarized variant
-        if (cls) { k_shade_pol<1><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_GRATING); }
-        else { k_shade_pol<0><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_OTHER); }
-        return;
+// one instantiation per material class (BSDF plugin type); `cls` selects it at run time
+template <template <int> class Launch, class... Args> static void dispatch_class(int cls, Args &&...args) {
+    switch (cls) {
+        case PLTB_BSDF_NULL: Launch<PLTB_BSDF_NULL>::run(args...); break;
+        case PLTB_BSDF_DIFFUSE: Launch<PLTB_BSDF_DIFFUSE>::run(args...); break;
+        case PLTB_BSDF_CONDUCTOR: Launch<PLTB_BSDF_CONDUCTOR>::run(args...); break;
+        case PLTB_BSDF_DIELECTRIC: Launch<PLTB_BSDF_DIELECTRIC>::run(args...); break;
+        case PLTB_BSDF_ROUGHCONDUCTOR: Launch<PLTB_BSDF_ROUGHCONDUCTOR>::run(args...); break;
+        case PLTB_BSDF_ROUGHGRATING: Launch<PLTB_BSDF_ROUGHGRATING>::run(args...); break;
+        case PLTB_BSDF_PRINCIPLED: Launch<PLTB_BSDF_PRINCIPLED>::run(args...); break;
+        default: break;
     }
-    if (cls) { k_shade<1><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_GRATING); }
-    else { k_shade<0><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_SHADE_OTHER); }
+}
+template <int C> struct LaunchShade {
+    static void run(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
+        if (st.pv_w) k_shade_pol<C><<<grid, 128, 0, s>>>(sc, st, bounce);   // polarized variant
+        else k_shade<C><<<grid, 128, 0, s>>>(sc, st, bounce);
+    }
+};
+template <int C> struct LaunchNeePost {
+    static void run(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s) {
+        if (st.pv_w) k_nee_post_pol<C><<<grid, 128, 0, s>>>(sc, st);        // polarized: grating scan and evaluation in one kernel
+        else k_nee_post<C><<<grid, 128, 0, s>>>(sc, st);
+    }
+};
+void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
+    dispatch_class<LaunchShade>(cls, sc, st, bounce, grid, s);
+    PLTB_AFTER(cls == PLTB_BSDF_ROUGHGRATING ? PLTB_K_SHADE_GRATING : PLTB_K_SHADE_OTHER);
 }
 // emitter sampling for both queues, then all shadow rays in one persistent-warp launch
-void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s) {
-    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 1); PLTB_AFTER(PLTB_K_NEE_LIGHT);
-    k_nee_light<<<grid, 256, 0, s>>>(sc, st, 0); PLTB_AFTER(PLTB_K_NEE_LIGHT);
+void launch_nee_light(const DeviceScene &sc, const PassState &st, uint32_t class_mask, int grid, cudaStream_t s) {
+    for (int cls = kClasses - 1; cls >= 0; --cls)
+        if (class_mask >> cls & 1u) { k_nee_light<<<grid, 256, 0, s>>>(sc, st, cls); PLTB_AFTER(PLTB_K_NEE_LIGHT); }
     k_trace<true><<<grid, 128, 0, s>>>(sc, st, 0); PLTB_AFTER(PLTB_K_TRACE_SHADOW);
 }
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
-    if (st.pv_w) {   // polarized variant: scan and evaluation of the grating in one kernel
-        if (cls) { k_nee_post_pol<1><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING); }
-        else { k_nee_post_pol<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
-        return;
-    }
-    if (cls) {
-        k_nee_post<1><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING);
-        k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL);
-    } else { k_nee_post<0><<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_OTHER); }
+    dispatch_class<LaunchNeePost>(cls, sc, st, grid, s);
+    PLTB_AFTER(cls == PLTB_BSDF_ROUGHGRATING ? PLTB_K_NEE_POST_GRATING : PLTB_K_NEE_POST_OTHER);
+    if (cls == PLTB_BSDF_ROUGHGRATING && !st.pv_w) { k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL); }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s) {

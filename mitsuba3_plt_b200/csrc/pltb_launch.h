@@ -11,7 +11,7 @@ extern thread_local LaunchHook g_launch_hook;
 void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s);
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s);
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s);
-void launch_nee_light(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s);
+void launch_nee_light(const DeviceScene &sc, const PassState &st, uint32_t class_mask, int grid, cudaStream_t s);
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s);
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s);

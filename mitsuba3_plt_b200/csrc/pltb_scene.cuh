@@ -42,8 +42,9 @@ struct DeviceScene {
 
 struct Ray { V3 o, d; float maxt; };
 struct Hit { float t, u, v; uint32_t prim; int32_t shape; uint32_t cls; };   // cls: material class of the shape (tri_data)
-// closest hit as stored per path: {t, u, v, prim | cls << 30}; prim < 2^24 (pltb_scene_create); 0xFFFFFFFF = miss
+// closest hit as stored per path: {t, u, v, prim | cls << 28}; prim < 2^24 (pltb_scene_create), cls < 8; 0xFFFFFFFF = miss
 constexpr uint32_t kHitPrimMask = 0x00FFFFFFu, kHitMiss = 0xFFFFFFFFu;
+constexpr int kHitClsShift = 28;
 
 PLTB_HD V3 ld3(const float *p, uint32_t i) { return mk3(PLTB_LDG(p + 3 * i), PLTB_LDG(p + 3 * i + 1), PLTB_LDG(p + 3 * i + 2)); }
 PLTB_HD V2 ld2(const float *p, uint32_t i) { return mk2(PLTB_LDG(p + 2 * i), PLTB_LDG(p + 2 * i + 1)); }

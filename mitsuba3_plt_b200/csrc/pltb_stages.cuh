@@ -75,10 +75,10 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
                        bool rng_dirty, Push &push) {
     if (h.shape >= 0) {
         if (rng_dirty) {   // bounce 0 (k_raygen); k_trace has already written the record
-            st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim | (h.cls << 30)));
+            st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim | (h.cls << kHitClsShift)));
             st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
         }
-        push(st.shade_q[h.cls], st.counts + 4 * i + 1 + h.cls, local);
+        push(st.shade_q[h.cls], st.counts + cnt_shade(i, h.cls), local);
     } else {
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
         st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
@@ -177,7 +177,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     const size_t r = (size_t) i * st.chunk + local;
     if (active_next) st.v_w[r] = s4_to_f4(wbsdf_weight<Class>(sc, b, si.wi, si.uv, wl, so.wo));
     cnt[2]++;
-    if (Class == 1) cnt[3]++;
+    if (Class == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
 
     Ray next = si.spawn_ray(si.sh.to_world(so.wo));
     if (active_next) { alpha = so.weight * alpha; eta = so.eta; }
@@ -200,7 +200,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.v_alpha[r] = s4_to_f4(ai);
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
         st.v_wiz_shape[r] = ws;
-        push(st.queue[Class], st.counts + kCountsNee + Class, local | (i << 27));
+        push(st.queue[Class], st.counts + cnt_nee(Class), local | (i << 27));
     } else {
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
@@ -212,7 +212,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.p_alpha[local] = s4_to_f4(alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = delta ? 1u : 0u;
-        push(st.live, st.counts + 4 * (i + 1), local);
+        push(st.live, st.counts + cnt_live(i + 1), local);
     } else {
         st.n_vertices[local] = i + 1;
     }
@@ -282,7 +282,7 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
 #if defined(__CUDA_ARCH__)
         if (st.n_shadow) atomicAdd(st.n_shadow + local, 1u);
 #endif
-        push(st.shadow_q, st.counts + kCountsNee + 3, entry);
+        push(st.shadow_q, st.counts + kCntShadow, entry);
     }
 }
 
@@ -294,66 +294,8 @@ PLTB_HD Ray nee_shadow_ray(const PassState &st, size_t r) {
     return si.spawn_ray_to(mk3(w4.x, w4.y, w4.z));
 }
 
-template <int Class, class Push>
-PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push) {
-    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
-    const size_t r = (size_t) depth * st.chunk + local;
-    const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
-    const float2 ws = st.v_wiz_shape[r];
-    SI si;
-    si.t = 0.f;
-    si.p = mk3(a0.x, a0.y, a0.z); si.n = mk3(a1.x, a1.y, a1.z); si.uv = mk2(a0.w, a1.w);
-    si.sh.s = mk3(a2.x, a2.y, a2.z); si.sh.n = mk3(a3.x, a3.y, a3.z); si.sh.t = cross(si.sh.n, si.sh.s);
-    si.wi = mk3(a2.w, a3.w, ws.x);
-    si.shape = (int32_t) f2u(ws.y);
-    const S4 wl = f4_to_s4(st.wl[local]);
-    DirectionSample ds;
-    ds.p = mk3(w4.x, w4.y, w4.z);
-    ds.delta = signbit_(w4.w);
-    ds.pdf = fabsf(w4.w);            // 0 when the shadow ray was occluded
-    ds.d = normalize(ds.p - si.p);
-    const S4 em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_nee[r]) : s4(0.f);
-    V3 wo = si.sh.to_local(ds.d);
-    const pltb_bsdf *b = si_bsdf(sc, si.shape);
-    S4 a = f4_to_s4(st.v_alpha[r]);
-    if (Class == 1) {
-        // RoughGrating::wbsdf_eval is only non-zero inside the few-degree windows around the diffraction lobes: 9 % of the NEE
-        // directions on cbox-grating, 6 % once unlit samples are excluded.  For well-formed inputs (finite, unit wi / wo,
-        // finite throughput: then every factor of the product is finite) an unlit sample or one outside every window
-        // contributes exactly 0, as in the reference; the rest is compacted into `queue_eval` so that the Bessel terms are
-        // evaluated by dense warps (k_nee_eval).  Anything else takes the generic path below.
-        V3 wi_f = si.wi, wo_f = wo;
-        twosided_flip(b, wi_f, wo_f);
-        const float fsum = wi_f.x + wi_f.y + wi_f.z + wo_f.x + wo_f.y + wo_f.z + a.v[0] + a.v[1] + a.v[2] + a.v[3] +
-                           em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
-        const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
-        if (sane) {
-            const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
-            bool inside = false;
-            if (lit) {
-                GratingLoop gl; gl.init(*b, wi_f, si.uv, wl, wo_f);
-                GratingHits h; grating_scan(gl, wo_f, h);
-                inside = h.n > 0;
-            }
-            if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
-            float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
-            float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-            st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
-            st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);
-            push(st.queue_eval, st.counts + kCountsNee + 2, entry);
-            return;
-        }
-    }
-    S4 bsdf_val = wbsdf_eval<Class>(sc, b, si.wi, si.uv, wl, wo);
-    float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
-    float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-    st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
-}
-
-#ifndef PLTB_NEEPOST_DIRECT
-// Form of stage_nee_post used by the block-rebalanced lobe scan of k_nee_post<1> (same arithmetic on the same inputs).
-// does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<1>; k_nee_post can
-// substitute a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
+// does the light direction fall inside any lobe window of the grating?  (the divergent part of stage_nee_post<roughgrating>;
+// k_nee_post substitutes a functor that hands the lit items of a block to dense threads -- same function, same inputs, other thread)
 struct GratingInsideDirect {
     PLTB_HD bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
         if (!want) return false;
@@ -363,10 +305,10 @@ struct GratingInsideDirect {
     }
 };
 
+// `valid` is false for the tail threads of a block-uniform loop (k_nee_post<roughgrating>): they load nothing and only take part in
+// the barriers a block-level `inside_fn` may contain, which is why that call sits at one program point that every thread reaches.
 template <int Class, class Push, class Inside>
-PLTB_HD void stage_nee_post_rb(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
-    // `valid` is false for the tail threads of a block-uniform loop: they load nothing and only take part in the barriers a
-    // block-level `inside_fn` may contain, which is why that call sits at one program point that every thread reaches.
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
     SI si;
@@ -393,7 +335,7 @@ PLTB_HD void stage_nee_post_rb(const DeviceScene &sc, const PassState &st, uint3
         b = si_bsdf(sc, si.shape);
         a = f4_to_s4(st.v_alpha[r]);
     }
-    if (Class == 1) {
+    if (Class == PLTB_BSDF_ROUGHGRATING) {
         // RoughGrating::wbsdf_eval is only non-zero inside the few-degree windows around the diffraction lobes: 9 % of the NEE
         // directions on cbox-grating, 6 % once unlit samples are excluded.  For well-formed inputs (finite, unit wi / wo,
         // finite throughput: then every factor of the product is finite) an unlit sample or one outside every window
@@ -413,7 +355,7 @@ PLTB_HD void stage_nee_post_rb(const DeviceScene &sc, const PassState &st, uint3
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
             st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
             st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);
-            push(st.queue_eval, st.counts + kCountsNee + 2, entry);
+            push(st.queue_eval, st.counts + kCntEval, entry);
             return;
         }
     }
@@ -423,7 +365,6 @@ PLTB_HD void stage_nee_post_rb(const DeviceScene &sc, const PassState &st, uint3
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
 }
-#endif
 
 // second half of solve_replay_NEE for the roughgrating vertices whose light direction falls inside a lobe window
 PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t entry) {
@@ -435,7 +376,7 @@ PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t
     const V2 uv = mk2(a0.w, a1.w);
     const S4 wl = f4_to_s4(st.wl[local]);
     const pltb_bsdf *b = si_bsdf(sc, (int32_t) f2u(ws.y));
-    S4 bsdf_val = wbsdf_eval<1>(sc, b, wi, uv, wl, wo);
+    S4 bsdf_val = wbsdf_eval<PLTB_BSDF_ROUGHGRATING>(sc, b, wi, uv, wl, wo);
     st.v_nee[r] = s4_to_f4((f4_to_s4(st.v_nee[r]) * bsdf_val) * f4_to_s4(st.v_alpha[r]));
 }
 

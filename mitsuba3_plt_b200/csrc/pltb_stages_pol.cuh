@@ -129,7 +129,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
                 st.pv_w[(size_t) (4 * k + row) * st.nv + r] = mkf4(W.m[row][0], W.m[row][1], W.m[row][2], W.m[row][3]);
         }
     cnt[2]++;
-    if (Class == 1) cnt[3]++;
+    if (Class == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
 
     Ray next = si.spawn_ray(si.sh.to_world(so.wo));
     if (active_next) {
@@ -153,7 +153,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         pol_store_col(st.pv_alpha, st.nv, r, ai);
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
         st.v_wiz_shape[r] = ws;
-        push(st.queue[Class], st.counts + kCountsNee + Class, local | (i << 27));
+        push(st.queue[Class], st.counts + cnt_nee(Class), local | (i << 27));
     } else {
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
@@ -165,7 +165,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         pol_store_col(st.pp_alpha, st.chunk, local, alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = delta ? 1u : 0u;
-        push(st.live, st.counts + 4 * (i + 1), local);
+        push(st.live, st.counts + cnt_live(i + 1), local);
     } else {
         st.n_vertices[local] = i + 1;
     }
