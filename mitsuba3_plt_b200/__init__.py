@@ -257,6 +257,10 @@ class PLTIntegrator:
         if self.max_depth < 0 and self.max_depth != -1:
             raise RuntimeError('"max_depth" must be set to -1 (infinite) or a value >= 0')
         if self.max_depth == -1 or self.max_depth > capi.PLTB_MAX_DEPTH:
+            import warnings   # the reference has no bound (dr.alloc_local(BounceData3f, max_depth), plt.py:60); the ABI does
+            warnings.warn(f"plt: max_depth={self.max_depth} exceeds the bound of this build (PLTB_MAX_DEPTH = {capi.PLTB_MAX_DEPTH}); "
+                          f"paths are truncated at {capi.PLTB_MAX_DEPTH} vertices, which biases the image relative to the reference",
+                          RuntimeWarning, stacklevel=3)
             self.max_depth = capi.PLTB_MAX_DEPTH
         if self.rr_depth <= 0:
             raise RuntimeError('"rr_depth" must be set to a value greater than zero!')

@@ -2,6 +2,7 @@
 // NCCL film reduce.  No CPU rendering path exists in this library: every entry point that computes launches CUDA kernels.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: ranges per wavefront stage for nsys / ncu --nvtx (no-ops without a tool attached)
 
 #include <atomic>
 #include <cstdio>
@@ -14,6 +15,8 @@
 #include "pltb_launch.h"
 
 using namespace pltb;
+
+struct NvtxRange { explicit NvtxRange(const char *name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
@@ -232,9 +235,10 @@ int pltb_scene_update_sensor(pltb_scene *s, uint32_t sensor_index, const float t
     if (!s || sensor_index >= s->sensors.size()) return fail(PLTB_ERR_INVALID, "pltb_scene_update_sensor: bad sensor index");
     CU(cudaSetDevice(s->ctx->device));
     memcpy(s->sensors[sensor_index].to_world, to_world, 16 * sizeof(float));
+    // stream-ordered: the copy is queued behind the renders already submitted and ahead of the next one; the source is pageable
+    // host memory, which the runtime stages before cudaMemcpyAsync returns, so no synchronisation is needed here
     CU(cudaMemcpyAsync(s->d_sensors + sensor_index, &s->sensors[sensor_index], sizeof(pltb_sensor), cudaMemcpyHostToDevice,
                        s->ctx->stream));
-    CU(cudaStreamSynchronize(s->ctx->stream));
     return 0;
 }
 
@@ -434,13 +438,22 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     const int nee_grid = wf_grid;
     const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
     for (uint64_t first = 0; first < total; first += st.chunk) {
-        if (c->cancel.load()) { cudaStreamSynchronize(s); return fail(PLTB_ERR_CANCELLED, "render cancelled"); }
+        if (c->cancel.load()) {
+            // with several ranks the peers are (or will be) waiting in the film reduce: take part in it before leaving, so that a
+            // cancel on one rank cannot hang the others (pltb_cancel should still be called on every rank)
+            if ((prm->flags & PLTB_RENDER_REDUCE) && c->world > 1)
+                g_nccl.Reduce(c->accum, c->accum, n_acc, /* ncclFloat32 */ 7, /* ncclSum */ 0, 0, c->comm, s);
+            cudaStreamSynchronize(s);
+            return fail(PLTB_ERR_CANCELLED, "render cancelled");
+        }
+        NvtxRange pass_range("pltb:pass");
         pp.first = first;
         pp.count = (uint32_t) std::min<uint64_t>(st.chunk, total - first);
         CU(cudaMemsetAsync(st.counts, 0, kCountsTotal * sizeof(uint32_t), s));
         PROF();
         if (profile) KHook::mark(-1, c);
         // sample phase as dense per-bounce wavefronts: raygen + trace(0), then shade(i) / trace(i + 1)
+        nvtxRangePushA("pltb:sample_phase");
         launch_raygen(scene->dev, st, pp, s);
         // one k_shade / k_nee_post launch per material class the scene contains (roughgrating first: the longest kernel)
         const uint32_t cm = scene->class_mask;
@@ -451,13 +464,17 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
             launches += n_cls;
             if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches += 2; }
         }
+        nvtxRangePop();
         PROF();
+        nvtxRangePushA("pltb:solve_nee");
         launch_nee_light(scene->dev, st, cm, nee_grid, s);
         for (int cls = kClasses - 1; cls >= 0; --cls)
             if ((cm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(scene->dev, st, cls, nee_grid, s);
         PROF();
         if (has_grating) launch_nee_post(scene->dev, st, PLTB_BSDF_ROUGHGRATING, nee_grid, s);
+        nvtxRangePop();
         PROF();
+        NvtxRange film_range("pltb:gather_splat");
         launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
@@ -466,6 +483,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     CU(cudaGetLastError());
     PROF();   // tail event 0
     if ((prm->flags & PLTB_RENDER_REDUCE) && c->world > 1) {
+        NvtxRange reduce_range("pltb:film_reduce");
         // one sum-reduce of the raw RGBW accumulator to rank 0 per render over NVLink
         int r = g_nccl.Reduce(c->accum, c->accum, n_acc, /* ncclFloat32 */ 7, /* ncclSum */ 0, 0, c->comm, s);
         if (r != 0) return fail(PLTB_ERR_CUDA, std::string("ncclReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error"));

@@ -36,6 +36,8 @@ struct DevFilm {
     }
 };
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 __device__ __forceinline__ void flush_counters(const uint32_t cnt[4], unsigned long long *counters) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -165,8 +167,27 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceSce
     const uint32_t *list = st.shade_q[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     DevPush push;
+#ifdef PLTB_SHADE_PREFETCH
+    // software pipeline over the grid-stride loop: the queue entry of the item after next is loaded two iterations ahead, and the
+    // per-path state lines of the next item are pulled towards L2 while the current one is shaded (the item is a chain of
+    // dependent DRAM reads otherwise: entry -> state -> scene tables)
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t cur = e < n ? list[e] : 0u, nxt = e + stride < n ? list[e + stride] : 0u;
+    for (; e < n; e += stride) {
+        const uint32_t nn = e + 2 * stride < n ? list[e + 2 * stride] : 0u;
+        if (e + stride < n) {
+            prefetch_l2(st.p_ray_o + nxt); prefetch_l2(st.p_ray_d + nxt); prefetch_l2(st.p_hit + nxt); prefetch_l2(st.wl + nxt);
+            prefetch_l2(st.rng_state + nxt); prefetch_l2(st.rng_inc + nxt);
+            if (bounce > 0) { prefetch_l2(st.p_alpha + nxt); prefetch_l2(st.p_prev + nxt); prefetch_l2(st.p_flags + nxt); }
+        }
+        stage_shade<Class>(sc, st, cur, bounce, push, cnt);
+        cur = nxt; nxt = nn;
+    }
+#else
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
         stage_shade<Class>(sc, st, list[e], bounce, push, cnt);
+#endif
     flush_counters(cnt, st.counters);
 }
 

@@ -212,6 +212,24 @@ PLTB_NI float bessel_j(const BesselTables &bt, float x, int nu) {
     float weight_fn = 1.0f / (1.0f + expf(-1.5f * (fabsf(x) - center)));
     return nsign * ((1.0f - weight_fn) * bessel_j_small(bt, x, nua) + weight_fn * bessel_j_asymp(x, nua));
 }
+// J_nu1(x) and J_nu2(x) in ONE pass over the Simpson nodes: the same operations per value as two bessel_j calls (bit-identical
+// results), but the two independent cosf chains overlap and a warp whose lanes need different orders makes one trip through the
+// loop instead of two half-empty ones (RoughGrating::wbsdf_sample evaluates lobe_intensity((lx, ly)) with lx, ly in -3..3).
+PLTB_NI void bessel_j_pair(const BesselTables &bt, float x, int nu1, int nu2, float &j1, float &j2) {
+    const int n1 = nu1 < 0 ? -nu1 : nu1, n2 = nu2 < 0 ? -nu2 : nu2;
+    const float f1 = (float) n1, f2 = (float) n2;
+    float o1 = 0.f, e1 = 0.f, o2 = 0.f, e2 = 0.f;
+#pragma unroll 1
+    for (int i = 1; i < 19; i += 2) { o1 += cosf(f1 * bt.t[i] - x * bt.sin_t[i]); o2 += cosf(f2 * bt.t[i] - x * bt.sin_t[i]); }
+#pragma unroll 1
+    for (int i = 2; i < 19; i += 2) { e1 += cosf(f1 * bt.t[i] - x * bt.sin_t[i]); e2 += cosf(f2 * bt.t[i] - x * bt.sin_t[i]); }
+    const float a1 = cosf(f1 * bt.t[0] - x * bt.sin_t[0]), b1 = cosf(f1 * bt.t[19] - x * bt.sin_t[19]);
+    const float a2 = cosf(f2 * bt.t[0] - x * bt.sin_t[0]), b2 = cosf(f2 * bt.t[19] - x * bt.sin_t[19]);
+    const float s1 = kInvPi * (bt.h_over_3 * (a1 + 4.0f * o1 + 2.0f * e1 + b1)), s2 = kInvPi * (bt.h_over_3 * (a2 + 4.0f * o2 + 2.0f * e2 + b2));
+    const float w1 = 1.0f / (1.0f + expf(-1.5f * (fabsf(x) - (45.f + f1)))), w2 = 1.0f / (1.0f + expf(-1.5f * (fabsf(x) - (45.f + f2))));
+    j1 = (nu1 < 0 ? -1.f : 1.f) * ((1.0f - w1) * s1 + w1 * bessel_j_asymp(x, n1));
+    j2 = (nu2 < 0 ? -1.f : 1.f) * ((1.0f - w2) * s2 + w2 * bessel_j_asymp(x, n2));
+}
 // Reduced-precision J_nu for *sampling decisions only* (DiffractionGrating::sample_lobe: which lobe is drawn and its discrete
 // pdf): the Simpson terms use MUFU.COS after a two-constant reduction to [-pi, pi] (absolute error ~5e-7 per term, ~1e-7 in
 // J).  Everything that scales radiance (lobe_intensity in wbsdf_sample / wbsdf_eval) keeps the precise cosf above: with the

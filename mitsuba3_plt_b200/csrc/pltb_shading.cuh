@@ -233,6 +233,15 @@ struct Grating {
     }
     PLTB_HD float lobe_intensity(const BesselTables &bt, int lx, int ly, V3 wi, float wl) const {
         const float a = kFourPi * q / (wl * fabsf(wi.z));
+#if defined(__CUDA_ARCH__) && !defined(PLTB_BESSEL_SEQUENTIAL)
+        if ((type & 0xFu) == 0 && !is_1d()) {   // sinusoidal, 2-D: both orders in one pass (same values as the two calls below)
+            if (lx == 0 && ly == 0) return multiplier * 1.0f * 1.0f;
+            float jx, jy;
+            bessel_j_pair(bt, a, lx, ly, jx, jy);
+            const float ix = lx == 0 ? 1.0f : sqr(jx), iy = ly == 0 ? 1.0f : sqr(jy);
+            return multiplier * ix * iy;
+        }
+#endif
         float ix = axis_term(bt, a, lx);
         float iy = is_1d() ? ix : axis_term(bt, a, ly);
         return multiplier * ix * iy;
