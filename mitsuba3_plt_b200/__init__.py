@@ -28,12 +28,25 @@ import numpy as np
 from . import capi, imageio
 from .scene import FlatScene, flatten
 from .xmlscene import Color, Properties, SpectrumValue, Transform, dict_to_tree, load_file_tree
+from .plt_types import (BounceData3f, Coherence3f, DiffractionGrating3f, DiffractionGratingType, Frame3f,  # noqa: F401
+                        GeneralizedRadiance3f, PLTBeam3f, PLTInteraction3f, PLTSamplePhaseData3f, ScalarVector2f, ScalarVector2i,
+                        ScalarVector3f, spectrum_from_file, spectrum_to_file)
 
 __all__ = ["set_variant", "variant", "load_file", "load_dict", "render", "traverse", "register_integrator",
            "PLTIntegrator", "Scene", "Properties", "ScalarTransform4f", "Transform4f", "Context", "context",
            "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized", "StokesIntegrator"]
 
 ScalarTransform4f = Transform4f = Transform
+
+
+class _Namespace:
+    """`mi.scalar_rgb.X`: the reference's scene-building scripts reach the scalar types through a variant module
+    (scripts/spectrograph/scene.py:75-86); here every variant exposes the same host-side types"""
+    DiffractionGrating3f, Coherence3f, Frame3f, Transform4f, PLTBeam3f = DiffractionGrating3f, Coherence3f, Frame3f, Transform, PLTBeam3f
+    ScalarVector2f, ScalarVector3f, ScalarVector2i = ScalarVector2f, ScalarVector3f, ScalarVector2i
+
+
+scalar_rgb = scalar_spectral = _Namespace
 
 _SUPPORTED_VARIANTS = ("cuda_spectral", "cuda_ad_spectral", "llvm_spectral", "llvm_ad_spectral", "scalar_spectral",
                        "cuda_spectral_polarized", "cuda_ad_spectral_polarized", "llvm_spectral_polarized",

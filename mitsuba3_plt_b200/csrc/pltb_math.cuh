@@ -16,6 +16,16 @@
 #  define PLTB_NI inline
 #endif
 
+// -DPLTB_DEBUG_CHECKS: device-side assertions on the invariants the kernels rely on (traversal stack bound, queue routing, record
+// indices).  compute-sanitizer is closed on the GPU pool this was developed on, so `tools/gpu.sh <tag> debugchecks` runs the GPU
+// test-suite against this build instead (profiles/r02_debugchecks.txt).
+#if defined(PLTB_DEBUG_CHECKS) && defined(__CUDA_ARCH__)
+#  include <assert.h>
+#  define PLTB_ASSERT(x) assert(x)
+#else
+#  define PLTB_ASSERT(x) ((void) 0)
+#endif
+
 namespace pltb {
 
 constexpr float kPi = 3.14159265358979323846f;

@@ -140,6 +140,7 @@ struct Traversal {
         t = umin_(k1, k3); k3 = umax_(k1, k3); k1 = t;
         t = umin_(k1, k2); k2 = umax_(k1, k2); k1 = t;
         if (k0 == 0xFFFFFFFFu) { pop(); return; }
+        PLTB_ASSERT(sp + 3 <= kBvhStack);
         if (k3 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k3 << 32) | child_ref(ch, k3);
         if (k2 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k2 << 32) | child_ref(ch, k2);
         if (k1 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k1 << 32) | child_ref(ch, k1);
@@ -156,6 +157,7 @@ struct Traversal {
             float4 q0 = PLTB_LDG(tp), q1 = PLTB_LDG(tp + 1), q2 = PLTB_LDG(tp + 2);
             uint32_t prim = f2u(q2.y);
             int32_t shape = (int32_t) f2u(q2.z);
+            PLTB_ASSERT(i < sc.n_prims && shape >= 0 && (uint32_t) shape < sc.n_shapes && f2u(q2.w) < 8u);
             float t, u = 0.f, v = 0.f;
             bool hit;
             if (prim < sc.n_faces) {

@@ -78,6 +78,7 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
             st.p_hit[local] = mkf4(h.t, h.u, h.v, u2f(h.prim | (h.cls << kHitClsShift)));
             st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
         }
+        PLTB_ASSERT(h.cls < (uint32_t) kClasses && st.shade_q[h.cls] != nullptr && local < st.chunk && i < st.max_depth);
         push(st.shade_q[h.cls], st.counts + cnt_shade(i, h.cls), local);
     } else {
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
@@ -128,9 +129,11 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
 // the parts of the solve phase that only depend on vertices 0..i (replay_path :408-472, solve_replay_emissive :315-405).
 template <int Class, class Push>
 PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
+    PLTB_ASSERT(local < st.chunk && i < st.max_depth);
     const float4 o4 = st.p_ray_o[local], d4 = st.p_ray_d[local], h4 = st.p_hit[local];
     Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
     Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w) & kHitPrimMask; h.cls = (uint32_t) Class;
+    PLTB_ASSERT(f2u(h4.w) != kHitMiss && ((f2u(h4.w) >> kHitClsShift) & 7u) == (uint32_t) Class && h.prim < sc.n_faces + sc.n_shapes);
     h.shape = h.prim < sc.n_faces ? (int32_t) PLTB_LDG(sc.face_shape + h.prim) : (int32_t) (h.prim - sc.n_faces);
     const S4 wl = f4_to_s4(st.wl[local]);
     PCG32 rng; rng.state = st.rng_state[local]; rng.inc = st.rng_inc[local];
@@ -229,6 +232,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 template <class Push>
 PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push, uint32_t cnt[4]) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    PLTB_ASSERT(local < st.chunk && depth < st.max_depth);
     const size_t r = (size_t) depth * st.chunk + local;
     const float4 a0 = st.v_p_u[r];
     const V3 p = mk3(a0.x, a0.y, a0.z);

@@ -404,39 +404,24 @@ def write_disk(directory):
     return path
 
 
-def _grating_diffract(wi, lobe, wl_um, inv_period, grating_angle=0.0):
-    """DiffractionGrating::diffract (include/mitsuba/plt/diffractiongrating.h:201-226), non-radial grating, float64;
-    only used to place the spectrograph's sensors."""
-    gd = (math.cos(grating_angle), math.sin(grating_angle))
-    sin_i = []
-    for c in (wi[0], wi[1]):
-        pp = math.sqrt(c * c + wi[2] * wi[2])
-        sin_i.append(c / pp if pp > 1.1920929e-07 else 0.0)
-    lr = (gd[0] * lobe[0] - gd[1] * lobe[1], gd[1] * lobe[0] + gd[0] * lobe[1])
-    a = wl_um * lr[0] * inv_period[0] - sin_i[0]
-    b = wl_um * lr[1] * inv_period[1] - sin_i[1]
-    m = (a * a - 1) / (a * a * b * b - 1)
-    q = 1 - b * b * m
-    return (a * math.sqrt(max(0.0, q)), b * math.sqrt(m), math.sqrt(max(0.0, 1 - a * a * q - b * b * m)))
-
-
 def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_wl=400.0, max_wl=700.0, use_srfs=True):
     """C3: the scene `scripts/spectrograph/scene.py:57-175` builds -- a batch of `n` orthographic 1x1 sensors, each looking
     along the second-order diffraction direction of its wavelength with a Gaussian SRF (`gen_srfs.py`), one `rectangle`
     with a ggx sinusoidal `roughgrating`, one `directional` light whose irradiance is `spectrum`:
     "bbody_<K>" (blackbody), "d65", "prior" (uniform 1)."""
-    from .xmlscene import look_at
+    import mitsuba3_plt_b200 as mi
     os.makedirs(os.path.join(directory, "spectra"), exist_ok=True)
+    # gen_srfs (scripts/spectrograph/gen_srfs.py:35-47)
     delta = (max_wl - min_wl) / (n + 2)
     domain = np.linspace(min_wl, max_wl, points)
     measured = np.linspace(min_wl, max_wl, n + 2)[1:-1]
-    # shading frame of the patch (s, t, n) and the light direction (scene.py:82-93)
-    fs, ft, fn = (0.0, -1.0, 0.0), (0.0, 0.0, 1.0), (1.0, 0.0, 0.0)
+    # generate_scene_elements (scripts/spectrograph/scene.py:57-144), through the same public types the script uses
+    grating = mi.scalar_rgb.DiffractionGrating3f(0.0, mi.ScalarVector2f(0.7, 0.7), 0.05, 5, mi.DiffractionGratingType.Sinusoidal, 1,
+                                                 mi.ScalarVector2f(0.0))
+    grating_frame = mi.scalar_rgb.Frame3f(mi.ScalarVector3f(0, -1, 0), mi.ScalarVector3f(0, 0, 1), mi.ScalarVector3f(1, 0, 0))
     inc = math.radians(-15) - math.pi / 2
-    light = (math.sin(inc), 0.0, math.cos(inc))
-    to_local = lambda v: tuple(sum(a * b for a, b in zip(f, v)) for f in (fs, ft, fn))
-    to_world = lambda v: tuple(fs[i] * v[0] + ft[i] * v[1] + fn[i] * v[2] for i in range(3))
-    ll = to_local(light)
+    light = (math.sin(inc), 0.0, math.cos(inc))   # scalar_sph_to_dir(incident, 0), scripts/utils/math.py:16-21
+    light_dir_local = grating_frame.to_local(light)
     x = ['<scene version="2.1.0">\n  <default name="spp" value="512"/>\n'
          '  <integrator type="plt"><integer name="max_depth" value="7"/><integer name="rr_depth" value="50"/></integrator>\n'
          '  <sensor type="batch">\n']
@@ -444,11 +429,10 @@ def write_spectrograph(directory, spectrum="bbody_3000", n=150, points=150, min_
         std = delta / 4
         srf = np.exp(-np.square(domain - wl) / (2 * std ** 2))
         srf /= np.trapezoid(srf, domain)
-        with open(os.path.join(directory, "spectra", f"srf_{i}.spd"), "w") as f:
-            for a, b in zip(domain, srf):
-                f.write(f"{np.float32(a)!r} {np.float32(b)!r}\n".replace("np.float32(", "").replace(")", ""))
-        d = to_world(_grating_diffract((-ll[0], -ll[1], -ll[2]), (2, 0), float(wl) * 1e-3, (0.7, 0.7)))
-        m = look_at([0.4 * c for c in d], [0, 0, 0], [0, 0, 1])
+        mi.spectrum_to_file(os.path.join(directory, "spectra", f"srf_{i}.spd"), domain, srf)
+        local_diff_dir, _ = grating.diffract(-light_dir_local, mi.ScalarVector2i(2, 0), float(wl * 1e-3))
+        diff_dir = grating_frame.to_world(local_diff_dir)
+        m = mi.scalar_rgb.Transform4f().look_at(origin=np.ravel(diff_dir * 0.4), target=[0, 0, 0], up=[0, 0, 1]).matrix
         srf_xml = f'<spectrum name="srf" filename="spectra/srf_{i}.spd"/>' if use_srfs else ""
         x.append(f'    <sensor type="orthographic" name="sensor{i}">{_xf(m.reshape(-1))}<film type="hdrfilm">'
                  '<integer name="width" value="1"/><integer name="height" value="1"/>'

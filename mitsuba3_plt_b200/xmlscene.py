@@ -87,6 +87,12 @@ class Transform:
     def rotate(self, axis, angle): return self @ Transform(rotate(axis, angle))
     def look_at(self, origin, target, up): return self @ Transform(look_at(origin, target, up))
 
+    def to_frame(self, frame):
+        """Transform4f.to_frame(Frame3f): columns s, t, n (include/mitsuba/core/transform.h)"""
+        m = np.eye(4)
+        m[:3, 0], m[:3, 1], m[:3, 2] = frame.s, frame.t, frame.n
+        return self @ Transform(m)
+
 
 def _floats(s):
     return [float(x) for x in re.split(r"[\s,]+", s.strip()) if x]

@@ -199,3 +199,21 @@ def test_errors(mi, integ):
     assert b"spp" in capi.lib().pltb_last_error()
     prm = capi.RenderParams(seed=0, spp=4, spp_begin=0, spp_count=4, max_depth=0, rr_depth=50)
     assert capi.lib().pltb_render(ctx._h, sc.device(ctx), C.byref(prm), None, None, None) == -1
+
+
+def test_strip_splat_equals_per_tap_atomics(mi, integ, monkeypatch):
+    """k_splat_strip merges 32 register footprints into a shared-memory strip with plain read-modify-writes ordered by
+    __syncwarp; a lost update would show as missing film weight.  Against the per-tap vector-atomic path (PLTB_SPLAT_DIRECT):
+    the W channel (a sum of filter weights, no cancellation) must agree to float32 summation-order accuracy, RGB likewise.
+    (compute-sanitizer's racecheck is closed on the GPU pool; this and the -DPLTB_DEBUG_CHECKS run stand in for it.)"""
+    from mitsuba3_plt_b200 import scenes
+    for name, res, spp in (("cbox-grating", 96, 64), ("veach-mis", 80, 32)):   # 5x5 Gaussian and 3x3 tent footprints
+        sc = scenes.load(name, resx=res, resy=res)
+        a = integ.render(sc, spp=spp, seed=2, develop=False)
+        monkeypatch.setenv("PLTB_SPLAT_DIRECT", "1")
+        b = integ.render(sc, spp=spp, seed=2, develop=False)
+        monkeypatch.delenv("PLTB_SPLAT_DIRECT")
+        np.testing.assert_allclose(a[..., 3], b[..., 3], rtol=2e-5, atol=1e-5)
+        fin = np.isfinite(a).all(-1) & np.isfinite(b).all(-1)
+        assert (np.isfinite(a).all(-1) == np.isfinite(b).all(-1)).all()
+        np.testing.assert_allclose(a[fin], b[fin], rtol=2e-4, atol=1e-4)

@@ -436,3 +436,51 @@ def test_polarized_oracle_converges_to_the_reference_published_spectrograph(mi, 
     s0 = r["image"][0, :, 3:6]
     assert np.median(np.abs(s0 - want) / np.maximum(np.abs(want), 1e-6)) <= 0.03
     assert abs(s0[:, 2].sum() / want[:, 2].sum() - 1) <= 0.015
+
+
+def test_plt_type_surface(mi, tmp_path):
+    """The PLT value types the reference binds (src/plt/python/plt_v.cpp:6-77): DiffractionGrating3f against the known answers of
+    the reference's own header (tests/golden/ref_kat.json), Coherence3f against ref_kat_pol.json, the record types, and -- the way
+    scripts/spectrograph/scene.py:57-144 uses them -- the sensor placement of the reference's published spectrograph scene."""
+    import json
+    G = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_kat.json")))
+    for e in G["grating"][::11]:
+        angle, ipx, ipy, q, lobes, typ, radial, mult, u, v = G["grating_params"][e["g"]]
+        t = int(typ) | (mi.DiffractionGratingType.Radial if radial else 0)
+        g = mi.DiffractionGrating3f(angle, mi.ScalarVector2f(ipx, ipy), q, int(lobes), t, mult, mi.ScalarVector2f(u, v))
+        d, valid = g.diffract(e["wi"], mi.ScalarVector2i(*e["lobe"]), e["wl"])
+        assert valid == bool(e["valid"])
+        np.testing.assert_allclose(d, e["dir"], rtol=3e-5, atol=1e-6)
+        np.testing.assert_allclose(g.lobe_intensity(e["lobe"], e["wi"], e["wl"]), e["intensity"], rtol=3e-5, atol=1e-9)
+        np.testing.assert_allclose(g.lobe_pdf(e["lobe"], e["wi"], e["wl"]), e["pdf"], rtol=3e-5, atol=1e-9)
+    wi = np.array([0.3, -0.2, 0.9], np.float32); wi /= np.linalg.norm(wi)
+    for e in G["grating_sample"]:
+        angle, ipx, ipy, q, lobes, typ, radial, mult, u, v = G["grating_params"][e["g"]]
+        g = mi.scalar_rgb.DiffractionGrating3f(angle, (ipx, ipy), q, int(lobes), int(typ) | (0x10 if radial else 0), mult, (u, v))
+        lobe, pdf = g.sample_lobe(e["u"], wi, 0.55)
+        assert list(lobe) == e["lobe"]
+        np.testing.assert_allclose(pdf, e["pdf"], rtol=3e-5)
+        np.testing.assert_allclose(g.alpha(wi, 2 * np.pi / 0.55), e["alpha"], rtol=3e-5)
+    P = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_kat_pol.json")))
+    for k, det0, det1, opl in P["coherence"]:
+        c = mi.Coherence3f(1e-18, 1.0)
+        assert c.inv_coherence_det(k) == np.float32(det0)
+        c.propagate(2.5, True)
+        assert c.opl == np.float32(opl) and c.inv_coherence_det(k) == np.float32(det1)
+    gr = mi.GeneralizedRadiance3f(0.25)
+    assert gr.L == 0.25 and gr.L1 == 0.0 and float(gr.coherence.dmat[0, 0]) == float(np.float32(1e-3))   # plt.h:167-168
+    b = mi.BounceData3f(id=0, wo=[0, 0, 1], active=True)
+    assert b.active and b.interaction is None
+    beam = mi.PLTBeam3f(1.0, np.eye(2) * 1e-3, [0, 0, 0], [0, 0, 1], [1, 0, 0], distant=True)
+    assert float(beam.coherence.opl) == float(np.float32(0.001)) and beam.transverse_rotation().shape == (2, 2)
+    # .spd round trip (mi.spectrum_to_file / spectrum_from_file, spectrum.h:515-534)
+    p = str(tmp_path / "x.spd")
+    mi.spectrum_to_file(p, [400.0, 550.5, 700.0], [0.1, 0.25, 0.5])
+    wl, val = mi.spectrum_from_file(p)
+    assert wl == [400.0, 550.5, 700.0] and np.allclose(val, [0.1, 0.25, 0.5])
+    # scripts/spectrograph/scene.py through these types == the sensors of the reference's published scene.xml
+    from mitsuba3_plt_b200 import scenes
+    ours = scenes.load("spectrograph:bbody_3000", resx=1, resy=1)
+    ref = mi.load_file(os.path.join(ROOT, "tests", "golden", "scenes", "spectrograph-bbody-3000", "scene.xml"), resx=150, resy=1)
+    a = np.array([list(s.to_world) for s in ours.flat.c_sensors]); r = np.array([list(s.to_world) for s in ref.flat.c_sensors])
+    assert a.shape == r.shape == (150, 16) and np.abs(a - r).max() < 2e-6

@@ -10,7 +10,8 @@
 #   full[:scene:res:spp]      ncu --set full of one render; details / raw / source pages exported as text
 #   configs[:C1,C4]    tools/config_bench.py
 #   anim               tools/anim_bench.py
-#   sanitize           compute-sanitizer memcheck + racecheck + initcheck of the smoke render
+#   sanitize           compute-sanitizer memcheck + racecheck + initcheck of the smoke render (closed on this pool: see debugchecks)
+#   debugchecks        pytest -m gpu against a -DPLTB_DEBUG_CHECKS build (device-side assertions)
 T=${1:-r}; shift
 mkdir -p gpurun_out
 O=gpurun_out/$T
@@ -48,6 +49,9 @@ for step in "$@"; do
       only=${step#configs}; only=${only#:}
       timeout 1500 python tools/config_bench.py ${only:+--only $only} 2> ${O}_configs.err | tee ${O}_configs.jsonl ;;
     anim) timeout 600 python tools/anim_bench.py 2> ${O}_anim.err | tee ${O}_anim.jsonl ;;
+    debugchecks)   # the GPU test-suite against a build with device-side assertions (-DPLTB_DEBUG_CHECKS); stands in for compute-sanitizer
+      bash tools/build_variant.sh dbg -DPLTB_DEBUG_CHECKS > ${O}_debugchecks_build.log 2>&1
+      PLTB200_LIB=mitsuba3_plt_b200/libpltb200_dbg.so timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -5 | tee ${O}_debugchecks.log ;;
     sanitize)
       for tool in memcheck racecheck initcheck; do
         timeout 1200 compute-sanitizer --tool $tool python -c "import __graft_entry__ as g; g.smoke()" > ${O}_sanitize_$tool.log 2>&1
