@@ -84,6 +84,79 @@ def load_ply(path):
     return pos, nrm, uv, data["face"]
 
 
+# ---------------------------------------------------------------------------------------------------------------------
+# .serialized loader (src/shapes/serialized.cpp:240-400): header 0x041C + version 3/4, one zlib stream per sub-mesh, offset
+# dictionary (uint64 for v4, uint32 for v3) followed by the mesh count at the end of the file
+# ---------------------------------------------------------------------------------------------------------------------
+_SER_HEADER, _SER_NORMALS, _SER_UV, _SER_COLORS, _SER_DOUBLE = 0x041C, 0x0001, 0x0002, 0x0008, 0x2000
+
+
+def load_serialized(path, shape_index=0):
+    import struct
+    import zlib
+    buf = open(path, "rb").read()
+    fmt, version = struct.unpack_from("<HH", buf, 0)
+    if fmt != _SER_HEADER:
+        raise RuntimeError(f'"{path}": encountered an invalid file format!')
+    if version not in (3, 4):
+        raise RuntimeError(f'"{path}": encountered an incompatible file version!')
+    start = 4
+    if shape_index != 0:
+        count, = struct.unpack_from("<I", buf, len(buf) - 4)
+        if shape_index > count:
+            raise RuntimeError(f"Unable to unserialize mesh, shape index is out of range! (requested {shape_index} out of "
+                               f"0..{count - 1})")
+        if version == 4:
+            offset, = struct.unpack_from("<Q", buf, len(buf) - 8 * (count - shape_index) - 4)
+        else:
+            offset, = struct.unpack_from("<I", buf, len(buf) - 4 * (count - shape_index + 1))
+        start = offset + 4
+    raw = zlib.decompressobj().decompress(buf[start:])
+    flags, = struct.unpack_from("<I", raw, 0)
+    at = 4
+    if version == 4:
+        at = raw.index(b"\0", at) + 1
+    nv, nf = struct.unpack_from("<QQ", raw, at)
+    at += 16
+    ft = np.dtype("<f8" if flags & _SER_DOUBLE else "<f4")
+
+    def take(dim):
+        nonlocal at
+        a = np.frombuffer(raw, ft, nv * dim, at).reshape(nv, dim).astype(F32)
+        at += nv * dim * ft.itemsize
+        return a
+    pos = take(3)
+    nrm = take(3) if flags & _SER_NORMALS else None
+    uv = take(2) if flags & _SER_UV else None
+    if flags & _SER_COLORS:
+        take(3)
+    faces = np.frombuffer(raw, "<u4", nf * 3, at).reshape(nf, 3).astype(np.uint32)
+    return pos, nrm, uv, faces
+
+
+def write_serialized(path, meshes, version=4):
+    """The inverse of load_serialized, for fixtures: meshes = [(positions, normals | None, texcoords | None, faces), ...]"""
+    import struct
+    import zlib
+    out, offsets = bytearray(), []
+    for i, (pos, nrm, uv, faces) in enumerate(meshes):
+        offsets.append(len(out))
+        flags = 0x1000 | (_SER_NORMALS if nrm is not None else 0) | (_SER_UV if uv is not None else 0)
+        body = struct.pack("<I", flags) + (b"mesh%d\0" % i if version == 4 else b"")
+        body += struct.pack("<QQ", len(pos), len(faces)) + np.asarray(pos, "<f4").tobytes()
+        if nrm is not None:
+            body += np.asarray(nrm, "<f4").tobytes()
+        if uv is not None:
+            body += np.asarray(uv, "<f4").tobytes()
+        body += np.asarray(faces, "<u4").tobytes()
+        out += struct.pack("<HH", _SER_HEADER, version) + zlib.compress(body)
+    for o in offsets:
+        out += struct.pack("<Q" if version == 4 else "<I", o)
+    out += struct.pack("<I", len(meshes))
+    with open(path, "wb") as f:
+        f.write(bytes(out))
+
+
 def _xf_points(m, p):
     m = np.asarray(m, dtype=np.float64)
     return (p.astype(np.float64) @ m[:3, :3].T + m[:3, 3]).astype(F32)
@@ -424,12 +497,12 @@ class FlatScene:
         s.flags = capi.SHAPE_FLIP_NORMALS if flip else 0
         s.to_world, s.to_object = _m16(np.eye(4)), _m16(np.eye(4))
         idx = len(self.shapes)
-        if t in ("ply", "cube"):
-            if t == "ply":
+        if t in ("ply", "serialized", "cube"):
+            if t != "cube":
                 path = p["filename"]
                 if not os.path.isabs(path):
                     path = os.path.join(getattr(p, "base_path", "."), path)
-                pos, nrm, uv, faces = load_ply(path)
+                pos, nrm, uv, faces = load_ply(path) if t == "ply" else load_serialized(path, int(p.get("shape_index", 0)))
             else:
                 pos, nrm, uv, faces = _cube_mesh()
             face_normals = bool(p.get("face_normals", False))

@@ -292,7 +292,7 @@ def dict_to_tree(d, base="."):
 
 
 _CLS = {
-    "scene": "scene", "ply": "shape", "obj": "shape", "rectangle": "shape", "sphere": "shape", "cube": "shape",
+    "scene": "scene", "ply": "shape", "serialized": "shape", "obj": "shape", "rectangle": "shape", "sphere": "shape", "cube": "shape",
     "diffuse": "bsdf", "conductor": "bsdf", "dielectric": "bsdf", "roughconductor": "bsdf", "roughgrating": "bsdf",
     "twosided": "bsdf", "principled": "bsdf", "area": "emitter", "directional": "emitter", "constant": "emitter", "envmap": "emitter",
     "perspective": "sensor", "orthographic": "sensor", "batch": "sensor", "hdrfilm": "film",

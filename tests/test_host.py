@@ -484,3 +484,54 @@ def test_plt_type_surface(mi, tmp_path):
     ref = mi.load_file(os.path.join(ROOT, "tests", "golden", "scenes", "spectrograph-bbody-3000", "scene.xml"), resx=150, resy=1)
     a = np.array([list(s.to_world) for s in ours.flat.c_sensors]); r = np.array([list(s.to_world) for s in ref.flat.c_sensors])
     assert a.shape == r.shape == (150, 16) and np.abs(a - r).max() < 2e-6
+
+
+def test_serialized_meshes_headless_outputs_and_params_json(mi, tmp_path):
+    """the `serialized` shape (src/shapes/serialized.cpp:240-400, v3 and v4 offset dictionaries, shape_index) and
+    the output contract of scripts/rendering/main-headless.py:57-87 (file names, params.json keys, format_time)."""
+    from mitsuba3_plt_b200 import headless, scenes
+    from mitsuba3_plt_b200.scene import load_serialized, write_serialized
+    a = scenes.uv_sphere((0.1, 0.2, 0.3), 0.5)
+    b = scenes.uv_sphere((-1.0, 0.0, 2.0), 0.25)
+    meshes = [(a[0], a[1], a[2], a[3]), (b[0], None, None, b[3])]
+    for version in (3, 4):
+        path = str(tmp_path / f"m{version}.serialized")
+        write_serialized(path, meshes, version)
+        for i, (p, n, t, f) in enumerate(meshes):
+            p2, n2, t2, f2 = load_serialized(path, i)
+            assert np.array_equal(p, p2) and np.array_equal(f, f2)
+            assert (n is None and n2 is None) or np.array_equal(n, n2)
+            assert (t is None and t2 is None) or np.array_equal(t, t2)
+        with pytest.raises(RuntimeError, match="out of range"):
+            load_serialized(path, 3)
+    bad = tmp_path / "bad.serialized"
+    bad.write_bytes(b"\x00\x00\x04\x00rest")
+    with pytest.raises(RuntimeError, match="invalid file format"):
+        load_serialized(str(bad))
+    # the same mesh as a ply and as a serialized shape flattens to the same scene
+    scenes.write_ply(str(tmp_path / "s.ply"), a[0], a[3], a[1], a[2])
+    xml = """<scene version="3.0.0"><integrator type="plt"/>
+      <sensor type="perspective"><float name="fov" value="40"/><film type="hdrfilm"><integer name="width" value="8"/>
+      <integer name="height" value="8"/></film></sensor>
+      <shape type="%s"><string name="filename" value="%s"/>%s<bsdf type="diffuse"/></shape></scene>"""
+    (tmp_path / "a.xml").write_text(xml % ("ply", "s.ply", ""))
+    (tmp_path / "b.xml").write_text(xml % ("serialized", "m4.serialized", '<integer name="shape_index" value="0"/>'))
+    fa, fb = mi.load_file(str(tmp_path / "a.xml")).flat, mi.load_file(str(tmp_path / "b.xml")).flat
+    assert np.array_equal(fa.positions, fb.positions) and np.array_equal(fa.faces, fb.faces) and np.array_equal(fa.normals, fb.normals)
+    # format_time: scripts/utils/misc.py:6-30
+    assert headless.format_time(999) == "999 ns" and headless.format_time(1500) == "1.5 us"
+    assert headless.format_time(90e9) == "1.5 m" and headless.format_time(2 * 86400e9) == "2.0 d"
+    # output files + params.json from a synthetic stokes result
+    res = np.random.default_rng(0).random((6, 9, 15)).astype(np.float32)
+    L, sp = headless.stokes_to_bitmaps(res)
+    assert L.shape == (6, 9, 3) and len(sp) == 4 and np.array_equal(sp[2], res[:, :, 9:12])
+    out = str(tmp_path / "out")
+    headless.write_outputs(mi, out, L, sp, 4, 8e9)
+    names = sorted(os.listdir(out))
+    assert names == sorted(["params.json", "result.exr", "result.png"] + [f"result_s{i}.{e}" for i in range(4) for e in ("exr", "png")])
+    import json
+    pj = json.load(open(os.path.join(out, "params.json")))
+    assert pj == {"bitmap_size": {"width": 9, "height": 6}, "samples": 4, "time": "8.0 s", "time_per_sample": "2.0 s"}
+    np.testing.assert_array_equal(np.asarray(mi.Bitmap(os.path.join(out, "result_s1.exr")))[..., :3], sp[1])
+    with pytest.raises(RuntimeError, match="15. channels"):
+        headless.stokes_to_bitmaps(res[..., :4])
