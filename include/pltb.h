@@ -290,6 +290,22 @@ int pltb_synchronize(pltb_context *ctx);
 int pltb_host_alloc(uint64_t bytes, void **out);
 void pltb_host_free(void *ptr);
 
+/* Develop a raw film accumulator (width * height * channels floats, channels = 4: R G B W, or 16: + the 12 Stokes AOVs, as
+ * pltb_render writes it without PLTB_RENDER_DEVELOP) into width * height * (channels - 1) floats -- every channel but W divided
+ * by (W == 0 ? 1 : W), the arithmetic of pltb_render's PLTB_RENDER_DEVELOP step -- WITHOUT any device allocation.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  `accum` and `out` may each be host or device memory;
+ * `stream` is a cudaStream_t (NULL = the default stream) on the CURRENT device.  The staged input and the developed image live
+ * in a file-scope static __device__ array (csrc/pltb_noalloc.cu) that every GPU loading the library holds until exit, so
+ * width * height * channels must not exceed PLTB_NOALLOC_MAX_FLOATS (PLTB_ERR_NOMEM with a message otherwise; 4 Mi floats =
+ * 1024 x 1024 RGBW or 512 x 512 Stokes; 2 x 16 MiB of device memory).  All calls on a device share that array: calls that
+ * overlap on the GPU (different streams, or PLTB_DEVELOP_ASYNC calls still in flight) race.  Without PLTB_DEVELOP_ASYNC the
+ * stream is synchronised before returning; with it the caller synchronises before reading `out`. */
+#define PLTB_NOALLOC_MAX_FLOATS (4u << 20)
+enum { PLTB_DEVELOP_ASYNC = 1 };
+int pltb_film_develop_noalloc(const float *accum, uint32_t width, uint32_t height, uint32_t channels, uint32_t flags,
+                              float *out, void *stream);
+
 const char *pltb_last_error(void);
 int pltb_abi_version(void);
 

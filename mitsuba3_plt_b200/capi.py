@@ -108,7 +108,9 @@ class Stats(C.Structure):
 
 EXPORTS = ["pltb_nccl_unique_id", "pltb_context_create", "pltb_context_destroy", "pltb_scene_create", "pltb_scene_update_sensor",
            "pltb_scene_release", "pltb_render", "pltb_cancel", "pltb_film_device_ptr", "pltb_synchronize", "pltb_host_alloc", "pltb_host_free",
-           "pltb_last_error", "pltb_abi_version"]
+           "pltb_last_error", "pltb_abi_version", "pltb_film_develop_noalloc"]
+NOALLOC_MAX_FLOATS = 4 << 20   # PLTB_NOALLOC_MAX_FLOATS: the static device scratch of pltb_film_develop_noalloc
+DEVELOP_ASYNC = 1
 
 _lib = None
 
@@ -137,6 +139,7 @@ def lib():
         L.pltb_host_alloc.argtypes = [u64, C.POINTER(vp)]
         L.pltb_host_free.argtypes = [vp]
         L.pltb_host_free.restype = None
+        L.pltb_film_develop_noalloc.argtypes = [vp, u32, u32, u32, u32, vp, vp]
         L.pltb_last_error.restype = C.c_char_p
         L.pltb_abi_version.restype = C.c_int
         if L.pltb_abi_version() != PLTB_ABI_VERSION:

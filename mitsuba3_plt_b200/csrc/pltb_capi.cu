@@ -100,6 +100,10 @@ template <class T> static int upload(std::vector<void *> &allocs, const T *host,
     return 0;
 }
 
+namespace pltb {
+int set_last_error(int code, const char *msg) { return fail(code, msg); }   // for pltb_noalloc.cu
+}
+
 extern "C" {
 
 const char *pltb_last_error(void) { return g_err.c_str(); }

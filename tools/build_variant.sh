@@ -11,6 +11,7 @@ base="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=fal
 [ -z "$EXACT_RSQRT" ] && base="$base -DPLTB_FAST_RSQRT"
 nvcc $base "$@" -Xptxas -v -c -o $tmp/k.o $src/pltb_kernels.cu 2> $root/gpurun_out/ptxas_$sfx.log
 nvcc $base "$@" -c -o $tmp/c.o $src/pltb_capi.cu
-nvcc -shared -o $root/mitsuba3_plt_b200/libpltb200_$sfx.so $tmp/k.o $tmp/c.o -ldl 2>/dev/null
+nvcc $base "$@" -c -o $tmp/n.o $src/pltb_noalloc.cu
+nvcc -shared -o $root/mitsuba3_plt_b200/libpltb200_$sfx.so $tmp/k.o $tmp/c.o $tmp/n.o -ldl 2>/dev/null
 rm -rf $tmp
 echo built libpltb200_$sfx.so
