@@ -38,9 +38,15 @@ def frames_of_rank(frames, rank, world):
 
 
 def render_frames(scene, integrator, frames=240, spp=1, sensor_key=None, *, ctx=None, on_frame=None,
-                  move_vector=MOVE_VECTOR, max_rotation=MAX_ROTATION, indices=None):
+                  move_vector=MOVE_VECTOR, max_rotation=MAX_ROTATION, indices=None, inflight=1):
     """Render the frames of this rank (all of them on one GPU).  Returns {frame index: (H, W, 3) float32 image}; with
-    `on_frame(i, image)` given, images are handed over instead of being kept."""
+    `on_frame(i, image)` given, images are handed over instead of being kept.
+
+    `inflight` > 1 keeps that many frames in flight on the GPU: a 1-spp frame is a chain of ~35 dependent kernels, each bounded
+    below by the latency of one path's work, so a single frame leaves most SMs idle most of the time.  Every lane has its own
+    context (stream, wavefront state, film) and device copy of the scene and renders whole frames with the seeds and sensors
+    of the serial loop, so each frame's image is the one the serial loop produces; only the order in which `on_frame` is
+    called changes (calls are serialised, not ordered)."""
     from . import context, traverse
     ctx = ctx or context()
     params = traverse(scene)
@@ -48,8 +54,13 @@ def render_frames(scene, integrator, frames=240, spp=1, sensor_key=None, *, ctx=
     initial = params[key]
     out = {}
     W, H = scene.film_size()
+    todo = list(indices if indices is not None else frames_of_rank(frames, ctx.rank, ctx.world))
+    if inflight > 1 and len(todo) > 1:
+        _render_frames_inflight(scene, integrator, todo, frames, spp, params._index[key], initial, ctx, on_frame, out,
+                                move_vector, max_rotation, min(inflight, len(todo)))
+        return out
     staging = capi.PinnedArray((H, W, 3))   # page-locked frame buffer: the per-frame image download runs at PCIe speed
-    for i in (indices if indices is not None else frames_of_rank(frames, ctx.rank, ctx.world)):
+    for i in todo:
         params[key] = camera_to_world(initial, i, frames, move_vector, max_rotation)
         params.update()
         img = integrator.render(scene, spp=spp, seed=i, ctx=ctx, reduce=False, out=staging.array)
@@ -60,3 +71,44 @@ def render_frames(scene, integrator, frames=240, spp=1, sensor_key=None, *, ctx=
     params[key] = initial
     params.update()
     return out
+
+
+def _render_frames_inflight(scene, integrator, todo, frames, spp, sensor_index, initial, ctx, on_frame, out, move_vector,
+                            max_rotation, n_lanes):
+    import copy
+    import threading
+    from . import Context, Scene
+    W, H = scene.film_size()
+    lock, errors = threading.Lock(), []
+    lanes = scene.__dict__.setdefault("_anim_lanes", {})
+
+    def lane(k):
+        try:
+            slot = lanes.get((ctx.device, k))   # reused across calls: a context owns its wavefront state and film
+            if slot is None:
+                slot = lanes[(ctx.device, k)] = (Context(ctx.device), Scene(scene.flat, scene.tree))
+            lctx, lscene = slot
+            integ = copy.copy(integrator)
+            staging = capi.PinnedArray((H, W, 3))
+            dev = lscene.device(lctx)
+            for i in todo[k::n_lanes]:
+                m = camera_to_world(initial, i, frames, move_vector, max_rotation).matrix
+                m = np.ascontiguousarray(np.asarray(m, np.float64).reshape(16).astype(np.float32))
+                capi.check(capi.lib().pltb_scene_update_sensor(dev, sensor_index, capi.fptr(m)))
+                img = integ.render(lscene, spp=spp, seed=i, ctx=lctx, reduce=False, out=staging.array)
+                with lock:
+                    integrator._last_stats = integ._last_stats
+                    if on_frame is not None:
+                        on_frame(i, img)
+                    else:
+                        out[i] = img.copy()
+        except Exception as e:   # noqa: BLE001 -- re-raised on the calling thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=lane, args=(k,)) for k in range(n_lanes)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]

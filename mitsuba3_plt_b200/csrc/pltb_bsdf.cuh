@@ -397,11 +397,8 @@ PLTB_HD const pltb_bsdf *si_bsdf(const DeviceScene &sc, int32_t shape) {
 template <int Class> PLTB_HD uint32_t class_type(const pltb_bsdf *b) {
 #ifndef PLTB_CLASS_PER_TYPE
     if (Class == PLTB_BSDF_CONDUCTOR) {   // the shared class of the delta BSDFs (pltb_bvh.h: material_class)
-        const uint32_t t = b->type;
-#if defined(__CUDA_ARCH__)
-        if (t != PLTB_BSDF_CONDUCTOR && t != PLTB_BSDF_DIELECTRIC) __builtin_unreachable();
-#endif
-        return t;
+        // a two-valued expression rather than b->type itself: the switch statements of the *_inner functions then keep two cases
+        return b->type == PLTB_BSDF_DIELECTRIC ? (uint32_t) PLTB_BSDF_DIELECTRIC : (uint32_t) PLTB_BSDF_CONDUCTOR;
     }
 #endif
     if (Class >= 0) return (uint32_t) Class;

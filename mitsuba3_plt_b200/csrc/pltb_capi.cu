@@ -70,6 +70,7 @@ struct pltb_context {
     uint32_t st_class_mask = 0;   // classes whose queues are allocated
     std::vector<void *> st_allocs;
     unsigned long long *counters = nullptr;
+    unsigned long long *h_counters = nullptr;   // page-locked: read back on the render stream, before its one synchronisation
     float *dump_wl = nullptr, *dump_L = nullptr, *dump_stokes = nullptr; uint32_t *dump_rays = nullptr; uint64_t dump_cap = 0;
     uint32_t *n_shadow = nullptr; uint32_t n_shadow_cap = 0;   // per-sample shadow-ray counts (only for pltb_sample_dump.n_rays)
     int sm_count = 148;
@@ -131,6 +132,7 @@ int pltb_context_create(int device, int rank, int world, const void *nccl_unique
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev[0])); CU(cudaEventCreate(&c->ev[1]));
     CU(cudaMalloc(&c->counters, 8 * sizeof(unsigned long long)));
+    CU(cudaHostAlloc((void **) &c->h_counters, 8 * sizeof(unsigned long long), cudaHostAllocDefault));
     if (world > 1) {
         if (!nccl_unique_id) { delete c; return fail(PLTB_ERR_INVALID, "world > 1 needs an NCCL unique id"); }
         if (!load_nccl()) { delete c; return fail(PLTB_ERR_UNSUPPORTED, "NCCL is not loaded in this process"); }
@@ -153,7 +155,7 @@ void pltb_context_destroy(pltb_context *c) {
     cudaStreamSynchronize(c->stream);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     free_state(c);
-    cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
+    cudaFree(c->accum); cudaFree(c->rgb); cudaFree(c->counters); cudaFreeHost(c->h_counters); cudaFree(c->dump_wl); cudaFree(c->dump_L);
     cudaFree(c->dump_rays); cudaFree(c->n_shadow); cudaFree(c->dump_stokes);
     cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]);
     for (cudaEvent_t e : c->prof) cudaEventDestroy(e);
@@ -520,12 +522,12 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (!(film_out && root)) PROF();
     PROF();   // tail event 3: after the copies
     CU(cudaEventRecord(c->ev[1], s));
+    if (stats) CU(cudaMemcpyAsync(c->h_counters, c->counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
     if (stats) {
         memset(stats, 0, sizeof(*stats));
-        unsigned long long h[8];
-        CU(cudaMemcpy(h, c->counters, sizeof(h), cudaMemcpyDeviceToHost));
+        const unsigned long long *h = c->h_counters;
         stats->samples = total; stats->closest_rays = h[0]; stats->shadow_rays = h[1];
         stats->vertices = h[2]; stats->grating_vertices = h[3];
         stats->nee_other = h[4]; stats->nee_grating = h[5];

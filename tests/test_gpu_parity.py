@@ -175,6 +175,22 @@ def test_animation_frames(mi, oracle, integ):
     params.update()
     again = integ.render(sc, spp=8, seed=12)
     np.testing.assert_allclose(again, frames[12], rtol=1e-4, atol=1e-6)
+    params[key] = initial
+    params.update()
+    # several frames in flight (one context and device scene copy per lane): the same images as the serial loop, frame by frame
+    idx = list(range(0, 24, 2))
+    serial = animation.render_frames(sc, integ, frames=24, spp=8, indices=idx)
+    for lanes in (3, 5):
+        seen = []
+        flying = animation.render_frames(sc, integ, frames=24, spp=8, indices=idx, inflight=lanes)
+        assert sorted(flying) == idx
+        for i in idx:
+            np.testing.assert_allclose(flying[i], serial[i], rtol=1e-4, atol=1e-6)
+        animation.render_frames(sc, integ, frames=24, spp=8, indices=idx, inflight=lanes, on_frame=lambda i, img: seen.append((i, float(np.nansum(img)))))
+        assert sorted(i for i, _ in seen) == idx
+        for i, total in seen:
+            assert abs(total - float(np.nansum(serial[i]))) <= 1e-3 * abs(float(np.nansum(serial[i])))
+    assert np.array_equal(mi.traverse(sc)[key].matrix, initial.matrix)
 
 
 def test_accumulate_and_raw_film(mi, oracle, integ):

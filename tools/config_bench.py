@@ -80,6 +80,10 @@ for c5_id, c5_scene in (("C5", "gratingcap"), ("C5d", "disk")):
     t0 = time.perf_counter()
     animation.render_frames(sc, it, frames=240, spp=1, on_frame=lambda i, img: dev.append(it.last_stats["ms_total"]))
     wall = time.perf_counter() - t0
+    animation.render_frames(sc, it, frames=240, spp=1, indices=list(range(32)), inflight=4)
+    t0 = time.perf_counter()
+    animation.render_frames(sc, it, frames=240, spp=1, on_frame=lambda i, img: None, inflight=4)
+    wall4 = time.perf_counter() - t0   # four frames in flight (animation.render_frames(inflight=4)): same frames, same images
     t1 = time.perf_counter()
     for i in range(4):
         oracle_lib.render(sc.flat, 1, seed=i)
@@ -87,4 +91,5 @@ for c5_id, c5_scene in (("C5", "gratingcap"), ("C5d", "disk")):
     print(json.dumps({"config": c5_id, "workload": f"scenes/{c5_scene} 800x600, 1 spp per frame x 240 frames, camera path of "
                       "disk_animation.py", "frames_per_s": round(240 / wall, 1), "ms_per_frame_wall": round(1e3 * wall / 240, 3),
                       "ms_per_frame_device": round(float(np.mean(dev)), 3), "gpu_msamples_per_s": round(480000 * 240 / wall / 1e6, 2),
+                      "frames_per_s_inflight4": round(240 / wall4, 1), "ms_per_frame_wall_inflight4": round(1e3 * wall4 / 240, 3),
                       "cpu_oracle_ms_per_frame": round(cpu * 1e3, 2), "cpu_cores": os.cpu_count()}), flush=True)
