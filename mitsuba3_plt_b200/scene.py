@@ -302,12 +302,17 @@ class FlatScene:
                 return self.texture(q, "c", None, within_emitter=True)
             off = self._push_data(self.d65_table(scale))
             return self._add_tex(type=capi.TEX_D65, flags=0, offset=off, count=95, p=[0, 0, 0, 360.0, 830.0])
+        def numbers(v):   # "1, 2" / "1 2" strings as well as sequences (src/spectra/regular.cpp:38-47 tokenises on " ,")
+            return np.array([float(x) for x in v.replace(",", " ").split()] if isinstance(v, str) else v, dtype=np.float64)
         if t == "regular":
-            vals = np.asarray(p["values"], dtype=np.float64)
+            vals = numbers(p["values"])
             wl = np.linspace(float(p["wavelength_min"]), float(p["wavelength_max"]), len(vals))
             return self.spectrum_table(wl, vals)
         if t == "irregular":
-            return self.spectrum_table(p["wavelengths"], p["values"])
+            wl, vals = numbers(p["wavelengths"]), numbers(p["values"])
+            if len(wl) != len(vals):
+                raise RuntimeError("IrregularSpectrum: 'wavelengths' and 'values' parameters must have the same size!")
+            return self.spectrum_table(wl, vals)
         if t == "blackbody":
             return self._add_tex(type=capi.TEX_BLACKBODY,
                                  p=[float(p.get("temperature", 5000.0)), 0, 0,

@@ -2298,6 +2298,54 @@ void plt_oracle_envmap_probe(const pltb_scene_desc *d, const float *u, const flo
     out[3] = envmap_eval_spectrum(sc, em, uv, wl)[0];
     out[4] = dw.x; out[5] = dw.y; out[6] = dw.z;
 }
+/* ---- plugin-level probes for the reference's own plugin tests (tests/test_oracle_ref_tests.py) ---- */
+/* BSDF of shape `shape`: out = { eval[4], pdf, weight[4], sample: wo[3], pdf, weight[4], eta } (src/render/bsdf.cpp:22-97 entry points) */
+void plt_oracle_bsdf_probe(const pltb_scene_desc *d, int32_t shape, const float *wi, const float *uv, const float *wl4, const float *wo,
+                           const float *u5, float *out) {
+    Scene sc; prepare_scene(sc, d);
+    SI si; si.t = 1.f; si.shape = shape; si.wi = V3(wi[0], wi[1], wi[2]); si.uv = V2{ uv[0], uv[1] };
+    si.n = V3(0.f, 0.f, 1.f); si.sh.n = si.n; si.sh.s = V3(1.f, 0.f, 0.f); si.sh.t = V3(0.f, 1.f, 0.f);
+    for (int k = 0; k < 4; ++k) si.wavelengths[k] = wl4[k];
+    const V3 w(wo[0], wo[1], wo[2]);
+    const S4 e = wbsdf_eval(sc, si, w), wt = wbsdf_weight(sc, si, w);
+    for (int k = 0; k < 4; ++k) { out[k] = e[k]; out[5 + k] = wt[k]; }
+    out[4] = wbsdf_pdf(sc, si, w);
+    const SampleOut so = wbsdf_sample(sc, si, u5[0], V2{ u5[1], u5[2] }, V2{ u5[3], u5[4] });
+    out[9] = so.bs.wo.x; out[10] = so.bs.wo.y; out[11] = so.bs.wo.z; out[12] = so.bs.pdf;
+    for (int k = 0; k < 4; ++k) out[13 + k] = so.weight[k];
+    out[17] = so.bs.eta;
+}
+/* Emitter sampling from a reference point (Scene::sample_emitter_direction without the visibility test, area.cpp:116-208):
+ * out = { ds.d[3], ds.pdf, ds.dist, ds.p[3], ds.n[3], pdf_direction(ds), eval_direction[4], eval(wi = -d)[4], eval(wi = +d)[4] } */
+void plt_oracle_area_emitter_probe(const pltb_scene_desc *d, uint32_t emitter, const float *p, const float *u, const float *wl4, float *out) {
+    Scene sc; prepare_scene(sc, d);
+    const pltb_emitter &em = d->emitters[emitter];
+    const pltb_shape &sh = d->shapes[em.shape];
+    S4 wl; for (int k = 0; k < 4; ++k) wl[k] = wl4[k];
+    const V3 ref(p[0], p[1], p[2]);
+    DirectionSample ds = shape_sample_direction(sc, sh, ref, V2{ u[0], u[1] });
+    out[0] = ds.d.x; out[1] = ds.d.y; out[2] = ds.d.z; out[3] = ds.pdf; out[4] = ds.dist;
+    out[5] = ds.p.x; out[6] = ds.p.y; out[7] = ds.p.z; out[8] = ds.n.x; out[9] = ds.n.y; out[10] = ds.n.z;
+    out[11] = shape_pdf_direction(sh, ref, ds);
+    const S4 rad = emitter_radiance(sc, em, wl, ds.uv);
+    for (int k = 0; k < 4; ++k) {
+        out[12 + k] = dot(ds.d, ds.n) < 0.f ? rad[k] : 0.f;   /* AreaLight::eval_direction, area.cpp:198-208 */
+        out[16 + k] = rad[k];                                  /* AreaLight::eval with cos_theta(si.wi) > 0, area.cpp:83-91 */
+        out[20 + k] = 0.f;                                     /* ... and with si.wi pointing into the shape */
+    }
+}
+/* Sensor::sample_ray for film position `pos` in [0,1]^2: out = { o[3], d[3] } */
+void plt_oracle_sensor_ray(const pltb_scene_desc *d, uint32_t sensor, const float *pos, float *out) {
+    const Ray r = sensor_ray(d->sensors[sensor], V2{ pos[0], pos[1] });
+    out[0] = r.o.x; out[1] = r.o.y; out[2] = r.o.z; out[3] = r.d.x; out[4] = r.d.y; out[5] = r.d.z;
+}
+/* Texture::eval of spectrum / texture `id` */
+void plt_oracle_tex_probe(const pltb_scene_desc *d, int32_t id, const float *wl4, const float *uv, float *out) {
+    Scene sc; prepare_scene(sc, d);
+    S4 wl; for (int k = 0; k < 4; ++k) wl[k] = wl4[k];
+    const S4 v = tex_eval(sc, id, wl, V2{ uv[0], uv[1] });
+    for (int k = 0; k < 4; ++k) out[k] = v[k];
+}
 /* ---- polarized building blocks and further header-level functions (pinned on tests/golden/ref_kat_pol.json) ---- */
 static void m4_store(const M4 &m, float *out) { for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) for (int k = 0; k < 4; ++k) out[16 * i + 4 * j + k] = m.e[i][j][k]; }
 static M4 m4_load(const float *in) { M4 m; for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) for (int k = 0; k < 4; ++k) m.e[i][j][k] = in[16 * i + 4 * j + k]; return m; }
@@ -2345,6 +2393,12 @@ float plt_oracle_inv_coherence_det(float k, float diffusivity, float opl) { retu
 float plt_oracle_rfilter_eval(uint32_t type, float radius, float stddev, float x) {
     pltb_film f{}; f.rfilter = type; f.radius = radius; f.stddev = stddev;
     return rfilter_eval(f, x);
+}
+/* ImageBlock::put of one sample of weight 1 into a W x H single-channel block without border (imageblock.cpp:429-500) */
+void plt_oracle_splat(uint32_t type, float radius, float stddev, uint32_t W, uint32_t H, const float *pos, float *film) {
+    pltb_film f{}; f.rfilter = type; f.radius = radius; f.stddev = stddev;
+    const float one = 1.f;
+    splat(f, W, H, film, V2{ pos[0], pos[1] }, &one, 1);
 }
 float plt_oracle_hier2d_eval(const float *block, const float *pos) { return Hier2D(block).eval(V2{ pos[0], pos[1] }); }
 

@@ -37,8 +37,12 @@ def short(name):
     if not m:
         return name[:24]
     k, t = m.group(1), m.group(2)
-    if k == "k_shade": return "k_shade<grating>" if t.startswith("1") else "k_shade<other>"
-    if k == "k_nee_post": return "k_nee_post<grating>" if t.startswith("1") else "k_nee_post<other>"
+    # material class = BSDF plugin type (include/pltb.h): 5 = roughgrating; "--per-class" keeps one row per class
+    names = {"0": "null", "1": "diffuse", "2": "delta", "3": "dielectric", "4": "roughconductor", "5": "grating", "6": "principled"}
+    if k in ("k_shade", "k_nee_post", "k_shade_pol", "k_nee_post_pol"):
+        c = re.sub(r"\D", "", t or "")
+        if "--per-class" in sys.argv: return f"{k}<{names.get(c, c)}>"
+        return f"{k}<grating>" if c == "5" else f"{k}<other>"
     if k == "k_trace": return "k_trace<shadow>" if t.startswith("1") or t.startswith("true") else "k_trace"
     return k
 
