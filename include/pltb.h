@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define PLTB_ABI_VERSION 5
+#define PLTB_ABI_VERSION 6
 #define PLTB_MAX_DEPTH 16      /* upper bound on the `max_depth` plugin parameter (plt.py:37) */
 #define PLTB_MAX_LOBES 9       /* diffractionGratingsMaxLobes (include/mitsuba/plt/diffractiongrating.h:24) */
 
@@ -60,8 +60,14 @@ enum {
     PLTB_TEX_IRREGULAR = 4, /* src/spectra/irregular.cpp: wavelengths at data[offset..+count), values after them */
     PLTB_TEX_BITMAP = 5,    /* src/textures/bitmap.cpp, spectral mode: per-texel rgb2spec coefficients
                                data[offset + 3*(y*w+x) ..], bilinear, wrap mode `wrap`, uv transform to_uv */
-    PLTB_TEX_BLACKBODY = 6  /* src/spectra/blackbody.cpp: p[0] = temperature, range p[3],p[4] */
+    PLTB_TEX_BLACKBODY = 6, /* src/spectra/blackbody.cpp: p[0] = temperature, range p[3],p[4] */
+    PLTB_TEX_RGB = 7        /* RGB variants (PLTB_RENDER_RGB) only -- src/spectra/srgb.cpp:56-57 with Spectrum = Color3f: p[0..2] = the
+                               linear RGB value itself.  Scenes for the RGB variants hold UNIFORM, RGB and BITMAP | PLTB_TEXFLAG_RGB
+                               textures only: d65 / regular / irregular / blackbody spectra are converted to RGB at load time
+                               (src/spectra/d65.cpp:140-160, src/core/xml.cpp:1176-1260) */
 };
+enum { PLTB_TEXFLAG_D65_PRODUCT = 1,  /* PLTB_TEX_D65: multiply the table with srgb(p[0..2]) */
+       PLTB_TEXFLAG_RGB = 1 };         /* PLTB_TEX_BITMAP: texels are linear RGB triples, not rgb2spec coefficients (RGB variants) */
 enum { PLTB_WRAP_REPEAT = 0, PLTB_WRAP_MIRROR = 1, PLTB_WRAP_CLAMP = 2 };
 
 typedef struct pltb_texture {
@@ -136,7 +142,10 @@ typedef struct pltb_shape {
 /* Emitters (src/emitters/{area,directional,constant,envmap}.cpp).  CONSTANT and ENVMAP are environment emitters: rays that leave the scene see
  * it (SurfaceInteraction::emitter(scene) of an invalid interaction, include/mitsuba/render/interaction.h:343-346); at most one
  * environment emitter per scene (src/render/scene.cpp:60-67). */
-enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1, PLTB_EMITTER_CONSTANT = 2, PLTB_EMITTER_ENVMAP = 3 };
+enum { PLTB_EMITTER_AREA = 0, PLTB_EMITTER_DIRECTIONAL = 1, PLTB_EMITTER_CONSTANT = 2, PLTB_EMITTER_ENVMAP = 3,
+       PLTB_EMITTER_DIRECTIONALSPOT = 4 };   /* src/emitters/directionalspot.cpp (the fork's directional emitter with an angular spread):
+                                                to_world = emitter frame (+z = direction of propagation), env_pad[0] = sin(spread_angle),
+                                                radiance = irradiance, bsphere_* as directional */
 
 typedef struct pltb_emitter {
     uint32_t type;
@@ -151,7 +160,8 @@ typedef struct pltb_emitter {
     uint32_t env_warp;    /* offset in tex_data of the Hierarchical2D<Float, 0> block over luminance * sin(theta): words
                              [n_levels, res_x, res_y, 0, {offset, width} per level] (integers as bit patterns), then the levels
                              (include/mitsuba/core/distr_2d.h:344-470; level >= 1 in 2x2-patch order, Level::index :772-776) */
-    uint32_t env_data;    /* offset in tex_data of the (res_y, res_x, 4) array: rgb2spec coefficients + scale per texel */
+    uint32_t env_data;    /* offset in tex_data of the (res_y, res_x, 4) array: rgb2spec coefficients + scale per texel (RGB variants:
+                             linear r, g, b and an unused fourth float) */
     uint32_t env_res[2];  /* res_x = bitmap width + 1 (last column repeats the first), res_y = bitmap height */
     float env_scale;      /* `scale` plugin parameter */
     float env_pad[3];
@@ -199,8 +209,9 @@ typedef struct pltb_scene_desc {
     const pltb_sensor *sensors;  /* n_sensors >= 1; > 1 == `batch` sensor */
     pltb_film film;
     /* colour tables shared by the film conversion (include/mitsuba/core/spectrum.h:126-181) */
-    const float *cie_srgb;       /* 4 * 95 on [360, 830] nm, 5 nm step: linear Rec.709 matching functions R, G, B (film
-                                    conversion), then the CIE 1931 Y function (luminance() of the principled BSDF) */
+    const float *cie_srgb;       /* 6 * 95 on [360, 830] nm, 5 nm step: linear Rec.709 matching functions R, G, B (film
+                                    conversion), then the CIE 1931 Y function (luminance() of the principled BSDF), then X and Z
+                                    (cie1931_xyz of the roughgrating RGB fallback, roughgrating.cpp:751) */
 } pltb_scene_desc;
 
 /* ---- render call -------------------------------------------------------------------------------------------- */
@@ -214,8 +225,13 @@ enum {
     PLTB_RENDER_PROFILE = 32,     /* bracket every kernel with CUDA events and fill the per-kernel ms_* fields of pltb_stats */
     PLTB_RENDER_POLARIZED = 64,   /* the `*_spectral_polarized` variants: Spectrum = 4x4 Mueller matrix of 4 wavelengths
                                      (include/mitsuba/core/spectrum.h:60-95); the film still receives unpolarized_spectrum(L) */
-    PLTB_RENDER_STOKES = 128      /* with POLARIZED: the `stokes` wrapper integrator (src/integrators/stokes.cpp:88-138): 12 more film
+    PLTB_RENDER_STOKES = 128,     /* with POLARIZED: the `stokes` wrapper integrator (src/integrators/stokes.cpp:88-138): 12 more film
                                      channels S0.R S0.G S0.B ... S3.B after R G B W (raw film H*W*16, developed H*W*15) */
+    PLTB_RENDER_RGB = 256         /* the `*_rgb` / `*_rgb_polarized` variants: Spectrum = Color3f, no wavelength
+                                     sampling (common.py:297-299), film value = L * weight without the CIE integration (:386-391),
+                                     roughgrating takes its RGB fallback (roughgrating.cpp:499-506,716-839,1027-1031) at the path's
+                                     three `sampling_wavelengths` (plt.py:64-70), which become live draws.  The scene must have been
+                                     flattened for an RGB variant (see PLTB_TEX_RGB); combines with POLARIZED and STOKES */
 };
 #define PLTB_FILM_CHANNELS(flags) (((flags) & PLTB_RENDER_STOKES) ? 16 : 4)   /* raw accumulator channels per pixel */
 
@@ -234,7 +250,7 @@ typedef struct pltb_render_params {
 /* Per-sample dump for parity checks: one record per (pixel in window, s in the spp range),
  * ordered as pixel-major then sample index. */
 typedef struct pltb_sample_dump {
-    float *wavelengths;   /* 4 per sample, may be NULL */
+    float *wavelengths;   /* 4 per sample, may be NULL (PLTB_RENDER_RGB: the three sampling_wavelengths of the path, third one repeated) */
     float *radiance;      /* 4 per sample (PLTIntegrator.sample result, before the sensor weight), may be NULL */
     uint32_t *n_rays;     /* 2 per sample: closest-hit rays, shadow rays; may be NULL */
     uint64_t capacity;    /* number of samples the arrays can hold */

@@ -34,7 +34,7 @@ from .plt_types import (BounceData3f, Coherence3f, DiffractionGrating3f, Diffrac
 
 __all__ = ["set_variant", "variant", "load_file", "load_dict", "render", "traverse", "register_integrator",
            "PLTIntegrator", "Scene", "Properties", "ScalarTransform4f", "Transform4f", "Context", "context",
-           "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized", "StokesIntegrator"]
+           "init_distributed", "Bitmap", "util", "is_spectral", "is_polarized", "is_rgb", "StokesIntegrator"]
 
 ScalarTransform4f = Transform4f = Transform
 
@@ -50,20 +50,27 @@ scalar_rgb = scalar_spectral = _Namespace
 
 _SUPPORTED_VARIANTS = ("cuda_spectral", "cuda_ad_spectral", "llvm_spectral", "llvm_ad_spectral", "scalar_spectral",
                        "cuda_spectral_polarized", "cuda_ad_spectral_polarized", "llvm_spectral_polarized",
-                       "llvm_ad_spectral_polarized", "scalar_spectral_polarized")
+                       "llvm_ad_spectral_polarized", "scalar_spectral_polarized",
+                       "cuda_rgb", "cuda_ad_rgb", "llvm_rgb", "llvm_ad_rgb",
+                       "cuda_rgb_polarized", "cuda_ad_rgb_polarized", "llvm_rgb_polarized", "llvm_ad_rgb_polarized")
 _variant = "cuda_spectral"
-is_spectral, is_polarized = True, False
+is_spectral, is_polarized, is_rgb = True, False, False
 
 
 def set_variant(*names):
     """mi.set_variant: the 4-wavelength spectral variants, unpolarized and polarized (Spectrum = Mueller matrix; what
     scripts/rendering/main-headless.py:128-130 selects); every accepted name runs the same CUDA path, the `_polarized`
-    suffix switches the kernels to Mueller arithmetic (PLTB_RENDER_POLARIZED)."""
-    global _variant, is_polarized
+    suffix switches the kernels to Mueller arithmetic (PLTB_RENDER_POLARIZED); `_rgb` selects the RGB variants (PLTB_RENDER_RGB).
+    A Scene remembers the colour mode it was loaded under (as a Mitsuba scene does) and must be rendered in it."""
+    global _variant, is_polarized, is_spectral, is_rgb
     for n in names:
         if n in _SUPPORTED_VARIANTS:
             _variant = n
             is_polarized = n.endswith("_polarized")
+            # the `*_rgb` variants (the second mode of main-headless.py:131-133): Spectrum = Color3f, scenes are flattened with RGB
+            # textures and rendered with PLTB_RENDER_RGB (roughgrating's RGB fallback, roughgrating.cpp:716-839)
+            is_rgb = "_rgb" in n
+            is_spectral = not is_rgb
             return
     raise ImportError(f"Requested an unsupported variant {names!r}. The following variants are available: "
                       f"{', '.join(_SUPPORTED_VARIANTS)}.")
@@ -304,7 +311,10 @@ class PLTIntegrator:
         # wavefront limit of the reference (common.py:358-363); larger renders are split into sub-renders with
         # consecutive seeds whose raw accumulators are summed (SURVEY.md 8b "Seed/pass convention")
         n_sub, sub_spp = split_subrenders(W, H, spp)
-        mode = (capi.RENDER_POLARIZED if is_polarized else 0) | (capi.RENDER_STOKES if _stokes else 0)
+        if flat.rgb != is_rgb:
+            raise RuntimeError(f"render(): the scene was loaded for {'an RGB' if flat.rgb else 'a spectral'} variant but the active "
+                               f"variant is {_variant!r}; load it again after set_variant()")
+        mode = (capi.RENDER_POLARIZED if is_polarized else 0) | (capi.RENDER_STOKES if _stokes else 0) | (capi.RENDER_RGB if flat.rgb else 0)
         nch = capi.film_channels(mode)
         shape = (H, W, nch - 1 if develop else nch)
         if out is not None:
@@ -420,7 +430,7 @@ def load_file(path, **defaults):
     if not os.path.exists(path):
         raise RuntimeError(f'"{path}": file does not exist!')
     tree = load_file_tree(path, **{k: str(v) for k, v in defaults.items()})
-    return Scene(flatten(tree), tree)
+    return Scene(flatten(tree, rgb=is_rgb), tree)
 
 
 def load_dict(d):
@@ -429,7 +439,7 @@ def load_dict(d):
         raise RuntimeError("load_dict(): expected a dictionary with a 'type' entry")
     if d["type"] == "scene":
         tree = dict_to_tree(d)
-        return Scene(flatten(tree), tree)
+        return Scene(flatten(tree, rgb=is_rgb), tree)
     if d["type"] in _integrator_registry or d["type"] == "stokes":
         p = Properties(d["type"], **{k: v for k, v in d.items() if k != "type" and not isinstance(v, dict)})
         children = [load_dict(v) for v in d.values() if isinstance(v, dict)]

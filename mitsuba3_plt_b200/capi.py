@@ -13,11 +13,12 @@ LIB_PATH = os.path.join(_HERE, "libpltb200.so")
 if os.environ.get("PLTB200_LIB"):   # developer switch: an experimental build of the same library (tools/gpu.sh ab:<suffix>)
     LIB_PATH = os.path.abspath(os.environ["PLTB200_LIB"])
 
-PLTB_ABI_VERSION = 5
+PLTB_ABI_VERSION = 6
 PLTB_MAX_DEPTH = 16
 
 # enums (include/pltb.h)
-TEX_UNIFORM, TEX_SRGB, TEX_D65, TEX_REGULAR, TEX_IRREGULAR, TEX_BITMAP, TEX_BLACKBODY = range(7)
+TEX_UNIFORM, TEX_SRGB, TEX_D65, TEX_REGULAR, TEX_IRREGULAR, TEX_BITMAP, TEX_BLACKBODY, TEX_RGB = range(8)
+TEXFLAG_RGB = 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = range(3)
 BSDF_NULL, BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_DIELECTRIC, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHGRATING, BSDF_PRINCIPLED = range(7)
 PRINCIPLED_HAS = {"anisotropic": 1, "metallic": 2, "clearcoat": 4, "sheen": 8, "sheen_tint": 16, "flatness": 32, "spec_tint": 64}
@@ -25,11 +26,11 @@ BSDF_FLAG_TWOSIDED = 1
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 SHAPE_MESH, SHAPE_SPHERE, SHAPE_RECTANGLE = range(3)
 SHAPE_HAS_NORMALS, SHAPE_HAS_UV, SHAPE_FLIP_NORMALS = 1, 2, 4
-EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2, 3
+EMITTER_AREA, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP, EMITTER_DIRECTIONALSPOT = 0, 1, 2, 3, 4
 SENSOR_PERSPECTIVE, SENSOR_ORTHOGRAPHIC = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = range(3)
 RENDER_DEVELOP, RENDER_REDUCE, RENDER_DEVICE_OUT, RENDER_ACCUMULATE, RENDER_NO_SPLAT, RENDER_PROFILE = 1, 2, 4, 8, 16, 32
-RENDER_POLARIZED, RENDER_STOKES = 64, 128
+RENDER_POLARIZED, RENDER_STOKES, RENDER_RGB = 64, 128, 256
 
 
 def film_channels(flags):

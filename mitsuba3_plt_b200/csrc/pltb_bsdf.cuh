@@ -81,7 +81,8 @@ PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &
             float pdf; V3 m = distr.sample(wi, s2, pdf);
             o.pdf = pdf;
             V3 reflection_dir = reflect(wi, m);
-            float wavelength = wl.v[0];
+            // spectral: the hero wavelength; RGB variants: "Use sample 1 for random wavelength sample" (roughgrating.cpp:499-506)
+            float wavelength = sc.rgb ? s1 * (830.f - 150.0f - 360.f) + 360.f : wl.v[0];
             Frame nf = frame_from_normal(m);
             V3 wi_local = nf.to_local(wi);
             Grating g = make_grating(b, uv);
@@ -274,6 +275,64 @@ PLTB_HD S4 grating_lobe_sum(const DeviceScene &sc, const pltb_bsdf &b, const Gra
     return result;
 }
 
+// cie1931_xyz (include/mitsuba/core/spectrum.h:236-264) followed by xyz_to_srgb (:406-412; Matrix * vector = fmadd chain over the
+// columns); rows 4, 3, 5 of the scene's colour table are X, Y, Z
+PLTB_HD void wavelength_to_srgb(const float *cie, float wl, float rgb[3]) {
+    const float t = (wl - 360.f) * (94 / (830.f - 360.f));
+    const bool active = wl >= 360.f && wl <= 830.f;
+    uint32_t i0 = (uint32_t) fmaxf(t, 0.f);
+    if (i0 > 93u) i0 = 93u;
+    const float w1 = t - (float) i0, w0 = 1.f - w1;
+    const float *X = cie + 4 * 95, *Y = cie + 3 * 95, *Z = cie + 5 * 95;
+    const float x = active ? fmadd(w0, PLTB_LDG(X + i0), w1 * PLTB_LDG(X + i0 + 1)) : 0.f,
+                y = active ? fmadd(w0, PLTB_LDG(Y + i0), w1 * PLTB_LDG(Y + i0 + 1)) : 0.f,
+                z = active ? fmadd(w0, PLTB_LDG(Z + i0), w1 * PLTB_LDG(Z + i0 + 1)) : 0.f;
+    rgb[0] = fmadd(-0.498535f, z, fmadd(-1.537150f, y, 3.240479f * x));
+    rgb[1] = fmadd(0.041556f, z, fmadd(1.875991f, y, -0.969256f * x));
+    rgb[2] = fmadd(1.057311f, z, fmadd(-0.204043f, y, 0.055648f * x));
+}
+
+// The RGB fallback of RoughGrating::wbsdf_eval (roughgrating.cpp:716-790) before the Fresnel factor and specular_reflectance:
+// exhaustive search over the lobes at the path's three sampling wavelengths (wl lanes 0..2), each lobe coloured with
+// xyz_to_srgb(cie1931_xyz(wl)); every lobe carries the angular coherence factor.  A lobe outside its window adds exactly 0 (the
+// select discards its intensity; colour and coherence are finite), so its Bessel terms are not evaluated.
+PLTB_NI S4 grating_lobe_sum_rgb(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
+    const Grating g = make_grating(b, uv);
+    const V3 reflection_dir = reflect(wi);
+    const V2 si_ = g.sin_i(wi);
+    float result[3] = { 0.f, 0.f, 0.f };
+    const float a = 2 * sqrtf(b.f[1] * b.f[2]);
+    const int half = (int) g.lobes / 2;
+    const float angle_offset = fabsf(unit_angle(reflection_dir, wo));
+    float colour[3][3], coh[3];
+    for (int i = 0; i < 3; ++i) {
+        wavelength_to_srgb(sc.cie_srgb, wl.v[i], colour[i]);
+        const float k = kTwoPi / (wl.v[i] * 1e-3f);
+        const float s = k / (kTwoPi * (1.0f * 1e+3f));   // Coherence(m_coherence, 1.0).inv_coherence_det(k), plt.h:57-100
+        const float d00 = s * b.f[8], d01 = s * 0.f;
+        const float det = fmsub(d00, d00, d01 * d01);
+        const float inv_det = isnan_(det) ? 0.0f : det;
+        const float ac = expf(-0.5f * angle_offset * inv_det * angle_offset);
+        coh[i] = isnan_(ac) ? 0.0f : ac;
+    }
+    for (int lx = -half; lx < half + 1; lx++) {
+#pragma unroll 1
+        for (int ly = -half; ly < half + 1; ly++) {
+#pragma unroll 1
+            for (int i = 0; i < 3; i++) {
+                const float wl_um = wl.v[i] * 1e-3f;
+                bool lobe_active;
+                const V3 center_dir = g.diffract_s(si_, lx, ly, wl_um, lobe_active);
+                if (!(lobe_active && fabsf(unit_angle(center_dir, wo)) < a)) continue;
+                const float lobes_result = g.lobe_intensity(sc.bessel, lx, ly, wi, wl_um);
+                for (int c = 0; c < 3; ++c) result[c] += (lobes_result * colour[i][c]) * coh[i];
+            }
+        }
+    }
+    S4 r; r.v[0] = result[0]; r.v[1] = result[1]; r.v[2] = r.v[3] = result[2];
+    return r;
+}
+
 PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const GratingLoop &gl, V3 wi, V2 uv, const S4 &wl, V3 wo,
                           const GratingHits &h) {
     S4 result = grating_lobe_sum(sc, b, gl, wi, wo, h);
@@ -283,12 +342,22 @@ PLTB_HD S4 grating_finish(const DeviceScene &sc, const pltb_bsdf &b, const Grati
     return F * result;
 }
 
+PLTB_HD S4 grating_eval_rgb(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {   // roughgrating.cpp:716-839
+    S4 result = grating_lobe_sum_rgb(sc, b, wi, uv, wl, wo);
+    V3 H = normalize(wo + wi);
+    S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));
+    if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+    return F * result;
+}
 PLTB_HD S4 grating_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     GratingLoop gl; gl.init(b, wi, uv, wl, wo);
     GratingHits h; grating_scan(gl, wo, h);
     return grating_finish(sc, b, gl, wi, uv, wl, wo, h);
 }
 
+// Rgb: the RGB variants (DeviceScene::rgb) -- a template parameter because only roughgrating's evaluation differs, and the spectral
+// instantiations should not carry the fallback's registers (k_nee_post<grating> 96 -> 128 with a run-time branch)
+template <bool Rgb = false>
 PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
     switch (type) {
@@ -307,7 +376,7 @@ PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t t
             if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
             return D != 0.f ? F * result : s4(0.f);
         }
-        case PLTB_BSDF_ROUGHGRATING: return grating_eval(sc, b, wi, uv, wl, wo);
+        case PLTB_BSDF_ROUGHGRATING: return Rgb ? grating_eval_rgb(sc, b, wi, uv, wl, wo) : grating_eval(sc, b, wi, uv, wl, wo);
         default: return s4(0.f);
     }
 }
@@ -315,6 +384,7 @@ PLTB_HD S4 bsdf_eval_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t t
 // wbsdf_eval without its Fresnel factor (wi / wo already twosided-flipped): what the polarized variants scale a Mueller matrix
 // with -- the whole value for the depolarizing BSDFs (diffuse, principled), D G / (4 cos) [* specular_reflectance] for the rough
 // conductor (0 where the unpolarized eval is masked), the lobe sum [* specular_reflectance] for the grating
+template <bool Rgb = false>
 PLTB_HD S4 bsdf_eval_nofresnel(const DeviceScene &sc, const pltb_bsdf &b, uint32_t type, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     switch (type) {
         case PLTB_BSDF_DIFFUSE:
@@ -329,6 +399,11 @@ PLTB_HD S4 bsdf_eval_nofresnel(const DeviceScene &sc, const pltb_bsdf &b, uint32
             return D != 0.f ? result : s4(0.f);
         }
         case PLTB_BSDF_ROUGHGRATING: {
+            if (Rgb) {
+                S4 result = grating_lobe_sum_rgb(sc, b, wi, uv, wl, wo);
+                if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], wl, uv);
+                return result;
+            }
             GratingLoop gl; gl.init(b, wi, uv, wl, wo);
             GratingHits h; grating_scan(gl, wo, h);
             S4 result = grating_lobe_sum(sc, b, gl, wi, wo, h);
@@ -352,7 +427,7 @@ PLTB_HD float bsdf_pdf_inner(const DeviceScene &sc, const pltb_bsdf &b, uint32_t
             return distr.sample_visible ? distr.eval(m) * distr.smith_g1(wi, m) / (4.f * cos_theta_i)
                                         : distr.pdf(wi, m) / (4.f * dot(wo, m));
         }
-        case PLTB_BSDF_ROUGHGRATING: {  // roughgrating.cpp:1009-1034
+        case PLTB_BSDF_ROUGHGRATING: {  // roughgrating.cpp:1009-1034 (RGB variants: wl.v[0] is sd.sampling_wavelengths[0], :1027-1031)
             float k = kTwoPi / (wl.v[0] * 1e-3f);
             return expf(-sqr(wi.z * b.f[6] * k));
         }
@@ -421,11 +496,11 @@ PLTB_HD BSDFSampleOut wbsdf_sample(const DeviceScene &sc, const pltb_bsdf *b, V3
 PLTB_HD void twosided_flip(const pltb_bsdf *b, V3 &wi, V3 &wo) {
     if (b->flags & PLTB_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
 }
-template <int Class = -1>
+template <int Class = -1, bool Rgb = false>
 PLTB_HD S4 wbsdf_eval(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     if (!b) return s4(0.f);
     twosided_flip(b, wi, wo);
-    return bsdf_eval_inner(sc, *b, class_type<Class>(b), wi, uv, wl, wo);
+    return bsdf_eval_inner<Rgb>(sc, *b, class_type<Class>(b), wi, uv, wl, wo);
 }
 template <int Class = -1>
 PLTB_HD float wbsdf_pdf(const DeviceScene &sc, const pltb_bsdf *b, V3 wi, V2 uv, const S4 &wl, V3 wo) {

@@ -89,6 +89,7 @@ struct pltb_scene {
     pltb_sensor *d_sensors = nullptr;
     uint32_t film_w = 0, film_h = 0;
     uint32_t class_mask = 0;   // material classes (BSDF plugin types) present: bit c <=> some shape uses a BSDF of type c
+    bool has_rgb_tex = false, has_spectral_tex = false;   // texture kinds present: a scene is flattened for ONE colour mode
 };
 
 template <class T> static int upload(std::vector<void *> &allocs, const T *host, size_t n, const T **dev) {
@@ -175,9 +176,18 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     }
     for (uint32_t i = 0; i < d->n_faces * 3; ++i)
         if (d->faces[i] >= d->n_vertices) return fail(PLTB_ERR_INVALID, "face index out of range");
+    bool has_rgb_tex = false, has_spectral_tex = false;
+    for (uint32_t i = 0; i < d->n_textures; ++i) {
+        const pltb_texture &t = d->textures[i];
+        if (t.type > PLTB_TEX_RGB) return fail(PLTB_ERR_UNSUPPORTED, "unsupported texture type");
+        if (t.type == PLTB_TEX_RGB || (t.type == PLTB_TEX_BITMAP && (t.flags & PLTB_TEXFLAG_RGB))) has_rgb_tex = true;
+        else if (t.type != PLTB_TEX_UNIFORM) has_spectral_tex = true;
+    }
+    if (has_rgb_tex && has_spectral_tex)
+        return fail(PLTB_ERR_INVALID, "pltb_scene_create: RGB (PLTB_TEX_RGB / RGB bitmap) and spectral textures in one scene");
     for (uint32_t i = 0; i < d->n_emitters; ++i) {
         const pltb_emitter &e = d->emitters[i];
-        if (e.type > PLTB_EMITTER_ENVMAP) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
+        if (e.type > PLTB_EMITTER_DIRECTIONALSPOT) return fail(PLTB_ERR_UNSUPPORTED, "unsupported emitter type");
         if (e.type == PLTB_EMITTER_ENVMAP &&
             (e.env_res[0] < 3 || e.env_res[1] < 3 || (uint64_t) e.env_data + 4ull * e.env_res[0] * e.env_res[1] > d->n_tex_data ||
              e.env_warp >= d->n_tex_data))
@@ -194,6 +204,7 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     CU(cudaSetDevice(ctx->device));
     pltb_scene *s = new pltb_scene();
     s->ctx = ctx;
+    s->has_rgb_tex = has_rgb_tex; s->has_spectral_tex = has_spectral_tex;
     DeviceScene &ds = s->dev;
     int rc = 0;
     const float *nodes = nullptr, *tris = nullptr;
@@ -213,7 +224,7 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
     rc |= upload(s->allocs, d->emitters, d->n_emitters, &ds.emitters);
     rc |= upload(s->allocs, d->area_cdf, d->n_area_cdf, &ds.area_cdf);
     rc |= upload(s->allocs, d->sensors, d->n_sensors, &ds.sensors);
-    rc |= upload(s->allocs, d->cie_srgb, 4 * 95, &ds.cie_srgb);
+    rc |= upload(s->allocs, d->cie_srgb, 6 * 95, &ds.cie_srgb);
     if (rc) { pltb_scene_release(s); return PLTB_ERR_CUDA; }
     s->d_sensors = (pltb_sensor *) ds.sensors;
     s->sensors.assign(d->sensors, d->sensors + d->n_sensors);
@@ -351,6 +362,17 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     const bool polarized = (prm->flags & PLTB_RENDER_POLARIZED) != 0, stokes = polarized && (prm->flags & PLTB_RENDER_STOKES) != 0;
     if ((prm->flags & PLTB_RENDER_STOKES) && !polarized)
         return fail(PLTB_ERR_INVALID, "This integrator should only be used in polarized mode!");   // stokes.cpp:73-74
+    // colour mode: the scene copy passed to the kernels of this call carries it (DeviceScene::rgb)
+    const bool rgb = (prm->flags & PLTB_RENDER_RGB) != 0;
+    if (rgb && scene->has_spectral_tex)
+        return fail(PLTB_ERR_INVALID, "PLTB_RENDER_RGB: the scene holds spectral textures (it was flattened for a spectral variant)");
+    if (!rgb && scene->has_rgb_tex)
+        return fail(PLTB_ERR_INVALID, "the scene holds RGB textures (it was flattened for an RGB variant): render it with PLTB_RENDER_RGB");
+    if (rgb)
+        for (const pltb_sensor &sn : scene->sensors)
+            if (sn.srf >= 0) return fail(PLTB_ERR_INVALID, "PLTB_RENDER_RGB: sensor response functions need a spectral variant");
+    DeviceScene dev_scene = scene->dev;
+    dev_scene.rgb = rgb ? 1u : 0u;
     const int nch = PLTB_FILM_CHANNELS(stokes ? PLTB_RENDER_STOKES : 0);
     const uint64_t n_acc = (uint64_t) W * H * nch;
     if (c->accum_floats != n_acc) {
@@ -460,28 +482,28 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         if (profile) KHook::mark(-1, c);
         // sample phase as dense per-bounce wavefronts: raygen + trace(0), then shade(i) / trace(i + 1)
         nvtxRangePushA("pltb:sample_phase");
-        launch_raygen(scene->dev, st, pp, s);
+        launch_raygen(dev_scene, st, pp, s);
         // one k_shade / k_nee_post launch per material class the scene contains (roughgrating first: the longest kernel)
         const uint32_t cm = scene->class_mask;
         const int n_cls = __builtin_popcount(cm), has_grating = (cm >> PLTB_BSDF_ROUGHGRATING) & 1;
         for (uint32_t b = 0; b < prm->max_depth; ++b) {
             for (int cls = kClasses - 1; cls >= 0; --cls)
-                if (cm >> cls & 1u) launch_shade(scene->dev, st, b, cls, wf_grid, s);
+                if (cm >> cls & 1u) launch_shade(dev_scene, st, b, cls, wf_grid, s);
             launches += n_cls;
-            if (b + 1 < prm->max_depth) { launch_trace(scene->dev, st, b + 1, wf_grid, s); launches += 2; }
+            if (b + 1 < prm->max_depth) { launch_trace(dev_scene, st, b + 1, wf_grid, s); launches += 2; }
         }
         nvtxRangePop();
         PROF();
         nvtxRangePushA("pltb:solve_nee");
-        launch_nee_light(scene->dev, st, cm, nee_grid, s);
+        launch_nee_light(dev_scene, st, cm, nee_grid, s);
         for (int cls = kClasses - 1; cls >= 0; --cls)
-            if ((cm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(scene->dev, st, cls, nee_grid, s);
+            if ((cm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(dev_scene, st, cls, nee_grid, s);
         PROF();
-        if (has_grating) launch_nee_post(scene->dev, st, PLTB_BSDF_ROUGHGRATING, nee_grid, s);
+        if (has_grating) launch_nee_post(dev_scene, st, PLTB_BSDF_ROUGHGRATING, nee_grid, s);
         nvtxRangePop();
         PROF();
         NvtxRange film_range("pltb:gather_splat");
-        launch_splat(scene->dev, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
+        launch_splat(dev_scene, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
         launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized ? 1 : 0) + 1 + (do_splat ? 1 : 0);

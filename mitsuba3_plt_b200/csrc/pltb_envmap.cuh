@@ -92,6 +92,15 @@ PLTB_NI S4 envmap_eval_spectrum(const DeviceScene &sc, const pltb_emitter &em, V
     // texel records stay in global memory: srgb_model_eval reads its coefficients through the read-only path
     const float *v00 = sc.tex_data + em.env_data + 4 * (size_t) (py * rx + px), *v10 = v00 + 4, *v01 = v00 + 4 * (size_t) rx,
                 *v11 = v01 + 4;
+    if (sc.rgb) {   // envmap.cpp:569-579: texels are (r, g, b, unused); no whitepoint
+        S4 result;
+        for (int c = 0; c < 3; ++c) {
+            const float v0 = fmadd(w0x, PLTB_LDG(v00 + c), w1x * PLTB_LDG(v10 + c)), v1 = fmadd(w0x, PLTB_LDG(v01 + c), w1x * PLTB_LDG(v11 + c));
+            result.v[c] = fmadd(w0y, v0, w1y * v1) * em.env_scale;
+        }
+        result.v[3] = result.v[2];
+        return result;
+    }
     const float q00 = PLTB_LDG(v00 + 3), q10 = PLTB_LDG(v10 + 3), q01 = PLTB_LDG(v01 + 3), q11 = PLTB_LDG(v11 + 3);
     const S4 white = tex_eval(sc, em.radiance, wl, mk2(0.f, 0.f));
     const float f0 = fmadd(w0x, q00, w1x * q10), f1 = fmadd(w0x, q01, w1x * q11), f = fmadd(w0y, f0, w1y * f1);

@@ -240,14 +240,14 @@ struct GratingInsideBlock {
 };
 #endif
 
-template <int Class>
+template <int Class, bool Rgb>
 __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc,
                                                                       const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[cnt_nee(Class)];
     const uint32_t *queue = st.queue[Class];
     DevPush push;
 #ifndef PLTB_NEEPOST_DIRECT
-    if (Class == PLTB_BSDF_ROUGHGRATING) {
+    if (Class == PLTB_BSDF_ROUGHGRATING && !Rgb) {
         __shared__ ScanItem items[128];
         __shared__ uint32_t n_items;
         __shared__ uint8_t flag[128];
@@ -255,13 +255,13 @@ __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ Device
         for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
             const uint32_t e = base + threadIdx.x;
             const bool valid = e < n;
-            stage_nee_post<Class>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
+            stage_nee_post<Class, Rgb>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
         }
         return;
     }
 #endif
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post<Class>(sc, st, queue[e], true, push, GratingInsideDirect());
+        stage_nee_post<Class, Rgb>(sc, st, queue[e], true, push, GratingInsideDirect());
 }
 
 __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
@@ -445,12 +445,12 @@ __global__ void __launch_bounds__(128) k_shade_pol(const __grid_constant__ Devic
     flush_counters(cnt, st.counters);
 }
 
-template <int Class>
+template <int Class, bool Rgb>
 __global__ void __launch_bounds__(128) k_nee_post_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[cnt_nee(Class)];
     const uint32_t *queue = st.queue[Class];
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post_pol<Class>(sc, st, queue[e]);
+        stage_nee_post_pol<Class, Rgb>(sc, st, queue[e]);
 }
 
 // plt_solve_phase accumulation for the first column of L, then StokesIntegrator::sample's rotation to the sensor frame
@@ -501,6 +501,10 @@ __global__ void __launch_bounds__(256) k_splat_stokes(const __grid_constant__ De
     float values[16];
     splat_values(sc, comp[0], wl, f4_to_s4(st.sensor_w[local]), values);
     for (int i = 0; i < 4; ++i) {
+        if (sc.rgb) {   // rgb = spec.entry(i, 0) (stokes.cpp:114-115)
+            for (int c = 0; c < 3; ++c) values[4 + 3 * i + c] = comp[i].v[c];
+            continue;
+        }
         S4 v;
         for (int k = 0; k < 4; ++k) { const float pdf = pdf_rgb_spectrum(wl.v[k]); v.v[k] = comp[i].v[k] * (pdf != 0.f ? rcp(pdf) : 0.f); }
         spectrum_to_srgb(sc.cie_srgb, v, wl, values + 4 + 3 * i);
@@ -556,8 +560,13 @@ template <int C> struct LaunchShade {
 };
 template <int C> struct LaunchNeePost {
     static void run(const DeviceScene &sc, const PassState &st, int grid, cudaStream_t s) {
-        if (st.pv_w) k_nee_post_pol<C><<<grid, 128, 0, s>>>(sc, st);        // polarized: grating scan and evaluation in one kernel
-        else k_nee_post<C><<<grid, 128, 0, s>>>(sc, st);
+        // the RGB variants differ in roughgrating's evaluation only (its RGB fallback): one more instantiation of that class
+        constexpr bool kGrating = C == PLTB_BSDF_ROUGHGRATING;
+        if (kGrating && sc.rgb) {
+            if (st.pv_w) k_nee_post_pol<C, kGrating><<<grid, 128, 0, s>>>(sc, st);
+            else k_nee_post<C, kGrating><<<grid, 128, 0, s>>>(sc, st);
+        } else if (st.pv_w) k_nee_post_pol<C, false><<<grid, 128, 0, s>>>(sc, st);   // polarized: grating scan and evaluation in one kernel
+        else k_nee_post<C, false><<<grid, 128, 0, s>>>(sc, st);
     }
 };
 void launch_shade(const DeviceScene &sc, const PassState &st, uint32_t bounce, int cls, int grid, cudaStream_t s) {
@@ -573,7 +582,7 @@ void launch_nee_light(const DeviceScene &sc, const PassState &st, uint32_t class
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
     dispatch_class<LaunchNeePost>(cls, sc, st, grid, s);
     PLTB_AFTER(cls == PLTB_BSDF_ROUGHGRATING ? PLTB_K_NEE_POST_GRATING : PLTB_K_NEE_POST_OTHER);
-    if (cls == PLTB_BSDF_ROUGHGRATING && !st.pv_w) { k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL); }
+    if (cls == PLTB_BSDF_ROUGHGRATING && !st.pv_w && !sc.rgb) { k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL); }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s) {

@@ -28,6 +28,7 @@ PLTB_HD bool mac_mic_compatibility(V3 m, V3 wi, V3 wo, float cos_theta_i, bool r
 }
 // mitsuba::luminance(value, wavelengths), spectral mode: mean(cie1931_y(wl) * value) (spectrum.h:272-295, 414-429)
 PLTB_HD float spectral_luminance(const DeviceScene &sc, const S4 &value, const S4 &wl) {
+    if (sc.rgb) return value.v[0] * 0.212671f + value.v[1] * 0.715160f + value.v[2] * 0.072169f;   // luminance(Color3f), spectrum.h:431-434
     const float *y = sc.cie_srgb + 3 * 95;
     float acc[4];
     for (int i = 0; i < 4; ++i) {

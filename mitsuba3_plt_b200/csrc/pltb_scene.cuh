@@ -37,6 +37,9 @@ struct DeviceScene {
     uint32_t n_faces, n_shapes, n_emitters, n_sensors;
     float emitter_pmf;
     int32_t env;   // index of the environment emitter (Scene::environment(), src/render/scene.cpp:60-67), -1 if none
+    uint32_t rgb;  // PLTB_RENDER_RGB (set per render call): Spectrum = Color3f in lanes 0..2 of S4, lane 3 repeats lane 2 (so per-lane
+                   // arithmetic and max() are those of a 3-vector); the per-sample wavelength slot then holds the path's
+                   // `sampling_wavelengths` (plt.py:64-70,158), which only roughgrating's RGB fallback reads
     BesselTables bessel;
 };
 
@@ -248,6 +251,7 @@ PLTB_NI S4 tex_eval(const DeviceScene &sc, int32_t id, const S4 &wl, V2 uv) {
     S4 r = s4(0.f);
     switch (t.type) {
         case PLTB_TEX_UNIFORM: return s4(t.p[0]);
+        case PLTB_TEX_RGB: r.v[0] = t.p[0]; r.v[1] = t.p[1]; r.v[2] = r.v[3] = t.p[2]; return r;   // srgb.cpp:56-57 in an RGB variant
         case PLTB_TEX_SRGB:
             for (int i = 0; i < 4; ++i) r.v[i] = srgb_model_eval(t.p, wl.v[i]);
             return r;
@@ -277,6 +281,16 @@ PLTB_NI S4 tex_eval(const DeviceScene &sc, int32_t id, const S4 &wl, V2 uv) {
             const float *v00 = data + 3 * ((size_t) y0 * t.width + x0), *v10 = data + 3 * ((size_t) y0 * t.width + x1),
                         *v01 = data + 3 * ((size_t) y1 * t.width + x0), *v11 = data + 3 * ((size_t) y1 * t.width + x1);
             float w1x = pu - (float) iu, w0x = 1.f - w1x, w1y = pv - (float) iv, w0y = 1.f - w1y;
+            if (t.flags & PLTB_TEXFLAG_RGB) {   // RGB variants: linear RGB texels, dr::Texture::eval (drjit/texture.h:386-419)
+                for (int c = 0; c < 3; ++c) {
+                    float acc = fmadd(PLTB_LDG(v00 + c), w0x * w0y, 0.f);
+                    acc = fmadd(PLTB_LDG(v10 + c), w1x * w0y, acc);
+                    acc = fmadd(PLTB_LDG(v01 + c), w0x * w1y, acc);
+                    r.v[c] = fmadd(PLTB_LDG(v11 + c), w1x * w1y, acc);
+                }
+                r.v[3] = r.v[2];
+                return r;
+            }
             for (int i = 0; i < 4; ++i) {
                 float c00 = srgb_model_eval(v00, wl.v[i]), c10 = srgb_model_eval(v10, wl.v[i]),
                       c01 = srgb_model_eval(v01, wl.v[i]), c11 = srgb_model_eval(v11, wl.v[i]);

@@ -103,21 +103,27 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
     PCG32 rng; rng.seed(v0, v1);
     float jx = rng.next_float32(), jy = rng.next_float32();
     V2 pos_f = mk2((float) x + jx, (float) y + jy);
-    float wav_sample = rng.next_float32();
+    const float wav_sample = sc.rgb ? 0.f : rng.next_float32();   // only drawn in spectral variants (common.py:297-299)
     const uint32_t fw = sc.film.width;
     uint32_t sidx = x / fw;   // BatchSensor: film split in x (src/sensors/batch.cpp:131-190)
     const pltb_sensor &sn = sc.sensors[sidx];
     V2 pos_adj = mk2((pos_f.x - (float) (sidx * fw)) * rcp((float) fw), pos_f.y * rcp((float) pp.film_h));
-    S4 wl, wgt;
-    sample_wavelengths(sc, sn, wav_sample, wl, wgt);
+    S4 wl = s4(0.f), wgt = s4(1.f);   // RGB variants: no wavelengths, ray weight 1 (sensor.cpp:113-127)
+    if (!sc.rgb) sample_wavelengths(sc, sn, wav_sample, wl, wgt);
     Ray ray = sensor_ray(sn, pos_adj);
-    st.wl[local] = s4_to_f4(wl);
+    if (!sc.rgb) st.wl[local] = s4_to_f4(wl);
     st.sensor_w[local] = s4_to_f4(wgt);
     float2 fp; fp.x = pos_f.x; fp.y = pos_f.y;
     st.film_pos[local] = fp;
     if (st.n_shadow) st.n_shadow[local] = 0;
     if (st.stokes_theta) st.stokes_theta[local] = stokes_rotation_angle(sc.sensors[0], ray.d, sc.n_sensors > 1);
-    for (int k = 0; k < 4; ++k) (void) rng.next_float32();   // dead sampling_wavelengths draws (N1, plt.py:65-70)
+    // sampling_wavelengths (plt.py:64-70): four draws times scale_wl = 680; dead in spectral variants (N1), in RGB variants the
+    // first three are what roughgrating's RGB fallback evaluates (kept in the wavelength slot, third one repeated)
+    {
+        float u[4];
+        for (int k = 0; k < 4; ++k) u[k] = rng.next_float32();
+        if (sc.rgb) st.wl[local] = mkf4(u[0] * 680.f, u[1] * 680.f, u[2] * 680.f, u[2] * 680.f);
+    }
     st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
     st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
     Hit h = bvh_intersect<false>(sc, ray);
@@ -265,6 +271,14 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
         envmap_sample_direction(sc, em, p, sample, dw, ds.dist, ds.uv, ds.pdf);
         ds.p = p + dw * ds.dist;
         ds.n = -dw; ds.delta = false; ds.d = dw;
+    } else if (em.type == PLTB_EMITTER_DIRECTIONALSPOT) {   // DirectionalSpreadEmitter::sample_direction (directionalspot.cpp:161-192)
+        const float rr = sqrtf(sample.y), ang = kTwoPi * sample.x;   // warp::square_to_uniform_disk (warp.h:25-30) * sin(spread)
+        const float sn = sinf(ang), cs = cosf(ang);
+        const V3 dd = xf_vector(em.to_world, normalize(mk3((cs * rr) * em.env_pad[0], (sn * rr) * em.env_pad[0], 1.f)));
+        const V3 c = mk3(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+        const float dist = 2.f * fmaxf(em.bsphere_radius, norm(p - c));
+        ds.p = p - dd * dist;
+        ds.n = dd; ds.uv = mk2(0.f, 0.f); ds.pdf = 1.f; ds.delta = true; ds.d = -dd; ds.dist = dist;
     } else {   // DirectionalEmitter::sample_direction (src/emitters/directional.cpp:149-176)
         V3 dirn = mk3(em.direction[0], em.direction[1], em.direction[2]);
         ds.d = -dirn;
@@ -311,7 +325,7 @@ struct GratingInsideDirect {
 
 // `valid` is false for the tail threads of a block-uniform loop (k_nee_post<roughgrating>): they load nothing and only take part in
 // the barriers a block-level `inside_fn` may contain, which is why that call sits at one program point that every thread reaches.
-template <int Class, class Push, class Inside>
+template <int Class, bool Rgb, class Push, class Inside>
 PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
@@ -339,7 +353,7 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         b = si_bsdf(sc, si.shape);
         a = f4_to_s4(st.v_alpha[r]);
     }
-    if (Class == PLTB_BSDF_ROUGHGRATING) {
+    if (Class == PLTB_BSDF_ROUGHGRATING && !Rgb) {
         // RoughGrating::wbsdf_eval is only non-zero inside the few-degree windows around the diffraction lobes: 9 % of the NEE
         // directions on cbox-grating, 6 % once unlit samples are excluded.  For well-formed inputs (finite, unit wi / wo,
         // finite throughput: then every factor of the product is finite) an unlit sample or one outside every window
@@ -351,6 +365,8 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
                            em_weight.v[0] + em_weight.v[1] + em_weight.v[2] + em_weight.v[3];
         const bool sane = finite_(fsum) && wi_f.z != 0.f && fabsf(sqnorm(wi_f) - 1.f) < 1e-3f && fabsf(sqnorm(wo_f) - 1.f) < 1e-3f;
         const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
+        // (RGB variants, Rgb = true: the fallback's lobe search differs -- other wavelengths, a coherence factor on every lobe --
+        // and takes the generic path below)
         const bool inside = inside_fn(valid && sane && lit, b, wi_f, wo_f, si.uv, wl);
         if (!valid) return;
         if (sane) {
@@ -364,7 +380,7 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         }
     }
     if (!valid) return;
-    S4 bsdf_val = wbsdf_eval<Class>(sc, b, si.wi, si.uv, wl, wo);
+    S4 bsdf_val = wbsdf_eval<Class, Rgb>(sc, b, si.wi, si.uv, wl, wo);
     float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
     st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
@@ -397,7 +413,8 @@ PLTB_HD S4 splat_gather(const PassState &st, uint32_t local, uint32_t n) {
 PLTB_HD S4 splat_gather(const PassState &st, uint32_t local) { return splat_gather(st, local, st.n_vertices[local]); }
 // _splat_to_block (common.py:370-397): sensor weight, spectrum -> sRGB, channels [R, G, B, W = 1]
 PLTB_HD void splat_values(const DeviceScene &sc, const S4 &L, const S4 &wl, const S4 &sensor_w, float values[4]) {
-    spectrum_to_srgb(sc.cie_srgb, L * sensor_w, wl, values);
+    if (sc.rgb) { const S4 v = L * sensor_w; values[0] = v.v[0]; values[1] = v.v[1]; values[2] = v.v[2]; }   // rgb = value (common.py:386-391)
+    else spectrum_to_srgb(sc.cie_srgb, L * sensor_w, wl, values);
     values[3] = 1.f;
 }
 PLTB_HD void splat_values(const DeviceScene &sc, const PassState &st, uint32_t local, const S4 &L, float values[4]) {

@@ -173,8 +173,8 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 
 // solve_replay_NEE's BSDF half in a polarized variant.  em_weight is depolarizer(e), so ((e mis) * B) has only row 0,
 // (e mis) B(0, j), and its product with alpha contributes only to L(0, 0): sum_j X(0, j) alpha(j, 0) in fmadd order.
-template <int Class>
-PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint32_t entry) {
+template <int Class, bool Rgb>
+PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint32_t entry) {   // Rgb: see bsdf_eval_inner
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
     const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
@@ -196,7 +196,7 @@ PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint
     const pltb_bsdf *b = si_bsdf(sc, si.shape);
     V3 wi_f = si.wi, wo_f = wo;
     if (b) twosided_flip(b, wi_f, wo_f);
-    const S4 value = b ? bsdf_eval_nofresnel(sc, *b, class_type<Class>(b), wi_f, si.uv, wl, wo_f) : s4(0.f);
+    const S4 value = b ? bsdf_eval_nofresnel<Rgb>(sc, *b, class_type<Class>(b), wi_f, si.uv, wl, wo_f) : s4(0.f);
     const float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     const float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
     PolEval pe;

@@ -74,9 +74,12 @@ def main(argv=None):
     if a.plot:
         raise SystemExit("--plot opens matplotlib windows: unavailable on this (headless) backend")
     import mitsuba3_plt_b200 as mi
-    if not a.spectral:
-        raise SystemExit("the RGB variants are not on the B200 hot path (SURVEY.md 8f f2): pass --spectral")
-    mi.set_variant("cuda_ad_spectral_polarized")
+    if a.spectral:   # main-headless.py:128-133
+        print("Loading spectral variant...")
+        mi.set_variant("cuda_ad_spectral_polarized")
+    else:
+        print("Loading RGB variant...")
+        mi.set_variant("cuda_ad_rgb_polarized")
     overrides = {k: float(v) for k, v in (o.split("=") for o in a.override)}
     print("Loading scene...")
     start = time.perf_counter_ns()

@@ -191,7 +191,10 @@ def _cube_mesh():
 class FlatScene:
     """Owns the numpy buffers behind a `pltb_scene_desc` (keeps them alive) plus the traversable parameters."""
 
-    def __init__(self):
+    def __init__(self, rgb=False):
+        # rgb: flatten for the `*_rgb` variants (Spectrum = Color3f): every spectrum / texture becomes an RGB value
+        # (PLTB_TEX_RGB, PLTB_TEX_UNIFORM or an RGB bitmap), as the plugins do under is_rgb_v<Spectrum>
+        self.rgb = bool(rgb)
         self.textures, self.tex_data = [], []
         self.bsdfs, self.shapes, self.emitters, self.sensors = [], [], [], []
         self.positions, self.normals, self.texcoords, self.faces, self.face_shape = [], [], [], [], []
@@ -242,6 +245,8 @@ class FlatScene:
             v = float(default)
         if isinstance(v, (int, float)) and not isinstance(v, bool):
             return self._add_tex(type=capi.TEX_UNIFORM, p=[float(v)], mean=float(v))
+        if self.rgb:
+            return self._texture_rgb(v, name, within_emitter)
         if isinstance(v, Color):
             rgb = np.array(v, dtype=F32)
             if within_emitter:  # src/spectra/d65.cpp:74-112
@@ -271,6 +276,35 @@ class FlatScene:
             return self.texture_plugin(v, within_emitter)
         raise RuntimeError(f'property "{name}": unsupported value {v!r}')
 
+    # ---- RGB variants (is_rgb_v<Spectrum>) ---------------------------------------------------------------------------
+    def _rgb_tex(self, rgb):
+        rgb = np.asarray(rgb, dtype=F32)
+        lum = float(F32(rgb[0]) * F32(0.212671) + F32(rgb[1]) * F32(0.715160) + F32(rgb[2]) * F32(0.072169))
+        return self._add_tex(type=capi.TEX_RGB, p=[float(rgb[0]), float(rgb[1]), float(rgb[2])], mean=lum)
+
+    def _texture_rgb(self, v, name, within_emitter):
+        """The rgb / spectrum -> plugin rules of xml.cpp:1146-1260 and the plugin constructors in an RGB variant."""
+        unbounded = name in ("eta", "k", "int_ior", "ext_ior")
+        if isinstance(v, Color):
+            # within an emitter: d65 with `color`, which expands to srgb(color * scale, unbounded) (d65.cpp:100-156); else srgb
+            rgb = np.array(v, dtype=F32)
+            if not within_emitter and not unbounded and (np.any(rgb < 0) or np.any(rgb > 1)):
+                raise RuntimeError(f"Invalid RGB reflectance value {list(rgb)}, must be in the range [0, 1]!")
+            return self._rgb_tex(rgb)
+        if isinstance(v, SpectrumValue):
+            if v.const is not None:
+                if within_emitter and not unbounded:   # xml.cpp:1176-1188: const * xyz_to_srgb(Color3f(1))
+                    white = spectra.xyz_to_srgb(np.ones(3, dtype=F32))
+                    return self._rgb_tex((F32(v.const) * white).astype(F32))
+                return self._add_tex(type=capi.TEX_UNIFORM, p=[v.const], mean=v.const)
+            vals = np.asarray(v.values, dtype=F32) * F32(spectra.MI_CIE_Y_NORMALIZATION)   # xml.cpp:1200-1204
+            rgb = spectra.spectrum_list_to_srgb(np.asarray(v.wavelengths, dtype=F32), vals,
+                                                bounded=not (within_emitter or unbounded), d65=not (within_emitter and not unbounded))
+            return self._rgb_tex(rgb)
+        if isinstance(v, Properties):
+            return self.texture_plugin(v, within_emitter)
+        raise RuntimeError(f'property "{name}": unsupported value {v!r}')
+
     def spectrum_table(self, wl, vals):
         """regular / irregular spectrum (xml.cpp:1192-1232); the CDF used by sample_spectrum is appended."""
         wl = np.asarray(wl, dtype=np.float64); vals = np.asarray(vals, dtype=np.float64)
@@ -293,6 +327,20 @@ class FlatScene:
         if t == "uniform":
             v = float(p.get("value", 1.0))
             return self._add_tex(type=capi.TEX_UNIFORM, p=[v], mean=v)
+        if self.rgb:
+            if t == "srgb":   # srgb.cpp:52-57
+                rgb = np.array(p["color"], dtype=F32)
+                if (np.any(rgb < 0) or np.any(rgb > 1)) and not p.get("unbounded", False):
+                    raise RuntimeError(f"Invalid RGB reflectance value {list(rgb)}, must be in the range [0, 1]!")
+                return self._rgb_tex(rgb)
+            if t == "d65":    # expands to srgb(color * scale, unbounded) or uniform(scale) (d65.cpp:140-160)
+                scale = F32(p.get("scale", 1.0))
+                if "color" in p:
+                    return self._rgb_tex((np.array(p["color"], dtype=F32) * scale).astype(F32))
+                return self._add_tex(type=capi.TEX_UNIFORM, p=[float(scale)], mean=float(scale))
+            if t == "bitmap":
+                return self.bitmap(p)
+            raise RuntimeError(f'Plugin "{t}": spectral textures are not available in the RGB variants (use <rgb> / <spectrum value=...>)')
         if t == "srgb":
             return self.texture(Properties("", color=Color(p["color"])), "color", None)
         if t == "d65":
@@ -334,7 +382,10 @@ class FlatScene:
         a = np.asarray(im.convert("RGB"), dtype=F32) / F32(255)
         if not raw:
             a = spectra.srgb_to_linear(a)
-        coeff = spectra.srgb_model_fetch(a)
+        if self.rgb:   # RGB variants: the texels stay linear RGB (bitmap.cpp:230-250), mean = mean luminance
+            coeff = np.ascontiguousarray(a, dtype=F32)
+        else:
+            coeff = spectra.srgb_model_fetch(a)
         h, w = coeff.shape[:2]
         wrap = {"repeat": capi.WRAP_REPEAT, "mirror": capi.WRAP_MIRROR, "clamp": capi.WRAP_CLAMP}[p.get("wrap_mode", "repeat")]
         if p.get("filter_type", "bilinear") != "bilinear":
@@ -344,16 +395,20 @@ class FlatScene:
             m = np.asarray(p["to_uv"], dtype=np.float64)
             to_uv = m if m.shape == (3, 3) else np.array([[m[0, 0], m[0, 1], m[0, 3]], [m[1, 0], m[1, 1], m[1, 3]], [0, 0, 1]])
         off = self._push_data(coeff)
-        mean = float(spectra.srgb_model_mean(coeff.reshape(-1, 3)).mean())
-        return self._add_tex(type=capi.TEX_BITMAP, offset=off, count=w * h * 3, width=w, height=h, wrap=wrap,
-                             to_uv=to_uv, mean=mean)
+        if self.rgb:
+            c = coeff.reshape(-1, 3)
+            mean = float((c[:, 0] * F32(0.212671) + c[:, 1] * F32(0.715160) + c[:, 2] * F32(0.072169)).mean())
+        else:
+            mean = float(spectra.srgb_model_mean(coeff.reshape(-1, 3)).mean())
+        return self._add_tex(type=capi.TEX_BITMAP, flags=capi.TEXFLAG_RGB if self.rgb else 0, offset=off, count=w * h * 3,
+                             width=w, height=h, wrap=wrap, to_uv=to_uv, mean=mean)
 
     def eval_1(self, tex_id):
         """Texture::eval_1 for spatially uniform parameters (roughness, grating parameters)."""
         t = self.textures[tex_id]
         if t.type == capi.TEX_UNIFORM:
             return float(t.p[0])
-        if t.type == capi.TEX_SRGB:
+        if t.type in (capi.TEX_SRGB, capi.TEX_RGB):
             return float(t.mean)
         raise RuntimeError("spatially varying scalar BSDF parameters are not supported on the plt path")
 
@@ -607,16 +662,31 @@ class FlatScene:
             return
         if t == "envmap":
             return self.envmap(p)
-        if t != "directional":
+        if t not in ("directional", "directionalspot"):
             raise RuntimeError(f'Plugin "{t}" not found (emitter outside the plt hot path)')
         e = capi.Emitter()
         e.type, e.shape = capi.EMITTER_DIRECTIONAL, -1
+        tw = np.asarray(getattr(p.get("to_world"), "matrix", p.get("to_world", np.eye(4))), dtype=np.float64).reshape(4, 4)
         if "direction" in p:  # src/emitters/directional.cpp:64-78
+            if "to_world" in p:
+                raise RuntimeError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!'")
             d = np.asarray(p["direction"], dtype=np.float64)
+            if t == "directionalspot":   # look_at(0, direction, up) with up from coordinate_system(direction) (directionalspot.cpp:70-79)
+                from .xmlscene import look_at
+                dn = d / np.linalg.norm(d)
+                sgn = 1.0 if dn[2] >= 0 else -1.0
+                a = -1.0 / (sgn + dn[2]); b = dn[0] * dn[1] * a
+                up = np.array([1.0 + sgn * dn[0] * dn[0] * a, sgn * b, -sgn * dn[0]])
+                tw = look_at(np.zeros(3), dn, up)
         else:
-            d = np.asarray(p.get("to_world", np.eye(4)), dtype=np.float64)[:3, :3] @ np.array([0, 0, 1.0])
+            d = tw[:3, :3] @ np.array([0, 0, 1.0])
         d = d / np.linalg.norm(d)
         e.direction[:] = list(d.astype(F32))
+        if t == "directionalspot":   # src/emitters/directionalspot.cpp:60-100: direction sampled in a cone of half-angle `spread_angle`
+            e.type = capi.EMITTER_DIRECTIONALSPOT
+            e.to_world[:] = list(tw.astype(F32).reshape(-1))
+            e.to_local[:] = list(np.linalg.inv(tw).astype(F32).reshape(-1))
+            e.env_pad[0] = float(np.sin(F32(p.get("spread_angle", 0.0)), dtype=F32))
         e.radiance = self.texture(p, "irradiance", None, within_emitter=True)
         if e.radiance < 0:
             e.radiance = self.texture_plugin(Properties("d65"), True)
@@ -660,9 +730,12 @@ class FlatScene:
             offset = F32(lum.astype(np.float64).sum() / (W * H))
             if offset - min(F32(0), lum.min()) <= F32(0.01) * offset:
                 offset = F32(0)
-        scale = (rgb.max(axis=2) * F32(2)).astype(F32)
-        coeff = spectra.srgb_model_fetch(rgb / np.maximum(F32(1e-8), scale)[..., None])
-        data = np.concatenate([coeff, scale[..., None]], axis=2).astype(F32)
+        if self.rgb:   # envmap.cpp:199-200: coeff = rgb (kept 4 floats wide; the fourth is unused)
+            data = np.concatenate([rgb, np.zeros_like(rgb[..., :1])], axis=2).astype(F32)
+        else:
+            scale = (rgb.max(axis=2) * F32(2)).astype(F32)
+            coeff = spectra.srgb_model_fetch(rgb / np.maximum(F32(1e-8), scale)[..., None])
+            data = np.concatenate([coeff, scale[..., None]], axis=2).astype(F32)
         data = np.concatenate([data, data[:, :1]], axis=1)                    # last column mirrors the first
         theta_scale = F32(1.0) / F32(H - 1) * F32(np.pi)
         sin_theta = np.sin((np.arange(H, dtype=F32) * theta_scale).astype(F32)).astype(F32)
@@ -704,6 +777,8 @@ class FlatScene:
         s = capi.Sensor()
         s.srf = -1
         if "srf" in p:
+            if self.rgb:
+                raise RuntimeError("sensor 'srf': spectral response functions need a spectral variant")
             s.srf = self.texture(p, "srf", None)
             if self.textures[s.srf].type not in (capi.TEX_REGULAR, capi.TEX_IRREGULAR):
                 raise RuntimeError("sensor 'srf' must be a regular/irregular spectrum")
@@ -788,7 +863,8 @@ class FlatScene:
         if self.a_cdf.size == 0:
             self.a_cdf = np.zeros(1, F32)
         tabs = spectra.cie_tables()
-        self.a_cie = np.ascontiguousarray(np.concatenate([tabs["srgb"], tabs["xyz"][1:2]]), dtype=F32)   # R, G, B, Y rows
+        self.a_cie = np.ascontiguousarray(np.concatenate([tabs["srgb"], tabs["xyz"][1:2], tabs["xyz"][0:1], tabs["xyz"][2:3]]),
+                                          dtype=F32)   # R, G, B, Y, X, Z rows
         # scene bounding sphere for directional emitters (src/render/scene.cpp:70-80, BoundingSphere from bbox)
         if np.all(np.isfinite(self.bbox[0])):
             c = (self.bbox[0] + self.bbox[1]) * 0.5
@@ -799,7 +875,8 @@ class FlatScene:
             if e.type == capi.EMITTER_DIRECTIONAL:
                 e.bsphere_center[:] = list(c.astype(F32))
                 e.bsphere_radius = r
-            elif e.type in (capi.EMITTER_CONSTANT, capi.EMITTER_ENVMAP):  # ::set_scene (constant.cpp:74-89, envmap.cpp:327-341)
+            elif e.type in (capi.EMITTER_CONSTANT, capi.EMITTER_ENVMAP, capi.EMITTER_DIRECTIONALSPOT):
+                # ::set_scene (constant.cpp:74-89, envmap.cpp:327-341, directionalspot.cpp:102-112)
                 ray_eps = F32(2.0 ** -24 * 1500)   # math::RayEpsilon = dr::Epsilon<float> * 1500 (include/mitsuba/core/math.h:18)
                 e.bsphere_center[:] = list(c.astype(F32))
                 e.bsphere_radius = max(ray_eps, F32(r) * (F32(1) + ray_eps)) if np.all(np.isfinite(self.bbox[0])) else ray_eps
@@ -872,9 +949,10 @@ def _parse_fov(p, aspect):
     raise RuntimeError("The 'fov_axis' parameter must be set to one of 'smaller', 'larger', 'diagonal', 'x', or 'y'!")
 
 
-def flatten(tree):
-    """Scene ctor (src/render/scene.cpp:22-96): walk the children of the <scene> node."""
-    fs = FlatScene()
+def flatten(tree, rgb=False):
+    """Scene ctor (src/render/scene.cpp:22-96): walk the children of the <scene> node.  rgb: instantiate the plugins as an RGB
+    variant does (is_rgb_v<Spectrum>)."""
+    fs = FlatScene(rgb)
     if tree.cls != "scene":
         raise RuntimeError("flatten(): expected a scene node")
     for _, c in tree.all_children():

@@ -489,6 +489,7 @@ def scene_path(name, cache_dir=None):
 # the reference's own files for the named configs (relative to the scenes directory) and the -D defaults its scripts pass
 _REFERENCE_FILES = {"cbox": ("cbox/cbox.xml", {}), "cbox-grating": ("cbox-grating/cbox.xml", {}),
                     "gratingcap": ("gratingcap/gratingcap.xml", {}),
+                    "gratings": ("gratings/gratings.xml", {}),   # directionalspot light on a non-radial sinusoidal grating (results/gratings)
                     "veach-mis": ("veach-mis/scene.xml", {"integrator": "plt", "max_depth": 7})}
 
 

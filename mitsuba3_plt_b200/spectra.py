@@ -15,6 +15,7 @@ _DATA = os.path.join(os.path.dirname(__file__), "data")
 
 MI_CIE_MIN, MI_CIE_MAX, MI_CIE_SAMPLES = 360.0, 830.0, 95
 MI_CIE_D65_NORMALIZATION = 1.0 / 98.99741751876255
+MI_CIE_Y_NORMALIZATION = 1.0 / 106.7502593994140625
 
 _tables = None
 _model = None
@@ -119,3 +120,42 @@ def srgb_to_linear(x):
     """Bitmap::convert sRGB gamma removal for 8-bit inputs (src/core/bitmap.cpp, struct converter)."""
     x = np.asarray(x, dtype=np.float32)
     return np.where(x <= 0.04045, x / 12.92, ((x + 0.055) / 1.055) ** 2.4).astype(np.float32)
+
+
+def xyz_to_srgb(xyz):
+    """include/mitsuba/core/spectrum.h:406-412 (float32)"""
+    M = np.array([[3.240479, -1.537150, -0.498535], [-0.969256, 1.875991, 0.041556], [0.055648, -0.204043, 1.057311]], dtype=np.float32)
+    x = np.asarray(xyz, dtype=np.float32)
+    acc = M[:, 0] * x[0]
+    for c in (1, 2):
+        acc = (M[:, c].astype(np.float64) * np.float64(x[c]) + acc.astype(np.float64)).astype(np.float32)
+    return acc.astype(np.float32)
+
+
+def spectrum_list_to_srgb(wavelengths, values, bounded=True, d65=False):
+    """src/core/spectrum.cpp:85-130 (float32): integrate a piecewise-linear spectrum against the CIE curves (times D65 for
+    reflectances) in 1000 steps and convert to linear sRGB; what the RGB variants do with <spectrum value="w:v, ..."> at load time."""
+    F = np.float32
+    wl = np.asarray(wavelengths, dtype=F); vals = np.asarray(values, dtype=F)
+    tabs = cie_tables()
+    steps = 1000
+    xyz = np.zeros(3, dtype=F)
+    scale = F(MI_CIE_SAMPLES - 1) / (F(MI_CIE_MAX) - F(MI_CIE_MIN))
+    for i in range(steps):
+        w = F(MI_CIE_MIN) + (F(i) / F(steps - 1)) * (F(MI_CIE_MAX) - F(MI_CIE_MIN))
+        if w < wl[0] or w > wl[-1]:
+            continue
+        index = int(np.clip(np.searchsorted(wl, w, side="right") - 1, 0, len(wl) - 2))   # math::find_interval
+        w0, w1, v0, v1 = wl[index], wl[index + 1], vals[index], vals[index + 1]
+        v = ((w - w1) * v0 + (w0 - w) * v1) / (w0 - w1)
+        t = (w - F(MI_CIE_MIN)) * scale
+        i0 = int(min(max(int(t), 0), MI_CIE_SAMPLES - 2))
+        f1 = F(t - F(i0)); f0 = F(1) - f1
+        c = (f0 * tabs["xyz"][:, i0] + f1 * tabs["xyz"][:, i0 + 1]).astype(F)
+        dv = F(1)
+        if d65:   # cie_d65(w): table lookup times MI_CIE_D65_NORMALIZATION (spectrum.h:300-326)
+            dv = F((f0 * tabs["d65"][i0] + f1 * tabs["d65"][i0 + 1]) * F(MI_CIE_D65_NORMALIZATION))
+        xyz = (xyz + c * v * dv).astype(F)
+    xyz = (xyz * ((F(MI_CIE_MAX) - F(MI_CIE_MIN)) / F(steps))).astype(F)
+    rgb = xyz_to_srgb(xyz)
+    return np.clip(rgb, 0, 1).astype(F) if bounded else np.maximum(rgb, 0).astype(F)

@@ -535,6 +535,9 @@ struct Scene {
     std::vector<uint32_t> prims; /* < n_faces: triangle, else analytic shape id + n_faces */
     float emitter_pmf = 0.f;
     int32_t env = -1; /* index of the environment emitter (Scene::environment(), scene.cpp:60-67), -1 if none */
+    bool rgb = false; /* PLTB_RENDER_RGB: the `*_rgb` variants -- Spectrum = Color3f in lanes 0..2 of S4 (lane 3 repeats lane 2, so
+                         per-lane arithmetic and max() are those of a 3-vector); SI::wavelengths then carries the path's
+                         `sampling_wavelengths` (plt.py:64-70,158) instead of sensor wavelengths, which do not exist */
     V3 pos(uint32_t i) const { return { d->positions[3 * i], d->positions[3 * i + 1], d->positions[3 * i + 2] }; }
     V3 nrm(uint32_t i) const { return { d->normals[3 * i], d->normals[3 * i + 1], d->normals[3 * i + 2] }; }
     V2 uv(uint32_t i) const { return { d->texcoords[2 * i], d->texcoords[2 * i + 1] }; }
@@ -878,6 +881,7 @@ S4 tex_eval(const Scene &sc, int32_t id, const S4 &wl, V2 uv) {
     const float *data = sc.d->tex_data + t.offset;
     switch (t.type) {
         case PLTB_TEX_UNIFORM: return S4(t.p[0]);
+        case PLTB_TEX_RGB: r[0] = t.p[0]; r[1] = t.p[1]; r[2] = r[3] = t.p[2]; return r;   /* srgb.cpp:56-57, eval :77-98 in RGB mode */
         case PLTB_TEX_SRGB: for (int i = 0; i < 4; ++i) r[i] = srgb_model_eval(t.p, wl[i]); return r;
         case PLTB_TEX_D65: /* src/spectra/d65.cpp:148-162 */
             for (int i = 0; i < 4; ++i) {
@@ -900,6 +904,17 @@ S4 tex_eval(const Scene &sc, int32_t id, const S4 &wl, V2 uv) {
             const float *v00 = data + 3 * ((size_t) y0 * t.width + x0), *v10 = data + 3 * ((size_t) y0 * t.width + x1),
                         *v01 = data + 3 * ((size_t) y1 * t.width + x0), *v11 = data + 3 * ((size_t) y1 * t.width + x1);
             float w1x = pu - (float) iu, w0x = 1.f - w1x, w1y = pv - (float) iv, w0y = 1.f - w1y;
+            if (t.flags & PLTB_TEXFLAG_RGB) {   /* RGB variants: texels are linear RGB, dr::Texture::eval with FilterMode::Linear
+                                                   (ext/drjit/include/drjit/texture.h:386-419): four fmadd accumulations */
+                for (int c = 0; c < 3; ++c) {
+                    float acc = fmadd(v00[c], w0x * w0y, 0.f);
+                    acc = fmadd(v10[c], w1x * w0y, acc);
+                    acc = fmadd(v01[c], w0x * w1y, acc);
+                    r[c] = fmadd(v11[c], w1x * w1y, acc);
+                }
+                r[3] = r[2];
+                return r;
+            }
             for (int i = 0; i < 4; ++i) {
                 float c00 = srgb_model_eval(v00, wl[i]), c10 = srgb_model_eval(v10, wl[i]),
                       c01 = srgb_model_eval(v01, wl[i]), c11 = srgb_model_eval(v11, wl[i]);
@@ -950,6 +965,7 @@ inline bool mac_mic_compatibility(V3 m, V3 wi, V3 wo, float cos_theta_i, bool re
 }
 /* mitsuba::luminance(value, wavelengths) in spectral mode: mean(cie1931_y(wl) * value) (spectrum.h:272-295,414-429) */
 inline float spectral_luminance(const Scene &sc, const S4 &value, const S4 &wl) {
+    if (sc.rgb) return value[0] * 0.212671f + value[1] * 0.715160f + value[2] * 0.072169f;   /* luminance(Color3f), spectrum.h:431-434 */
     const float *y = sc.d->cie_srgb + 3 * 95;
     float acc[4];
     for (int i = 0; i < 4; ++i) {
@@ -1229,7 +1245,8 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
             float pdf; V3 m = distr.sample(si.wi, s2, pdf);
             o.bs.pdf = pdf;
             V3 reflection_dir = reflect(si.wi, m);
-            float wavelength = si.wavelengths[0];
+            /* spectral: the hero wavelength; RGB variants: "Use sample 1 for random wavelength sample" (roughgrating.cpp:499-506) */
+            float wavelength = sc.rgb ? s1 * (830.f - 150.0f - 360.f) + 360.f : si.wavelengths[0];
             /* sample_diffract */
             Frame nf(m);
             V3 wi_local = nf.to_local(si.wi);
@@ -1317,6 +1334,55 @@ S4 grating_lobe_sum(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     return result;
 }
 
+/* cie1931_xyz (include/mitsuba/core/spectrum.h:236-264) followed by xyz_to_srgb (:406-412; Matrix * vector = fmadd chain over the
+ * columns, ext/drjit/include/drjit/matrix.h:142-150).  cie = the 6 x 95 table of pltb_scene_desc: rows 4, 3, 5 are X, Y, Z. */
+inline void wavelength_to_srgb(const float *cie, float wl, float rgb[3]) {
+    float t = (wl - 360.f) * (94 / (830.f - 360.f));
+    bool active = wl >= 360.f && wl <= 830.f;
+    uint32_t i0 = std::min((uint32_t) std::max(t, 0.f), 93u), i1 = i0 + 1;   /* clip(UInt32(t), 0, 93) */
+    float w1 = t - (float) i0, w0 = 1.f - w1;
+    const float *X = cie + 4 * 95, *Y = cie + 3 * 95, *Z = cie + 5 * 95;
+    float x = active ? fmadd(w0, X[i0], w1 * X[i1]) : 0.f, y = active ? fmadd(w0, Y[i0], w1 * Y[i1]) : 0.f,
+          z = active ? fmadd(w0, Z[i0], w1 * Z[i1]) : 0.f;
+    rgb[0] = fmadd(-0.498535f, z, fmadd(-1.537150f, y, 3.240479f * x));
+    rgb[1] = fmadd(0.041556f, z, fmadd(1.875991f, y, -0.969256f * x));
+    rgb[2] = fmadd(1.057311f, z, fmadd(-0.204043f, y, 0.055648f * x));
+}
+
+/* The RGB fallback of RoughGrating::wbsdf_eval (roughgrating.cpp:716-790), before the Fresnel factor and specular_reflectance:
+ * exhaustive search over the lobes at the three `sampling_wavelengths` of the path (si.wavelengths here), each lobe coloured with
+ * xyz_to_srgb(cie1931_xyz(wl)); every lobe (the (0, 0) one too) carries the angular coherence factor. */
+S4 grating_lobe_sum_rgb(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
+    Grating g = make_grating(b, si.uv);
+    V3 reflection_dir = reflect(si.wi);
+    float result[3] = { 0.f, 0.f, 0.f };
+    float a = 2 * std::sqrt(b.f[1] * b.f[2]);
+    int half = (int) b.u[2] / 2;
+    for (int lx = -half; lx < half + 1; lx++) {
+        for (int ly = -half; ly < half + 1; ly++) {
+            for (int i = 0; i < 3; i++) {
+                float wl = si.wavelengths[i];
+                float k = kTwoPi / (wl * 1e-3f);
+                float lobe_intensity = g.lobe_intensity(lx, ly, si.wi, wl * 1e-3f);
+                bool lobe_active; V3 center_dir = g.diffract(si.wi, lx, ly, wl * 1e-3f, lobe_active);
+                float colour[3]; wavelength_to_srgb(sc.d->cie_srgb, wl, colour);
+                float lobes_result = (lobe_active && std::fabs(unit_angle(center_dir, wo)) < a) ? lobe_intensity : 0.0f;
+                float det = inv_coherence_det(k, b.f[8], 1.0f);
+                float angle_offset = std::fabs(unit_angle(reflection_dir, wo));
+                float inv_det = std::isnan(det) ? 0.0f : det;
+                float angular_coh = std::exp(-0.5f * angle_offset * inv_det * angle_offset);
+                if (std::isnan(angular_coh)) angular_coh = 0.0f;
+                for (int c = 0; c < 3; ++c) result[c] += (lobes_result * colour[c]) * angular_coh;   /* lobes_result * colour * angular_coh */
+            }
+        }
+    }
+    S4 r; r[0] = result[0]; r[1] = result[1]; r[2] = r[3] = result[2];
+    return r;
+}
+inline S4 grating_lobe_sum_any(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
+    return sc.rgb ? grating_lobe_sum_rgb(sc, b, si, wo) : grating_lobe_sum(sc, b, si, wo);
+}
+
 /* wbsdf_eval: base -> eval (src/render/bsdf.cpp:59-71) */
 S4 bsdf_eval_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     float cos_theta_i = si.wi.z, cos_theta_o = wo.z;
@@ -1341,7 +1407,7 @@ S4 bsdf_eval_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
         case PLTB_BSDF_ROUGHGRATING: { /* roughgrating.cpp:676-970, spectral branch :841-969 (JIT semantics: the
                                           cos_theta tests do not mask the returned value) */
             V3 H = normalize(wo + si.wi);
-            S4 result = grating_lobe_sum(sc, b, si, wo);
+            S4 result = grating_lobe_sum_any(sc, b, si, wo);   /* RGB variants: the fallback of :716-790 */
             S4 F = conductor_F(sc, b, si, dot(si.wi, H));
             if (b.tex[2] >= 0) result = result * tex_eval(sc, b.tex[2], si.wavelengths, si.uv);
             return F * result;
@@ -1366,7 +1432,7 @@ float bsdf_pdf_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
         }
         case PLTB_BSDF_ROUGHGRATING: {
             Grating g = make_grating(b, si.uv);
-            float k = kTwoPi / (si.wavelengths[0] * 1e-3f);
+            float k = kTwoPi / (si.wavelengths[0] * 1e-3f);   /* RGB variants: sd.sampling_wavelengths[0] (:1027-1031) == si.wavelengths[0] here */
             return g.alpha(si.wi, k);
         }
         default: (void) sc; return 0.f;
@@ -1518,6 +1584,15 @@ S4 envmap_eval_spectrum(const Scene &sc, const pltb_emitter &em, V2 uv, const S4
     const float *data = sc.d->tex_data + em.env_data;
     uint32_t index = py * rx + px;
     const float *v00 = data + 4 * (size_t) index, *v10 = v00 + 4, *v01 = v00 + 4 * (size_t) rx, *v11 = v01 + 4;
+    if (sc.rgb) {   /* envmap.cpp:569-579: texels are (r, g, b, unused); no whitepoint */
+        S4 result;
+        for (int c = 0; c < 3; ++c) {
+            float v0 = fmadd(w0x, v00[c], w1x * v10[c]), v1 = fmadd(w0x, v01[c], w1x * v11[c]);
+            result[c] = fmadd(w0y, v0, w1y * v1) * em.env_scale;
+        }
+        result[3] = result[2];
+        return result;
+    }
     S4 white = tex_eval(sc, em.radiance, wl, V2{ 0.f, 0.f });
     S4 result;
     float f0 = fmadd(w0x, v00[3], w1x * v10[3]), f1 = fmadd(w0x, v01[3], w1x * v11[3]), f = fmadd(w0y, f0, w1y * f1);
@@ -1805,6 +1880,16 @@ bool nee_light_sample(const Scene &sc, const Bounce &b, V2 u2, Counters &cnt, Ne
         ds.p = si.p + dw * dist;
         ds.n = -dw; ds.uv = uv; ds.delta = false; ds.d = dw; ds.dist = dist;
         ds.pdf = act_s ? pdf * inv_sin_theta * (1.f / (2.f * sqr(kPi))) : 0.f;
+    } else if (em.type == PLTB_EMITTER_DIRECTIONALSPOT) { /* DirectionalSpreadEmitter::sample_direction, src/emitters/directionalspot.cpp:161-192 */
+        /* warp::square_to_uniform_disk (warp.h:37-42) * sin(spread_angle) */
+        float r = std::sqrt(sample.y), ang = kTwoPi * sample.x;
+        float sn = std::sin(ang), cs = std::cos(ang);
+        V2 angular = { (cs * r) * em.env_pad[0], (sn * r) * em.env_pad[0] };
+        V3 dd = xf_vector(em.to_world, normalize(V3(angular.x, angular.y, 1.f)));
+        V3 c(em.bsphere_center[0], em.bsphere_center[1], em.bsphere_center[2]);
+        float radius = std::max(em.bsphere_radius, norm(si.p - c)), dist = 2.f * radius;
+        ds.p = si.p - dd * dist;
+        ds.n = dd; ds.uv = V2{ 0.f, 0.f }; ds.pdf = 1.f; ds.delta = true; ds.d = -dd; ds.dist = dist;
     } else { /* DirectionalEmitter::sample_direction, src/emitters/directional.cpp:149-176 */
         V3 dirn(em.direction[0], em.direction[1], em.direction[2]);
         ds.d = -dirn;
@@ -1854,12 +1939,21 @@ static void trace_nonfinite(const Scene &sc, const Bounce *bb, uint32_t n_writte
     fflush(f);
 }
 
-S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, const S4 &wavelengths, uint32_t max_depth, uint32_t rr_depth,
+/* plt.py:64-70: four draws scaled by scale_wl = (MI_CIE_MAX - 150 - MI_CIE_MIN) + MI_CIE_MIN = 680.  Dead in the spectral
+ * variants (N1); in the RGB variants the first three are the path's `sampling_wavelengths` (BounceData / PLTSamplePhaseData,
+ * :158,280), which the RGB fallback of roughgrating reads -- they replace `wavelengths` (empty in RGB mode) from here on. */
+inline void draw_sampling_wavelengths(const Scene &sc, PCG32 &rng, S4 &wavelengths) {
+    float u[4];
+    for (int i = 0; i < 4; ++i) u[i] = rng.next_float32();
+    if (sc.rgb) { wavelengths[0] = u[0] * 680.f; wavelengths[1] = u[1] * 680.f; wavelengths[2] = wavelengths[3] = u[2] * 680.f; }
+}
+
+S4 plt_sample(const Scene &sc, PCG32 &rng, Ray ray, S4 &wavelengths, uint32_t max_depth, uint32_t rr_depth,
               Counters &cnt) {
     Bounce bb[PLTB_MAX_DEPTH];
 
     /* ---- plt_sample_phase, plt.py:50-171 ---- */
-    for (int i = 0; i < 4; ++i) (void) rng.next_float32(); /* dead "sampling_wavelengths" draws (N1), :65-70 */
+    draw_sampling_wavelengths(sc, rng, wavelengths);
     S4 alpha(1.f);
     float eta = 1.f;
     uint32_t depth = 0, i = 0;
@@ -2088,6 +2182,7 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
                          pltb_sample_dump *dump, pltb_stats *stats, int n_threads) {
     Scene sc;
     prepare_scene(sc, desc);
+    sc.rgb = (prm->flags & PLTB_RENDER_RGB) != 0;
     const uint32_t fw = desc->film.width, W = fw * desc->n_sensors, H = desc->film.height;
     uint32_t cx = prm->crop_x, cy = prm->crop_y, cw = prm->crop_w ? prm->crop_w : W, ch = prm->crop_h ? prm->crop_h : H;
     if (n_threads <= 0) n_threads = (int) std::thread::hardware_concurrency();
@@ -2115,13 +2210,14 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
                     PCG32 rng; rng.seed(v0, v1);
                     V2 jitter; jitter.x = rng.next_float32(); jitter.y = rng.next_float32();
                     V2 pos_f = { (float) x + jitter.x, (float) y + jitter.y };
-                    float wav_sample = rng.next_float32();
+                    /* wavelength_sample is only drawn in spectral variants (common.py:297-299) */
+                    float wav_sample = sc.rgb ? 0.f : rng.next_float32();
                     /* BatchSensor (src/sensors/batch.cpp:131-190): the film is split in x between the sensors */
                     uint32_t sidx = x / fw;
                     const pltb_sensor &sn = desc->sensors[sidx];
                     V2 pos_adj = { (pos_f.x - (float) (sidx * fw)) * rcp((float) fw), pos_f.y * rcp((float) H) };
-                    S4 wl, wgt;
-                    sample_wavelengths(sc, sn, wav_sample, wl, wgt);
+                    S4 wl, wgt(1.f);   /* RGB variants: no wavelengths, ray weight 1 (sensor.cpp:113-127) */
+                    if (!sc.rgb) sample_wavelengths(sc, sn, wav_sample, wl, wgt);
                     Ray ray = sensor_ray(sn, pos_adj);
                     Counters c0 = cnt;
                     S4 L;
@@ -2153,7 +2249,8 @@ double plt_oracle_render(const pltb_scene_desc *desc, const pltb_render_params *
                         }
                     }
                     if (!films.empty()) {
-                        spectrum_to_srgb(desc->cie_srgb, L * wgt, wl, values);
+                        if (sc.rgb) { S4 v = L * wgt; values[0] = v[0]; values[1] = v[1]; values[2] = v[2]; }   /* rgb = value, common.py:386-391 */
+                        else spectrum_to_srgb(desc->cie_srgb, L * wgt, wl, values);
                         values[3] = 1.f;
                         splat(desc->film, W, H, films[tid].data(), pos_f, values, nch);
                     }
@@ -2256,6 +2353,22 @@ void plt_oracle_spectrum_to_srgb(const float *cie_srgb, const float *value, cons
     spectrum_to_srgb(cie_srgb, v, w, rgb);
 }
 float plt_oracle_srgb_model_eval(const float *c, float wl) { return srgb_model_eval(c, wl); }
+/* xyz_to_srgb(cie1931_xyz(wl)), the lobe colour of roughgrating's RGB fallback; cie = the 6 x 95 table of pltb_scene_desc */
+void plt_oracle_wavelength_to_srgb(const float *cie, float wl, float *rgb) { wavelength_to_srgb(cie, wl, rgb); }
+/* RoughGrating::wbsdf_eval / wbsdf_pdf in an RGB variant for the BSDF of shape `shape`: si.wavelengths = the path's sampling wavelengths.
+ * out = { eval[3], pdf, lobe sum before Fresnel[3] } */
+void plt_oracle_bsdf_probe_rgb(const pltb_scene_desc *d, int32_t shape, const float *wi, const float *uv, const float *swl3, const float *wo, float *out) {
+    Scene sc; prepare_scene(sc, d); sc.rgb = true;
+    SI si; si.t = 1.f; si.shape = shape; si.wi = V3(wi[0], wi[1], wi[2]); si.uv = V2{ uv[0], uv[1] };
+    si.n = V3(0.f, 0.f, 1.f); si.sh.n = si.n; si.sh.s = V3(1.f, 0.f, 0.f); si.sh.t = V3(0.f, 1.f, 0.f);
+    si.wavelengths[0] = swl3[0]; si.wavelengths[1] = swl3[1]; si.wavelengths[2] = si.wavelengths[3] = swl3[2];
+    const V3 w(wo[0], wo[1], wo[2]);
+    const S4 e = wbsdf_eval(sc, si, w);
+    out[0] = e[0]; out[1] = e[1]; out[2] = e[2]; out[3] = wbsdf_pdf(sc, si, w);
+    const pltb_bsdf *b = si_bsdf(sc, si);
+    S4 ls = (b && b->type == PLTB_BSDF_ROUGHGRATING) ? grating_lobe_sum_rgb(sc, *b, si, w) : S4(0.f);
+    out[4] = ls[0]; out[5] = ls[1]; out[6] = ls[2];
+}
 /* Principled::eval / ::pdf for a spatially uniform base colour (KAT against src/bsdfs/tests/test_principled.py:124-200);
  * cie is the 4 x 95 table of pltb_scene_desc (its Y row defines luminance()). out = { eval[4], pdf } */
 void plt_oracle_principled_eval_pdf(const pltb_bsdf *b_in, float base_color, const float *cie, const float *wi, const float *wo,

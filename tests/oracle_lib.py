@@ -75,6 +75,8 @@ def render(flat, spp, seed=0, max_depth=7, rr_depth=50, spp_begin=0, spp_count=N
     prm.crop_x, prm.crop_y, prm.crop_w, prm.crop_h = cx, cy, cw, ch
     if polarized:
         prm.flags |= capi.RENDER_POLARIZED | (capi.RENDER_STOKES if stokes else 0)
+    if getattr(flat, "rgb", False):   # scene flattened for an RGB variant
+        prm.flags |= capi.RENDER_RGB
     nch = capi.film_channels(prm.flags)
     out = {}
     dmp = None

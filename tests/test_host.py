@@ -208,9 +208,14 @@ def test_plugin_parameters_and_errors(mi):
     with pytest.raises(RuntimeError):
         mi.load_dict({"type": "volpath"})
     with pytest.raises(ImportError):
-        mi.set_variant("cuda_ad_rgb_polarized")          # the RGB variants are not built
-    mi.set_variant("cuda_ad_rgb_polarized", "llvm_spectral")
-    assert mi.variant() == "llvm_spectral" and not mi.is_polarized
+        mi.set_variant("cuda_ad_mono")                   # monochromatic variants are not built
+    mi.set_variant("cuda_ad_mono", "llvm_spectral")
+    assert mi.variant() == "llvm_spectral" and not mi.is_polarized and mi.is_spectral and not mi.is_rgb
+    try:   # the RGB variants (the second mode of main-headless.py:131-133)
+        mi.set_variant("cuda_ad_rgb_polarized")
+        assert mi.is_rgb and mi.is_polarized and not mi.is_spectral
+    finally:
+        mi.set_variant("llvm_spectral")
     try:   # the polarized spectral variants: Spectrum = Mueller matrix; `stokes` needs one of them and one nested integrator
         mi.set_variant("cuda_ad_spectral_polarized")
         assert mi.is_polarized
