@@ -88,7 +88,7 @@ PLTB_HD BSDFSampleOut bsdf_sample_inner(const DeviceScene &sc, const pltb_bsdf &
             Grating g = make_grating(b, uv);
             V2 pdf_xy; int lx, ly;
             g.sample_lobe(sc.bessel, lobe_s2, wi_local, wavelength * 1e-3f, lx, ly, pdf_xy);
-            float intensity = g.lobe_intensity(sc.bessel, lx, ly, wi_local, wavelength);  // nm as written (N2)
+            float intensity = g.lobe_intensity_sampled(sc.bessel, lx, ly, wi_local, wavelength);  // nm as written (N2)
             bool valid; V3 wo_local = g.diffract(wi_local, lx, ly, wavelength * 1e-3f, valid);
             o.wo = nf.to_world(wo_local);
             float grating_pdf = pdf_xy.x * pdf_xy.y;

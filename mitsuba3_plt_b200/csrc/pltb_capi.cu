@@ -5,6 +5,8 @@
 #include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: ranges per wavefront stage for nsys / ncu --nvtx (no-ops without a tool attached)
 
 #include <atomic>
+#include <cmath>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -240,6 +242,41 @@ int pltb_scene_create(pltb_context *ctx, const pltb_scene_desc *d, pltb_scene **
         for (int i = 0; i < 20; ++i) { float t = a + h * (float) i; ds.bessel.t[i] = t; ds.bessel.sin_t[i] = sinf(t); }
         ds.bessel.t[0] = a; ds.bessel.sin_t[0] = sinf(a); ds.bessel.t[19] = b; ds.bessel.sin_t[19] = sinf(b);
         ds.bessel.h_over_3 = h / 3.0f;
+        // the same rule tabulated as cubic Hermite segments (BesselTables::tab): values and derivatives in double from the float nodes
+        static std::vector<float4> tab;   // scene-independent; built once per process
+        static std::mutex tab_mutex;
+        {
+            std::lock_guard<std::mutex> lock(tab_mutex);
+            if (tab.empty()) {
+                tab.resize((size_t) kBesselTabOrders * kBesselTabN);
+                const double hs = 1.0 / kBesselTabInvH, pi = 3.14159265358979323846;
+                auto eval = [&](int l, double x, double &f, double &df) {
+                    double sum = 0, dsum = 0;
+                    for (int i = 0; i < 20; ++i) {
+                        const double w = (i == 0 || i == 19) ? 1.0 : ((i & 1) ? 4.0 : 2.0), ti = ds.bessel.t[i], si = ds.bessel.sin_t[i];
+                        const double arg = (double) l * ti - x * si;
+                        sum += w * cos(arg); dsum += w * si * sin(arg);
+                    }
+                    const double c = (double) kInvPi * (double) ds.bessel.h_over_3;
+                    const double sm = c * sum, dsm = c * dsum;
+                    const double wf = 1.0 / (1.0 + exp(-1.5 * (fabs(x) - (45.0 + l))));
+                    f = (1.0 - wf) * sm; df = (1.0 - wf) * dsm;
+                    if (wf > 1e-30 && x > 1e-3) {   // blend with the asymptotic form (math.h:316-347)
+                        const double amp = sqrt(2.0 / (pi * x)), ph = x - pi * l / 2.0 - pi / 4.0, as = amp * cos(ph);
+                        const double das = -amp * sin(ph) - 0.5 / x * as, dwf = 1.5 * wf * (1.0 - wf);
+                        f += wf * as; df += wf * das + dwf * (as - sm);
+                    }
+                };
+                for (int l = 1; l <= kBesselTabOrders; ++l)
+                    for (int i = 0; i < kBesselTabN; ++i) {
+                        double f0, d0, f1, d1;
+                        eval(l, i * hs, f0, d0); eval(l, (i + 1) * hs, f1, d1);
+                        tab[(size_t) (l - 1) * kBesselTabN + i] = make_float4((float) f0, (float) (hs * d0), (float) f1, (float) (hs * d1));
+                    }
+            }
+        }
+        rc |= upload(s->allocs, tab.data(), tab.size(), &ds.bessel.tab);
+        if (rc) { pltb_scene_release(s); return PLTB_ERR_CUDA; }
     }
     s->film_w = d->film.width * d->n_sensors; s->film_h = d->film.height;
     for (uint32_t i = 0; i < d->n_shapes; ++i)

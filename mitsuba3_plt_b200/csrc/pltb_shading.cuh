@@ -227,9 +227,30 @@ struct Grating {
     // the same for sample_lobe's selection weights (sinusoidal gratings: reduced-precision Bessel, see bessel_j_fast)
     PLTB_HD float axis_term_select(const BesselTables &bt, float a, int l) const {
 #ifndef PLTB_EXACT_SELECT
-        if (l != 0 && (type & 0xFu) == 0) return sqr(bessel_j_fast(bt, a, l));
+        if (l != 0 && (type & 0xFu) == 0) {
+            float j;
+            if (bessel_j_tab(bt, a, l, j)) return sqr(j);   // tabulated 20-node rule (BesselTables::tab)
+            return sqr(bessel_j_fast(bt, a, l));
+        }
 #endif
         return axis_term(bt, a, l);
+    }
+    // lobe_intensity for the lobe RoughGrating::wbsdf_sample has just drawn (roughgrating.cpp:440, the nanometre-unit call N2): the
+    // value scales the sample-phase throughput only, never the replayed one, so sinusoidal gratings read the tabulated rule
+    PLTB_HD float lobe_intensity_sampled(const BesselTables &bt, int lx, int ly, V3 wi, float wl) const {
+#ifndef PLTB_EXACT_SELECT
+        if ((type & 0xFu) == 0) {
+            const float a = kFourPi * q / (wl * fabsf(wi.z));
+            float jx = 1.f, jy = 1.f;
+            const bool okx = lx == 0 || bessel_j_tab(bt, a, lx, jx), oky = ly == 0 || is_1d() || bessel_j_tab(bt, a, ly, jy);
+            if (okx && oky) {
+                const float ix = lx == 0 ? 1.0f : sqr(jx);
+                const float iy = is_1d() ? ix : (ly == 0 ? 1.0f : sqr(jy));
+                return multiplier * ix * iy;
+            }
+        }
+#endif
+        return lobe_intensity(bt, lx, ly, wi, wl);
     }
     PLTB_HD float lobe_intensity(const BesselTables &bt, int lx, int ly, V3 wi, float wl) const {
         const float a = kFourPi * q / (wl * fabsf(wi.z));
