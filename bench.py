@@ -221,6 +221,15 @@ def run_ours(args):
             traffic = round(t["dram_bytes_per_launch"] * scale)
             traffic_note = (f"dram__bytes_read+write per launch from profiles/ncu_traffic.json ({t['dram_bytes_per_launch']} B at "
                             f"{tj.get('_samples_per_pass_in_capture', 1 << 23)} samples per pass) scaled by {scale:.2f} to this run's pass size")
+    # the limiter of this path is the SM issue rate at low occupancy, not HBM: next to the contract's HBM roofline the
+    # line carries the issue-slot utilisation of the dominant kernel from the committed ncu capture (share must agree, not absolutes)
+    issue = None
+    if os.path.exists(tpath) and tj.get(top, {}).get("issue_slots_busy_pct") is not None:
+        t = tj[top]
+        issue = {"kernel": top, "bound": "issue", "achieved": t["issue_slots_busy_pct"], "peak": 100.0, "unit": "% of issue slots busy",
+                 "frac": round(t["issue_slots_busy_pct"] / 100.0, 3), "active_lanes_of_32": t.get("active_lanes"),
+                 "occupancy_pct": t.get("occupancy_pct"), "registers": t.get("registers"),
+                 "source": "profiles/ncu_traffic.json (ncu --set full, one pass of the same scene)"}
     out = {
         "metric": METRIC, "value": round(value, 3), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "strong",
@@ -251,6 +260,8 @@ def run_ours(args):
                              "utilisation, active lanes and stall mix per kernel from ncu; kernel times here come from CUDA "
                              "events after every launch in a separate profiled step"},
     }
+    if issue:
+        out["roofline_issue"] = issue
     if not args.no_cpu_baseline:
         c = cpu_oracle_run(args, scene, args.cpu_seconds)
         out["cpu_baseline"] = {"value": round(c["samples"] / c["seconds"] / 1e6, 4), "unit": "Msamples/s",

@@ -90,14 +90,14 @@ enum {
     PLTB_BSDF_ROUGHCONDUCTOR = 4,/* src/bsdfs/roughconductor.cpp tex[0..2] as conductor (tex[2] may be -1),
                                                                  f[1] = alpha_u, f[2] = alpha_v, u[0] = distribution,
                                                                  u[1] = sample_visible */
-    PLTB_BSDF_PRINCIPLED = 6,    /* src/bsdfs/principled.cpp (without a transmission lobe: spec_trans absent or 0)
+    PLTB_BSDF_PRINCIPLED = 6,    /* src/bsdfs/principled.cpp
                                                                  tex[0] = base_color, f[0] = eta (from `eta` or `specular`,
                                                                  principled.cpp:217-231), f[1] = roughness, f[2] = anisotropic,
                                                                  f[3] = metallic, f[4] = clearcoat, f[5] = clearcoat_gloss,
                                                                  f[6] = sheen, f[7] = sheen_tint, f[8] = flatness,
-                                                                 f[9] = spec_tint, f[10] = spec_trans (lobe weights only; the
-                                                                 refraction lobe itself is not on the path and the loader
-                                                                 rejects spec_trans != 0), u[0] = PLTB_PRINCIPLED_HAS_* bits,
+                                                                 f[9] = spec_tint, f[10] = spec_trans (the GGX refraction lobe,
+                                                                 principled.cpp:437-453,604-621,816-828; not under `twosided`),
+                                                                 u[0] = PLTB_PRINCIPLED_HAS_* bits,
                                                                  u[1..3] = float bits of main_specular / clearcoat /
                                                                  diffuse_reflectance _sampling_rate */
     PLTB_BSDF_ROUGHGRATING = 5   /* src/bsdfs/roughgrating.cpp   as roughconductor, plus f[3] = grating_angle,

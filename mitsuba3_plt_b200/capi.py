@@ -21,7 +21,8 @@ TEX_UNIFORM, TEX_SRGB, TEX_D65, TEX_REGULAR, TEX_IRREGULAR, TEX_BITMAP, TEX_BLAC
 TEXFLAG_RGB = 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = range(3)
 BSDF_NULL, BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_DIELECTRIC, BSDF_ROUGHCONDUCTOR, BSDF_ROUGHGRATING, BSDF_PRINCIPLED = range(7)
-PRINCIPLED_HAS = {"anisotropic": 1, "metallic": 2, "clearcoat": 4, "sheen": 8, "sheen_tint": 16, "flatness": 32, "spec_tint": 64}
+PRINCIPLED_HAS = {"anisotropic": 1, "metallic": 2, "clearcoat": 4, "sheen": 8, "sheen_tint": 16, "flatness": 32, "spec_tint": 64,
+                  "spec_trans": 128}
 BSDF_FLAG_TWOSIDED = 1
 MICROFACET_BECKMANN, MICROFACET_GGX = 0, 1
 SHAPE_MESH, SHAPE_SPHERE, SHAPE_RECTANGLE = range(3)

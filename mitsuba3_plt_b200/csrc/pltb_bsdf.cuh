@@ -9,6 +9,12 @@ namespace pltb {
 struct BSDFSampleOut { V3 wo; float pdf, eta; uint32_t type; S4 weight; float aux; /* roughgrating: sampled lobe intensity */ };
 
 PLTB_HD S4 conductor_F(const DeviceScene &sc, const pltb_bsdf &b, const S4 &wl, V2 uv, float cos_theta) {
+    if (b.tex[0] >= 0 && b.tex[1] >= 0) {
+        // spectrally and spatially flat eta and k (`uniform` spectra, the plugins' defaults 0 / 1 included): the four lanes would run
+        // the same operations on the same inputs -- one Fresnel evaluation instead of four
+        const pltb_texture &te = sc.textures[b.tex[0]], &tk = sc.textures[b.tex[1]];
+        if (te.type == PLTB_TEX_UNIFORM && tk.type == PLTB_TEX_UNIFORM) return s4(fresnel_conductor(cos_theta, te.p[0], tk.p[0]));
+    }
     S4 eta = tex_eval(sc, b.tex[0], wl, uv), k = tex_eval(sc, b.tex[1], wl, uv), F;
     for (int i = 0; i < 4; ++i) F.v[i] = fresnel_conductor(cos_theta, eta.v[i], k.v[i]);
     return F;
@@ -119,7 +125,7 @@ PLTB_HD void rough_eval_pdf(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2
     if (!active) return;
     Microfacet distr = make_mf(b);
     float D = distr.eval(H);
-    active = D != 0.f;
+    if (!(D != 0.f)) return;   // value and pdf stay 0: no need for G and the Fresnel factor (half of the diffracted directions)
     float g1 = distr.smith_g1(wi, H), G = g1 * distr.smith_g1(wo, H);
     float val = D * G / (4.f * cos_theta_i);
     S4 F = conductor_F(sc, b, wl, uv, dot(wi, H));

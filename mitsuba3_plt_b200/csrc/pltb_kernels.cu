@@ -26,6 +26,22 @@ struct DevPush {
         base = __shfl_sync(peers, base, leader);
         list[base + __popc(peers & ((1u << lane) - 1u))] = entry;
     }
+    // The same append in two halves, so that a stage which appends to two lists (k_shade: NEE queue and live list) has both
+    // reservations in flight at once and spends the round trips of the atomics on its record stores instead of waiting twice.
+    // begin() and finish() of one ticket must sit under the same predicate (the peers meet again in finish()).
+    struct Ticket { unsigned peers; uint32_t base; int leader; };
+    __device__ __forceinline__ Ticket begin(uint32_t *count) const {
+        Ticket t;
+        t.peers = __match_any_sync(__activemask(), (unsigned long long) count);
+        t.leader = __ffs(t.peers) - 1;
+        t.base = 0;
+        if ((int) (threadIdx.x & 31) == t.leader) t.base = atomicAdd(count, (uint32_t) __popc(t.peers));
+        return t;
+    }
+    __device__ __forceinline__ void finish(uint32_t *list, const Ticket &t, uint32_t entry) const {
+        const uint32_t base = __shfl_sync(t.peers, t.base, t.leader);
+        list[base + __popc(t.peers & ((1u << (threadIdx.x & 31)) - 1u))] = entry;
+    }
 };
 
 struct DevFilm {
@@ -160,8 +176,11 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
 
 // (register budget: ptxas settles on 128 registers = 4 blocks/SM; forcing 3, 5, 6 or 8 blocks/SM measured 495 / 477 / 490 / 466 ms
 // against 462 ms for the whole sample phase, profiles/r01_ab_shade_occupancy.txt)
+#ifndef PLTB_SHADE_MINBLOCKS
+#define PLTB_SHADE_MINBLOCKS 5   // blocks of 128 threads per SM the register allocation must allow: 5 = 96 registers (4: 1789, 5: 1804, 6: 1792 Msamples/s on C2)
+#endif
 template <int Class>
-__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+__global__ void __launch_bounds__(128, PLTB_SHADE_MINBLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
     const uint32_t n = st.counts[cnt_shade(bounce, Class)];
     const uint32_t *list = st.shade_q[Class];

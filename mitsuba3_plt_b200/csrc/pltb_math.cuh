@@ -202,7 +202,10 @@ PLTB_HD float dr_erfinv(float x) {
 // for the quadrature ONLY where the value does not scale radiance: DiffractionGrating::sample_lobe's selection weights and the
 // sampled lobe's intensity in RoughGrating::wbsdf_sample, which enters the sample-phase throughput (Russian roulette, the
 // `alpha != 0` test) but never the replayed one.  |table - float32 rule| <~ 2e-6 absolute (the rule's own float32 rounding).
-constexpr int kBesselTabOrders = 4, kBesselTabInvH = 64, kBesselTabN = 4096;
+#ifndef PLTB_BESSEL_INVH
+#define PLTB_BESSEL_INVH 16   // segments per unit of x: interpolation error (h^4 / 384) |f''''| <= 4e-8; 64 KB, L1-resident
+#endif
+constexpr int kBesselTabOrders = 4, kBesselTabInvH = PLTB_BESSEL_INVH, kBesselTabN = 64 * PLTB_BESSEL_INVH;
 constexpr float kBesselTabMax = (float) kBesselTabN / (float) kBesselTabInvH;   // 64
 #if !defined(__CUDACC__)
 struct pltb_host_float4;                      // host builds (tests/hostcheck) never have a table

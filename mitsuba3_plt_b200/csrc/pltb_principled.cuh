@@ -71,7 +71,7 @@ struct Principled {
         m.au = fmaxf(m.au, 1e-4f); m.av = fmaxf(m.av, 1e-4f);   // MicrofacetDistribution::configure (microfacet.h:169-173)
         return m;
     }
-    // lobe selection probabilities with spec_trans == 0 (principled.cpp:376-399 == :760-786)
+    // lobe selection probabilities (principled.cpp:376-399 == :760-786)
     PLTB_HD void probs(float F_spec, bool front, float &p_spec, float &p_cc, float &p_diff, float &p_trans) const {
         float brdf = (1.0f - metallic) * (1.0f - spec_trans), bsdf = has_spec_trans ? (1.0f - metallic) * spec_trans : 0.0f;
         float ps = front ? spec_srate * (1.0f - bsdf * (1.0f - F_spec)) : F_spec;
@@ -107,7 +107,7 @@ PLTB_HD float smith_ggx1(V3 v, V3 wh, float alpha) {   // principledhelpers.h:73
     return result;
 }
 
-// Principled::eval (principled.cpp:488-712), spec_trans == 0
+// Principled::eval (principled.cpp:488-712)
 PLTB_NI S4 principled_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, V3 wo) {
     Principled P; P.init(b);
     const float cos_theta_i = wi.z;
@@ -115,8 +115,8 @@ PLTB_NI S4 principled_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 
     const S4 base_color = tex_eval(sc, b.tex[0], wl, uv);
     const float brdf = (1.0f - P.metallic) * (1.0f - P.spec_trans), bsdf = (1.0f - P.metallic) * P.spec_trans;
     const float cos_theta_o = wo.z;
-    const bool reflect_ = cos_theta_i * cos_theta_o > 0.0f, front_side = cos_theta_i > 0.0f;
-    const float inv_eta = rcp(P.eta), eta_path = front_side ? P.eta : inv_eta;
+    const bool reflect_ = cos_theta_i * cos_theta_o > 0.0f, refract_ = cos_theta_i * cos_theta_o < 0.0f, front_side = cos_theta_i > 0.0f;
+    const float inv_eta = rcp(P.eta), eta_path = front_side ? P.eta : inv_eta, inv_eta_path = front_side ? inv_eta : P.eta;
     const Microfacet spec_dist = P.spec_distr();
     V3 wh = normalize(wi + wo * (reflect_ ? 1.0f : eta_path));
     wh = mk3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
@@ -125,6 +125,8 @@ PLTB_NI S4 principled_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 
     const bool reflection_compat = mac_mic_compatibility(wh, wi, wo, cos_theta_i, true);
     const bool spec_reflect_active = reflect_ && reflection_compat && F_spec_dielectric > 0.0f;
     const bool clearcoat_active = P.has_clearcoat && P.clearcoat > 0.0f && reflect_ && reflection_compat && front_side;
+    const bool spec_trans_active = P.has_spec_trans && bsdf > 0.0f && refract_ && mac_mic_compatibility(wh, wi, wo, cos_theta_i, false) &&
+                                   F_spec_dielectric < 1.0f;
     const bool diffuse_active = brdf > 0.0f && reflect_ && front_side;
     const bool sheen_active = P.has_sheen && P.sheen > 0.0f && reflect_ && (1.0f - P.metallic > 0.0f) && front_side;
     const float D = spec_dist.eval(wh), G = spec_dist.G(wi, wo, wh);
@@ -146,6 +148,12 @@ PLTB_NI S4 principled_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 
             float Fp = front_side ? F_front : bsdf * F_spec_dielectric;
             value.v[i] += Fp * D * G / (4.0f * fabsf(cos_theta_i));
         }
+    }
+    if (spec_trans_active) {   // main specular transmission (principled.cpp:604-621), TransportMode::Radiance: scale = inv_eta_path^2
+        const float scale = sqr(inv_eta_path), dwi = dot(wi, wh), dwo = dot(wo, wh);
+        const float t = fabsf((scale * (1.0f - F_spec_dielectric) * D * G * eta_path * eta_path * dwi * dwo) /
+                              (cos_theta_i * sqr(dwi + eta_path * dwo)));
+        for (int i = 0; i < 4; ++i) value.v[i] += sqrtf(base_color.v[i]) * bsdf * t;
     }
     if (clearcoat_active) {
         const float Fcc = calc_schlick(0.04f, dot(wi, wh), P.eta);
@@ -187,26 +195,34 @@ PLTB_NI S4 principled_eval(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 
     return value;
 }
 
-// Principled::pdf (principled.cpp:714-834), spec_trans == 0
+// Principled::pdf (principled.cpp:714-834)
 PLTB_NI float principled_pdf(const pltb_bsdf &b, V3 wi, V3 wo) {
     Principled P; P.init(b);
     const float cos_theta_i = wi.z;
     if (!(cos_theta_i != 0.0f)) return 0.0f;
     const bool front_side = cos_theta_i > 0.0f;
     const float eta_path = front_side ? P.eta : rcp(P.eta), cos_theta_o = wo.z;
-    const bool reflect_ = cos_theta_i * cos_theta_o > 0.0f;
+    const bool reflect_ = cos_theta_i * cos_theta_o > 0.0f, refract_ = cos_theta_i * cos_theta_o < 0.0f;
     V3 wh = normalize(wi + wo * (reflect_ ? 1.0f : eta_path));
     wh = mk3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
     const Microfacet spec_distr = P.spec_distr();
     const FresnelResult fr = fresnel(dot(wi, wh), P.eta);
     float p_spec, p_cc, p_diff, p_trans;
     P.probs(fr.r, front_side, p_spec, p_cc, p_diff, p_trans);
-    const float dwh_dwo_abs = fabsf(rcp(4.0f * dot(wo, wh)));
+    float dwh_dwo_abs;   // different for reflection and transmission (principled.cpp:789-801)
+    if (P.has_spec_trans) {
+        const float dot_wi_h = dot(wi, wh), dot_wo_h = dot(wo, wh);
+        dwh_dwo_abs = fabsf(reflect_ ? rcp(4.0f * dot_wo_h) : (sqr(eta_path) * dot_wo_h) / sqr(dot_wi_h + eta_path * dot_wo_h));
+    } else {
+        dwh_dwo_abs = fabsf(rcp(4.0f * dot(wo, wh)));
+    }
     float pdf = 0.0f;
     const bool macmic = mac_mic_compatibility(wh, wi, wo, cos_theta_i, true) && reflect_;
     const V3 wi_s = mk3(mulsign(wi.x, cos_theta_i), mulsign(wi.y, cos_theta_i), mulsign(wi.z, cos_theta_i));
     if (macmic) pdf += p_spec * spec_distr.pdf(wi_s, wh) * dwh_dwo_abs;
     if (reflect_) pdf += p_diff * (kInvPi * wo.z);
+    if (P.has_spec_trans && mac_mic_compatibility(wh, wi, wo, cos_theta_i, false) && refract_)
+        pdf += p_trans * spec_distr.pdf(wi_s, wh) * dwh_dwo_abs;
     if (P.has_clearcoat) {
         GTR1 cc; cc.alpha = dr_lerp(0.1f, 0.001f, P.clearcoat_gloss);
         if (macmic) pdf += p_cc * cc.pdf(wh) * dwh_dwo_abs;
@@ -214,7 +230,7 @@ PLTB_NI float principled_pdf(const pltb_bsdf &b, V3 wi, V3 wo) {
     return pdf;
 }
 
-// Principled::sample (principled.cpp:330-486), spec_trans == 0
+// Principled::sample (principled.cpp:330-486)
 PLTB_HD void principled_sample(const DeviceScene &sc, const pltb_bsdf &b, V3 wi, V2 uv, const S4 &wl, float s1, V2 s2,
                                V3 &out_wo, float &out_pdf, float &out_eta, uint32_t &out_type, S4 &out_weight) {
     const float cos_theta_i = wi.z;
@@ -225,7 +241,8 @@ PLTB_HD void principled_sample(const DeviceScene &sc, const pltb_bsdf &b, V3 wi,
     const V3 wi_s = mk3(mulsign(wi.x, cos_theta_i), mulsign(wi.y, cos_theta_i), mulsign(wi.z, cos_theta_i));
     float mpdf; const V3 m_spec = spec_distr.sample(wi_s, s2, mpdf);
     const FresnelResult fr = fresnel(dot(wi, m_spec), P.eta);
-    bool active = front_side;   // (front_side || bsdf > 0) with bsdf == 0
+    const float bsdf = P.has_spec_trans ? (1.0f - P.metallic) * P.spec_trans : 0.0f;
+    bool active = front_side || bsdf > 0.0f;   // the inside case is only sampled when the BSDF major lobe is on
     float p_spec, p_cc, p_diff, p_trans;
     P.probs(fr.r, front_side, p_spec, p_cc, p_diff, p_trans);
     float curr = 0.0f;
@@ -233,13 +250,20 @@ PLTB_HD void principled_sample(const DeviceScene &sc, const pltb_bsdf &b, V3 wi,
     curr += p_diff;
     const bool sample_clearcoat = P.has_clearcoat && active && s1 >= curr && s1 < curr + p_cc;
     curr += p_cc;
-    curr += p_trans;   // prob_spec_trans: 0 on this path (the loader rejects spec_trans != 0)
+    const bool sample_spec_trans = P.has_spec_trans && active && s1 >= curr && s1 < curr + p_trans;
+    curr += p_trans;
     const bool sample_spec_reflect = active && s1 >= curr;
     out_eta = 1.0f;
     if (sample_spec_reflect) {
         V3 wo = reflect(wi, m_spec);
         out_wo = wo; out_type = F_GlossyReflection;
         active = active && mac_mic_compatibility(m_spec, wi, wo, cos_theta_i, true) && cos_theta_i * wo.z > 0.0f;
+    }
+    if (sample_spec_trans) {   // refract(wi, m, cos_theta_t, eta_ti) (fresnel.h:310-314)
+        const float c = fmadd(dot(wi, m_spec), fr.eta_ti, fr.cos_theta_t);
+        V3 wo = mk3(fmsub(m_spec.x, c, wi.x * fr.eta_ti), fmsub(m_spec.y, c, wi.y * fr.eta_ti), fmsub(m_spec.z, c, wi.z * fr.eta_ti));
+        out_wo = wo; out_type = F_GlossyTransmission; out_eta = fr.eta_it;
+        active = active && mac_mic_compatibility(m_spec, wi, wo, cos_theta_i, false) && cos_theta_i * wo.z < 0.0f;
     }
     if (sample_clearcoat) {
         GTR1 cc; cc.alpha = dr_lerp(0.1f, 0.001f, P.clearcoat_gloss);

@@ -9,7 +9,7 @@
 namespace pltb {
 
 enum : uint32_t {
-    F_Null = 0x1, F_DiffuseReflection = 0x2, F_GlossyReflection = 0x8, F_DeltaReflection = 0x20,
+    F_Null = 0x1, F_DiffuseReflection = 0x2, F_GlossyReflection = 0x8, F_GlossyTransmission = 0x10, F_DeltaReflection = 0x20,
     F_DeltaTransmission = 0x40, F_Smooth = 0x2 | 0x4 | 0x8 | 0x10, F_Delta = 0x1 | 0x20 | 0x40
 };
 

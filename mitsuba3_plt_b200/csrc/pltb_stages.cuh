@@ -200,6 +200,9 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 
     // bounce record
     const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
+    typename Push::Ticket t_nee, t_live;   // both list reservations are issued before the record stores (DevPush::begin)
+    if (nee) t_nee = push.begin(st.counts + cnt_nee(Class));
+    if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
     st.v_em[r] = s4_to_f4(em);
     if (nee) {
         st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
@@ -209,7 +212,6 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.v_alpha[r] = s4_to_f4(ai);
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
         st.v_wiz_shape[r] = ws;
-        push(st.queue[Class], st.counts + cnt_nee(Class), local | (i << 27));
     } else {
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
@@ -221,7 +223,10 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.p_alpha[local] = s4_to_f4(alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = delta ? 1u : 0u;
-        push(st.live, st.counts + cnt_live(i + 1), local);
+    }
+    if (nee) push.finish(st.queue[Class], t_nee, local | (i << 27));
+    if (active_next) {
+        push.finish(st.live, t_live, local);
     } else {
         st.n_vertices[local] = i + 1;
     }

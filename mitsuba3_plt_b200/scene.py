@@ -512,11 +512,13 @@ class FlatScene:
                     return False
                 v = inner[name]
                 return not (isinstance(v, float) and v == 0.0)
-            if get_flag("spec_trans"):
-                raise RuntimeError("principled: a transmission lobe (spec_trans != 0) is outside the plt hot path")
+            has_trans = get_flag("spec_trans")
+            if has_trans and flags & capi.BSDF_FLAG_TWOSIDED:
+                raise RuntimeError("twosided: only materials without a transmission component can be nested!")   # twosided.cpp:52-57
             b.tex[0] = self.texture(inner, "base_color", 0.5)
             b.f[1] = self.scalar(inner, "roughness", 0.5)
-            slots = {"anisotropic": 2, "metallic": 3, "clearcoat": 4, "sheen": 6, "sheen_tint": 7, "flatness": 8, "spec_tint": 9}
+            slots = {"anisotropic": 2, "metallic": 3, "clearcoat": 4, "sheen": 6, "sheen_tint": 7, "flatness": 8, "spec_tint": 9,
+                     "spec_trans": 10}
             flags = 0
             for name, slot in slots.items():
                 b.f[slot] = self.scalar(inner, name, 0.0)
@@ -531,8 +533,12 @@ class FlatScene:
                 raise RuntimeError('Specified an invalid index of refraction property, either use "eta" or "specular" !')
             if "eta" in inner:
                 b.f[0] = float(inner["eta"])
+                if has_trans and b.f[0] == 1.0:       # "m_eta = 1 is not plausible for transmission" (principled.cpp:222-223)
+                    b.f[0] = 1.001
             else:
                 specular = F32(inner.get("specular", 0.5))
+                if has_trans and specular == 0:        # principled.cpp:227-228
+                    specular = F32(1e-3)
                 b.f[0] = F32(2.0) * (F32(1.0) / (F32(1.0) - np.sqrt(F32(0.08) * specular, dtype=F32))) - F32(1.0)
         else:
             raise RuntimeError(f'Plugin "{t}" not found (bsdf outside the plt hot path)')

@@ -942,7 +942,7 @@ inline S4 conductor_F(const Scene &sc, const pltb_bsdf &b, const SI &si, float c
     return F;
 }
 
-/* ---- principled BSDF without a transmission lobe (src/bsdfs/principled.cpp, principledhelpers.h) ------------------ */
+/* ---- principled BSDF (src/bsdfs/principled.cpp, principledhelpers.h) ------------------ */
 inline float dr_lerp(float a, float b, float t) { return fmadd(b, t, fnmadd(a, t, a)); }
 inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 inline float schlick_weight(float cos_i) { /* principledhelpers.h:108-112 */
@@ -1036,7 +1036,7 @@ inline float smith_ggx1(V3 v, V3 wh, float alpha) { /* principledhelpers.h:73-93
     return result;
 }
 
-/* Principled::eval (principled.cpp:488-712), spec_trans == 0 */
+/* Principled::eval (principled.cpp:488-712) */
 S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     const Principled P(b);
     float cos_theta_i = si.wi.z;
@@ -1044,9 +1044,9 @@ S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     S4 base_color = tex_eval(sc, b.tex[0], si.wavelengths, si.uv);
     float brdf = (1.0f - P.metallic) * (1.0f - P.spec_trans), bsdf = (1.0f - P.metallic) * P.spec_trans;
     float cos_theta_o = wo.z;
-    bool reflect = cos_theta_i * cos_theta_o > 0.0f;
+    bool reflect = cos_theta_i * cos_theta_o > 0.0f, refract_ = cos_theta_i * cos_theta_o < 0.0f;
     bool front_side = cos_theta_i > 0.0f;
-    float inv_eta = rcp(P.eta), eta_path = front_side ? P.eta : inv_eta;
+    float inv_eta = rcp(P.eta), eta_path = front_side ? P.eta : inv_eta, inv_eta_path = front_side ? inv_eta : P.eta;
     Microfacet spec_dist = P.spec_distr();
     V3 wh = normalize(si.wi + wo * (reflect ? 1.0f : eta_path));
     wh = V3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
@@ -1055,6 +1055,8 @@ S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     bool reflection_compat = mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, true);
     bool spec_reflect_active = reflect && reflection_compat && F_spec_dielectric > 0.0f;
     bool clearcoat_active = P.has_clearcoat && P.clearcoat > 0.0f && reflect && reflection_compat && front_side;
+    bool spec_trans_active = P.has_spec_trans && bsdf > 0.0f && refract_ && mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, false) &&
+                             F_spec_dielectric < 1.0f;   /* principled.cpp:563-565 */
     bool diffuse_active = brdf > 0.0f && reflect && front_side;
     bool sheen_active = P.has_sheen && P.sheen > 0.0f && reflect && (1.0f - P.metallic > 0.0f) && front_side;
     float D = spec_dist.eval(wh), G = spec_dist.G(si.wi, wo, wh);
@@ -1079,6 +1081,12 @@ S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
             float Fp = front_side ? F_front : bsdf * F_spec_dielectric;
             value[i] += Fp * D * G / (4.0f * std::fabs(cos_theta_i));
         }
+    }
+    if (spec_trans_active) { /* main specular transmission, principled.cpp:604-621; ctx.mode == Radiance: scale = inv_eta_path^2 */
+        float scale = sqr(inv_eta_path), dwi = dot(si.wi, wh), dwo = dot(wo, wh);
+        float t = std::fabs((scale * (1.0f - F_spec_dielectric) * D * G * eta_path * eta_path * dwi * dwo) /
+                            (cos_theta_i * sqr(dwi + eta_path * dwo)));
+        for (int i = 0; i < 4; ++i) value[i] += std::sqrt(base_color[i]) * bsdf * t;
     }
     if (clearcoat_active) {
         float Fcc = calc_schlick(0.04f, dot(si.wi, wh), P.eta);
@@ -1120,26 +1128,34 @@ S4 principled_eval(const Scene &sc, const pltb_bsdf &b, const SI &si, V3 wo) {
     return value;
 }
 
-/* Principled::pdf (principled.cpp:714-834), spec_trans == 0 */
+/* Principled::pdf (principled.cpp:714-834) */
 float principled_pdf(const pltb_bsdf &b, const SI &si, V3 wo) {
     const Principled P(b);
     float cos_theta_i = si.wi.z;
     if (!(cos_theta_i != 0.0f)) return 0.0f;
     bool front_side = cos_theta_i > 0.0f;
     float eta_path = front_side ? P.eta : rcp(P.eta), cos_theta_o = wo.z;
-    bool reflect = cos_theta_i * cos_theta_o > 0.0f;
+    bool reflect = cos_theta_i * cos_theta_o > 0.0f, refract_ = cos_theta_i * cos_theta_o < 0.0f;
     V3 wh = normalize(si.wi + wo * (reflect ? 1.0f : eta_path));
     wh = V3(mulsign(wh.x, wh.z), mulsign(wh.y, wh.z), mulsign(wh.z, wh.z));
     Microfacet spec_distr = P.spec_distr();
     FresnelResult fr = fresnel(dot(si.wi, wh), P.eta);
     float p_spec, p_cc, p_diff, p_trans;
     P.probs(fr.r, p_spec, p_cc, p_diff, front_side, p_trans);
-    float dwh_dwo_abs = std::fabs(rcp(4.0f * dot(wo, wh)));
+    float dwh_dwo_abs; /* principled.cpp:789-801 */
+    if (P.has_spec_trans) {
+        float dot_wi_h = dot(si.wi, wh), dot_wo_h = dot(wo, wh);
+        dwh_dwo_abs = std::fabs(reflect ? rcp(4.0f * dot_wo_h) : (sqr(eta_path) * dot_wo_h) / sqr(dot_wi_h + eta_path * dot_wo_h));
+    } else {
+        dwh_dwo_abs = std::fabs(rcp(4.0f * dot(wo, wh)));
+    }
     float pdf = 0.0f;
     bool macmic = mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, true) && reflect;
     V3 wi_s(mulsign(si.wi.x, cos_theta_i), mulsign(si.wi.y, cos_theta_i), mulsign(si.wi.z, cos_theta_i));
     if (macmic) pdf += p_spec * spec_distr.pdf(wi_s, wh) * dwh_dwo_abs;
     if (reflect) pdf += p_diff * (kInvPi * wo.z);
+    if (P.has_spec_trans && mac_mic_compatibility(wh, si.wi, wo, cos_theta_i, false) && refract_) /* :816-828 */
+        pdf += p_trans * spec_distr.pdf(wi_s, wh) * dwh_dwo_abs;
     if (P.has_clearcoat) {
         GTR1 cc{ dr_lerp(0.1f, 0.001f, P.clearcoat_gloss) };
         if (macmic) pdf += p_cc * cc.pdf(wh) * dwh_dwo_abs;
@@ -1183,7 +1199,7 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
             o.weight = w;
             return o;
         }
-        case PLTB_BSDF_PRINCIPLED: { /* src/bsdfs/principled.cpp:330-486, spec_trans == 0 */
+        case PLTB_BSDF_PRINCIPLED: { /* src/bsdfs/principled.cpp:330-486 */
             if (!(cos_theta_i != 0.0f)) return o;
             const Principled P(b);
             bool front_side = cos_theta_i > 0.0f;
@@ -1191,7 +1207,8 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
             V3 wi_s(mulsign(si.wi.x, cos_theta_i), mulsign(si.wi.y, cos_theta_i), mulsign(si.wi.z, cos_theta_i));
             float mpdf; V3 m_spec = spec_distr.sample(wi_s, s2, mpdf);
             FresnelResult fr = fresnel(dot(si.wi, m_spec), P.eta);
-            bool active = front_side;   /* (front_side || bsdf > 0) with bsdf == 0 */
+            float bsdf = P.has_spec_trans ? (1.0f - P.metallic) * P.spec_trans : 0.0f;
+            bool active = front_side || bsdf > 0.0f;   /* principled.cpp:370-372 */
             float p_spec, p_cc, p_diff, p_trans;
             P.probs(fr.r, p_spec, p_cc, p_diff, front_side, p_trans);
             float curr = 0.0f;
@@ -1199,13 +1216,20 @@ SampleOut bsdf_sample_inner(const Scene &sc, const pltb_bsdf &b, const SI &si, f
             curr += p_diff;
             bool sample_clearcoat = P.has_clearcoat && active && s1 >= curr && s1 < curr + p_cc;
             curr += p_cc;
-            curr += p_trans;   /* prob_spec_trans: 0 on this path (the loader rejects spec_trans != 0) */
+            bool sample_spec_trans = P.has_spec_trans && active && s1 >= curr && s1 < curr + p_trans;
+            curr += p_trans;
             bool sample_spec_reflect = active && s1 >= curr;
             o.bs.eta = 1.0f;
             if (sample_spec_reflect) {
                 V3 wo = reflect(si.wi, m_spec);
                 o.bs.wo = wo; o.bs.type = F_GlossyReflection;
                 active = active && mac_mic_compatibility(m_spec, si.wi, wo, cos_theta_i, true) && cos_theta_i * wo.z > 0.0f;
+            }
+            if (sample_spec_trans) { /* :437-453; refract(wi, m, cos_theta_t, eta_ti), fresnel.h:310-314 */
+                float c = fmadd(dot(si.wi, m_spec), fr.eta_ti, fr.cos_theta_t);
+                V3 wo(fmsub(m_spec.x, c, si.wi.x * fr.eta_ti), fmsub(m_spec.y, c, si.wi.y * fr.eta_ti), fmsub(m_spec.z, c, si.wi.z * fr.eta_ti));
+                o.bs.wo = wo; o.bs.type = F_GlossyTransmission; o.bs.eta = fr.eta_it;
+                active = active && mac_mic_compatibility(m_spec, si.wi, wo, cos_theta_i, false) && cos_theta_i * wo.z < 0.0f;
             }
             if (sample_clearcoat) {
                 GTR1 cc{ dr_lerp(0.1f, 0.001f, P.clearcoat_gloss) };
@@ -2427,6 +2451,32 @@ void plt_oracle_bsdf_probe(const pltb_scene_desc *d, int32_t shape, const float 
     out[9] = so.bs.wo.x; out[10] = so.bs.wo.y; out[11] = so.bs.wo.z; out[12] = so.bs.pdf;
     for (int k = 0; k < 4; ++k) out[13 + k] = so.weight[k];
     out[17] = so.bs.eta;
+}
+/* batched forms of the probe for statistical tests (the reference's chi^2 tests, src/bsdfs/tests/test_principled.py:60-121):
+ * sample: u = n x {sample1, sample2.x, sample2.y} -> out = n x {wo[3], pdf, weight[0]};  pdf: wo = n x 3 -> out = n x {pdf, eval[0]} */
+static SI probe_si(int32_t shape, const float *wi, const float *uv, const float *wl4) {
+    SI si; si.t = 1.f; si.shape = shape; si.wi = V3(wi[0], wi[1], wi[2]); si.uv = V2{ uv[0], uv[1] };
+    si.n = V3(0.f, 0.f, 1.f); si.sh.n = si.n; si.sh.s = V3(1.f, 0.f, 0.f); si.sh.t = V3(0.f, 1.f, 0.f);
+    for (int k = 0; k < 4; ++k) si.wavelengths[k] = wl4[k];
+    return si;
+}
+void plt_oracle_bsdf_sample_batch(const pltb_scene_desc *d, int32_t shape, const float *wi, const float *uv, const float *wl4, uint64_t n,
+                                  const float *u, float *out) {
+    Scene sc; prepare_scene(sc, d);
+    const SI si = probe_si(shape, wi, uv, wl4);
+    for (uint64_t i = 0; i < n; ++i) {
+        const SampleOut so = wbsdf_sample(sc, si, u[3 * i], V2{ u[3 * i + 1], u[3 * i + 2] }, V2{ 0.5f, 0.5f });
+        out[5 * i] = so.bs.wo.x; out[5 * i + 1] = so.bs.wo.y; out[5 * i + 2] = so.bs.wo.z; out[5 * i + 3] = so.bs.pdf; out[5 * i + 4] = so.weight[0];
+    }
+}
+void plt_oracle_bsdf_pdf_batch(const pltb_scene_desc *d, int32_t shape, const float *wi, const float *uv, const float *wl4, uint64_t n,
+                               const float *wo, float *out) {
+    Scene sc; prepare_scene(sc, d);
+    const SI si = probe_si(shape, wi, uv, wl4);
+    for (uint64_t i = 0; i < n; ++i) {
+        const V3 w(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
+        out[2 * i] = wbsdf_pdf(sc, si, w); out[2 * i + 1] = wbsdf_eval(sc, si, w)[0];
+    }
 }
 /* Emitter sampling from a reference point (Scene::sample_emitter_direction without the visibility test, area.cpp:116-208):
  * out = { ds.d[3], ds.pdf, ds.dist, ds.p[3], ds.n[3], pdf_direction(ds), eval_direction[4], eval(wi = -d)[4], eval(wi = +d)[4] } */

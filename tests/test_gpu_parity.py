@@ -233,3 +233,43 @@ def test_strip_splat_equals_per_tap_atomics(mi, integ, monkeypatch):
         fin = np.isfinite(a).all(-1) & np.isfinite(b).all(-1)
         assert (np.isfinite(a).all(-1) == np.isfinite(b).all(-1)).all()
         np.testing.assert_allclose(a[fin], b[fin], rtol=2e-4, atol=1e-4)
+
+
+def glass_scene(mi, res=64):
+    """a rough refractive `principled` sphere and slab (spec_trans lobe, principled.cpp:437-453,604-621,816-828; outside and inside
+    incidence, eta > 1) over a diffuse floor under an area light"""
+    T = mi.Transform
+    glass = {"type": "principled", "base_color": {"type": "rgb", "value": [0.8, 0.9, 0.7]}, "roughness": 0.35, "spec_trans": 0.8,
+             "eta": 1.45, "clearcoat": 0.3, "metallic": 0.1, "anisotropic": 0.2}
+    return mi.load_dict({
+        "type": "scene",
+        "sensor": {"type": "perspective", "fov": 40, "to_world": T().look_at([0, 1.2, 4.5], [0, 0.6, 0], [0, 1, 0]),
+                   "film": {"type": "hdrfilm", "width": res, "height": res}},
+        "floor": {"type": "rectangle", "to_world": T().rotate([1, 0, 0], -90).scale([4, 4, 1]),
+                  "bsdf": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.6, 0.5, 0.4]}}},
+        "ball": {"type": "sphere", "center": [-0.7, 0.7, 0], "radius": 0.7, "bsdf": glass},
+        # (the slab floats: a face coplanar with the floor would make closest hits depend on traversal order)
+        "slab": {"type": "cube", "to_world": T().translate([0.9, 0.75, 0.2]).rotate([0, 1, 0], 20).scale([0.5, 0.6, 0.08]), "bsdf": glass},
+        "light": {"type": "rectangle", "to_world": T().translate([0, 3.0, 0]).rotate([1, 0, 0], 90).scale([1.0, 1.0, 1]),
+                  "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [12, 12, 12]}}}})
+
+
+def test_principled_transmission(mi, oracle, integ):
+    sc = glass_scene(mi)
+    dump = {}
+    img = integ.render(sc, spp=16, seed=5, dump=dump)
+    ref = oracle.render(sc.flat, 16, seed=5, dump=True)
+    frac = sample_agreement(dump["radiance"], ref["radiance"])
+    assert frac >= MIN_FRACTION, f"principled glass: only {frac * 100:.4f}% of samples within 1e-4"
+    ray_count_agreement("glass", dump["n_rays"], ref["n_rays"])
+    assert ref["stats"]["vertices"] > 1.5 * ref["stats"]["samples"] * 0.3      # paths do go through the glass
+    rmse, mism = relative_mse(img, ref["image"])
+    assert rmse <= MAX_RMSE and mism <= max_finiteness_mismatch(img.shape[0] * img.shape[1]), (rmse, mism)
+    try:   # polarized variant: principled stays a depolarizer (principled.cpp:708)
+        mi.set_variant("cuda_ad_spectral_polarized")
+        dump = {}
+        integ.render(sc, spp=8, seed=6, dump=dump)
+        refp = oracle.render(sc.flat, 8, seed=6, dump=True, polarized=True)
+        assert sample_agreement(dump["radiance"], refp["radiance"]) >= MIN_FRACTION
+    finally:
+        mi.set_variant("cuda_spectral")

@@ -40,7 +40,7 @@ def short(name):
     # material class = BSDF plugin type (include/pltb.h): 5 = roughgrating; "--per-class" keeps one row per class
     names = {"0": "null", "1": "diffuse", "2": "delta", "3": "dielectric", "4": "roughconductor", "5": "grating", "6": "principled"}
     if k in ("k_shade", "k_nee_post", "k_shade_pol", "k_nee_post_pol"):
-        c = re.sub(r"\D", "", t or "")
+        c = re.sub(r"\D", "", (t or "").split(",")[0])   # first template argument (k_nee_post<class, rgb>)
         if "--per-class" in sys.argv: return f"{k}<{names.get(c, c)}>"
         return f"{k}<grating>" if c == "5" else f"{k}<other>"
     if k == "k_trace": return "k_trace<shadow>" if t.startswith("1") or t.startswith("true") else "k_trace"

@@ -8,11 +8,12 @@ utilisation, DRAM bytes and GB/s, L1/L2 hit rates, active lanes) and, optionally
 {kernel: {"dram_bytes_per_launch": ..}} which bench.py reports as `roofline.traffic`."""
 import collections, csv, gzip, json, re, sys
 
-NAMES = [(r"k_raygen", "k_raygen"), (r"k_shade<1>|k_shade<\(int\)1>", "k_shade<grating>"),
-         (r"k_shade<0>|k_shade<\(int\)0>", "k_shade<other>"), (r"k_trace<0>|k_trace<\(bool\)0>|k_trace<false>", "k_trace"),
+# material classes are BSDF plugin types (PLTB_BSDF_*): 5 = roughgrating, everything else is reported as "other" (as bench.py does)
+NAMES = [(r"k_raygen", "k_raygen"), (r"k_shade(_pol)?<\(int\)5>|k_shade(_pol)?<5>", "k_shade<grating>"),
+         (r"k_shade(_pol)?<", "k_shade<other>"), (r"k_trace<0>|k_trace<\(bool\)0>|k_trace<false>", "k_trace"),
          (r"k_trace<1>|k_trace<\(bool\)1>|k_trace<true>", "k_trace<shadow>"), (r"k_classify", "k_classify"),
-         (r"k_nee_light", "k_nee_light"), (r"k_nee_post<0>|k_nee_post<\(int\)0>", "k_nee_post<other>"),
-         (r"k_nee_post<1>|k_nee_post<\(int\)1>", "k_nee_post<grating>"), (r"k_nee_eval", "k_nee_eval"),
+         (r"k_nee_light", "k_nee_light"), (r"k_nee_post(_pol)?<\(int\)5|k_nee_post(_pol)?<5", "k_nee_post<grating>"),
+         (r"k_nee_post(_pol)?<", "k_nee_post<other>"), (r"k_nee_eval", "k_nee_eval"),
          (r"k_gather", "k_gather"), (r"k_splat", "k_splat"), (r"k_develop", "k_develop")]
 COLS = {"t": "gpu__time_duration.sum", "rd": "dram__bytes_read.sum", "wr": "dram__bytes_write.sum",
         "issue": "smsp__issue_active.avg.pct_of_peak_sustained_active",
@@ -59,7 +60,8 @@ def main():
                      f"{a['alu'] / t:6.1f} {a['xu'] / t:6.1f} {a['lanes'] / t:6.1f} {a['occ'] / t:5.1f} {int(a['regs']):5d} {mb:8.1f} "
                      f"{mb / t * 1e3:7.1f} {a['l1'] / t:7.1f} {a['l2'] / t:7.1f}")
         traffic[name] = {"dram_bytes_per_launch": round((a["rd"] + a["wr"]) / a["n"]), "launches_in_capture": int(a["n"]),
-                         "avg_launch_us": round(a["t"] / a["n"], 2)}
+                         "avg_launch_us": round(a["t"] / a["n"], 2), "issue_slots_busy_pct": round(a["issue"] / t, 1),
+                         "active_lanes": round(a["lanes"] / t, 1), "occupancy_pct": round(a["occ"] / t, 1), "registers": int(a["regs"])}
     open(out, "w").write("\n".join(lines) + "\n")
     print("\n".join(lines))
     if len(sys.argv) > 3:
