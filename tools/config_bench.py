@@ -13,6 +13,7 @@ import oracle_lib
 ap = argparse.ArgumentParser()
 ap.add_argument("--cpu-seconds", type=float, default=6.0)
 ap.add_argument("--only", default="")
+ap.add_argument("--profile", action="store_true", help="add per-kernel device times (a second, event-bracketed render)")
 args = ap.parse_args()
 
 CONFIGS = [  # id, builtin scene, resx, resy, spp, note    (ids ending in "pol": polarized spectral variant + `stokes` wrapper, 8f f1)
@@ -22,6 +23,9 @@ CONFIGS = [  # id, builtin scene, resx, resy, spp, note    (ids ending in "pol":
                                     "(params.json: 1.654 min on the authors' GPU, JIT included)"),
     ("C2pol", "cbox-grating", 1024, 1024, 128, "scenes/cbox-grating 1024x1024, 128 spp, stokes{plt}, polarized"),
     ("C2", "cbox-grating", 1024, 1024, 1024, "scenes/cbox-grating 1024x1024, 1024 spp"),
+    ("C2rgb", "cbox-grating", 1024, 1024, 256, "scenes/cbox-grating 1024x1024, 256 spp, cuda_ad_rgb (RGB fallback of roughgrating, 8f f2)"),
+    ("Grgbpol", "gratings", 800, 600, 8192, "scenes/gratings 800x600, 8192 spp, stokes{plt}, cuda_ad_rgb_polarized: the reference's published "
+                                         "results/gratings/rgb/period=0.6 (params.json: 12.93 min on the authors' GPU, JIT included)"),
     ("C3", "spectrograph:bbody_3000", 1, 1, 1 << 20, "spectrograph, 150 sensors x 2^20 spp (largest row of synthetic-times.csv)"),
     ("C3p", "spectrograph:bbody_3000", 1, 1, 10_000_000, "spectrograph prior pass, 150 sensors x 1e7 spp"),
     ("C4", "veach-mis", 1920, 1080, 4096, "scenes/veach-mis 1920x1080, 4096 spp (2 sub-renders)"),
@@ -44,8 +48,8 @@ def oracle_rate(sc, spp, W, H, pol=False):
 for cid, name, rx, ry, spp, note in CONFIGS:
     if only and cid not in only:
         continue
-    pol = cid.endswith("pol")
-    mi.set_variant("cuda_ad_spectral_polarized" if pol else "cuda_spectral")
+    pol, rgb = cid.endswith("pol"), "rgb" in cid
+    mi.set_variant(("cuda_ad_rgb" if rgb else "cuda_ad_spectral") + ("_polarized" if pol else ""))
     it = mi.load_dict({"type": "stokes", "nested": {"type": "plt", "max_depth": 7, "rr_depth": 50}} if pol else
                       {"type": "plt", "max_depth": 7, "rr_depth": 50})
     sc = scenes.load(name, resx=rx, resy=ry)
@@ -57,8 +61,12 @@ for cid, name, rx, ry, spp, note in CONFIGS:
     wall = time.perf_counter() - t0
     st = it.last_stats
     ms = st["ms_total"]
-    cpu_ms, cpu_mr, n = oracle_rate(sc, spp, W, H, pol)
-    print(json.dumps({"config": cid, "workload": note, "film": [W, H], "spp": spp, "samples": st["samples"],
+    cpu_ms, cpu_mr, n = oracle_rate(sc, spp, W, H, pol) if not args.profile else (0.0, 0.0, 0)
+    kern = None
+    if args.profile:
+        it.render(sc, spp=spp, seed=0, profile=True, download=False)
+        kern = {k: (round(v["ms"], 2), v["launches"]) for k, v in it.last_stats["kernels"].items() if v["launches"]}
+    print(json.dumps({"config": cid, "kernels_ms_launches": kern, "workload": note, "film": [W, H], "spp": spp, "samples": st["samples"],
                       "gpu_ms": round(ms, 3), "gpu_wall_ms": round(wall * 1e3, 3),
                       "gpu_msamples_per_s": round(st["samples"] / ms / 1e3, 2),
                       "gpu_mrays_per_s": round((st["closest_rays"] + st["shadow_rays"]) / ms / 1e3, 2),
