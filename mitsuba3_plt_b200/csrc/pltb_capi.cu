@@ -543,7 +543,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         launch_splat(dev_scene, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
-        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized ? 1 : 0) + 1 + (do_splat ? 1 : 0);
+        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized && !rgb ? 2 : 0) + 1 + (do_splat ? 1 : 0);   // grating: + k_nee_scan, k_nee_eval
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0

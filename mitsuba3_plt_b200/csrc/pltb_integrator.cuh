@@ -259,7 +259,8 @@ struct PassState {
                                    // classes the scene does not contain
     uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: entry = sample_local | depth << 27
     uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee_post<1> -> k_nee_eval)
-    uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>)
+    uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>); after
+                               // the shadow trace the array is reused as the scan list of k_nee_post<grating> (counts[kCntScan])
     // counters, zeroed once per pass (cnt_* below index them)
     uint32_t *counts;
     // statistics
@@ -275,6 +276,7 @@ PLTB_HD int cnt_cursor(uint32_t i) { return kCountsStride * (int) i + 1; }
 PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCountsStride * (int) i + 2 + (int) c; }
 PLTB_HD int cnt_nee(uint32_t c) { return kCountsNee + (int) c; }
 constexpr int kCntEval = kCountsNee + kClasses, kCntShadow = kCountsNee + kClasses + 1, kCntShadowCursor = kCountsNee + kClasses + 2;
+constexpr int kCntScan = kCountsNee + kClasses + 3;   // roughgrating NEE items whose lobe windows have to be scanned (k_nee_post<grating> -> k_nee_scan)
 
 struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;

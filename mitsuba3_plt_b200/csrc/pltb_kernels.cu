@@ -224,65 +224,27 @@ __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ Devic
     flush_counters(cnt, st.counters);
 }
 
-// Class 1 (roughgrating): only the lit, well-formed items (about a third on cbox-grating) run the lobe-window scan, so with one item
-// per thread the scan runs at ~10 of 32 lanes.  The block therefore lists those items in shared memory and its first threads scan
-// them densely; every thread then picks up the answer for its own item (queue order and results unchanged; same function on the
-// same inputs, only on another thread).  Measured on cbox-grating 1024 spp: k_nee_post<grating> 53.6 -> 48.6 ms per 2^30 samples,
-// 1724 -> 1738 Msamples/s (gpurun_out/ab4.log, summarised in profiles/r01_ab_neepost_bvhleaf.txt).  -DPLTB_NEEPOST_DIRECT
-// restores the one-item-per-thread form.  The barriers inside the functor need a block-uniform loop and ONE call site that
-// every thread reaches (a first version that called it from two branches deadlocked on the tail block).
-#ifndef PLTB_NEEPOST_DIRECT
-struct ScanItem { const pltb_bsdf *b; float wi[3], wo[3], uv[2], wl[4]; };
-struct GratingInsideBlock {
-    ScanItem *items; uint32_t *n_items; uint8_t *flag;
-    __device__ bool operator()(bool want, const pltb_bsdf *b, V3 wi_f, V3 wo_f, V2 uv, const S4 &wl) const {
-        if (threadIdx.x == 0) *n_items = 0;
-        __syncthreads();
-        uint32_t slot = 0;
-        if (want) {
-            slot = atomicAdd(n_items, 1u);
-            ScanItem &it = items[slot];
-            it.b = b; it.wi[0] = wi_f.x; it.wi[1] = wi_f.y; it.wi[2] = wi_f.z; it.wo[0] = wo_f.x; it.wo[1] = wo_f.y; it.wo[2] = wo_f.z;
-            it.uv[0] = uv.x; it.uv[1] = uv.y;
-            for (int i = 0; i < 4; ++i) it.wl[i] = wl.v[i];
-        }
-        __syncthreads();
-        if (threadIdx.x < *n_items) {
-            const ScanItem &it = items[threadIdx.x];
-            S4 w; for (int i = 0; i < 4; ++i) w.v[i] = it.wl[i];
-            flag[threadIdx.x] = GratingInsideDirect()(true, it.b, mk3(it.wi[0], it.wi[1], it.wi[2]), mk3(it.wo[0], it.wo[1], it.wo[2]),
-                                                      mk2(it.uv[0], it.uv[1]), w);
-        }
-        __syncthreads();
-        return want && flag[slot];
-    }
-};
-#endif
-
+// solve_replay_NEE's BSDF half per material class.  roughgrating (not Rgb): this kernel finishes the unlit / malformed items and
+// lists the lit ones in the scan list (stage_nee_post<kNeeFilter>); k_nee_scan walks that list densely, k_nee_eval the items inside a window.
+// (Measured before: scan inside this kernel, one item per thread 53.6 ms per 2^30 samples on cbox-grating; block-level hand-over
+// of the lit items to dense threads 47.2 ms with 29 % of the warp samples at its barrier; this form: see profiles/r02_ab_session16.txt)
 template <int Class, bool Rgb>
 __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc,
                                                                       const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[cnt_nee(Class)];
     const uint32_t *queue = st.queue[Class];
     DevPush push;
-#ifndef PLTB_NEEPOST_DIRECT
-    if (Class == PLTB_BSDF_ROUGHGRATING && !Rgb) {
-        __shared__ ScanItem items[128];
-        __shared__ uint32_t n_items;
-        __shared__ uint8_t flag[128];
-        GratingInsideBlock inside{ items, &n_items, flag };
-        for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {   // block-uniform trip count
-            const uint32_t e = base + threadIdx.x;
-            const bool valid = e < n;
-            stage_nee_post<Class, Rgb>(sc, st, valid ? queue[e] : 0u, valid, push, inside);
-        }
-        return;
-    }
-#endif
+    constexpr int kMode = (Class == PLTB_BSDF_ROUGHGRATING && !Rgb) ? kNeeFilter : kNeeFull;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post<Class, Rgb>(sc, st, queue[e], true, push, GratingInsideDirect());
+        stage_nee_post<Class, Rgb, kMode>(sc, st, queue[e], true, push, GratingInsideDirect());
 }
 
+__global__ void __launch_bounds__(128) k_nee_scan(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
+    const uint32_t n = st.counts[kCntScan];
+    DevPush push;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
+        stage_nee_post<PLTB_BSDF_ROUGHGRATING, false, kNeeScan>(sc, st, st.shadow_q[e], true, push, GratingInsideDirect());
+}
 __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
     const uint32_t n = st.counts[kCntEval];
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(st.counters + 6, (unsigned long long) n);
@@ -601,7 +563,10 @@ void launch_nee_light(const DeviceScene &sc, const PassState &st, uint32_t class
 void launch_nee_post(const DeviceScene &sc, const PassState &st, int cls, int grid, cudaStream_t s) {
     dispatch_class<LaunchNeePost>(cls, sc, st, grid, s);
     PLTB_AFTER(cls == PLTB_BSDF_ROUGHGRATING ? PLTB_K_NEE_POST_GRATING : PLTB_K_NEE_POST_OTHER);
-    if (cls == PLTB_BSDF_ROUGHGRATING && !st.pv_w && !sc.rgb) { k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL); }
+    if (cls == PLTB_BSDF_ROUGHGRATING && !st.pv_w && !sc.rgb) {
+        k_nee_scan<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_POST_GRATING);
+        k_nee_eval<<<grid, 128, 0, s>>>(sc, st); PLTB_AFTER(PLTB_K_NEE_EVAL);
+    }
 }
 void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &pp, float *accum, int do_splat, float *dump_wl,
                   float *dump_L, uint32_t *dump_rays, float *dump_stokes, int stokes, uint64_t dump_cap, cudaStream_t s) {

@@ -328,9 +328,17 @@ struct GratingInsideDirect {
     }
 };
 
-// `valid` is false for the tail threads of a block-uniform loop (k_nee_post<roughgrating>): they load nothing and only take part in
-// the barriers a block-level `inside_fn` may contain, which is why that call sits at one program point that every thread reaches.
-template <int Class, bool Rgb, class Push, class Inside>
+// Mode (roughgrating, spectral variants): the queue is processed by two kernels running this one body.
+//   kNeeFilter  k_nee_post<grating>: loads the record, finishes the unlit well-formed items (contribution exactly 0) and the
+//               malformed ones (non-finite or non-unit inputs, the reference's quirks of DESIGN.md 5: evaluated as written), and
+//               lists the lit ones in the scan list (shadow_q, dead after the shadow trace)
+//   kNeeScan    k_nee_scan: the lobe-window scan of the lit items, one per lane, all lanes busy (inside one kernel, one item per
+//               thread ran the scan at 10 of 32 lanes; a block-level hand-over to dense threads left 29 % of the warp samples at its
+//               barrier: 53.6 / 47.2 / 45.4 ms per 2^30 samples on cbox-grating.  Moving the malformed items to a third kernel made
+//               the filter 40 registers wide but no faster, and the handful of exhaustive evaluations cost 0.2 ms per pass alone.)
+//   kNeeFull    everything in one call: the other material classes and the RGB variants
+enum { kNeeFull = 0, kNeeFilter = 1, kNeeScan = 2 };
+template <int Class, bool Rgb, int Mode, class Push, class Inside>
 PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
     const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
     const size_t r = (size_t) depth * st.chunk + local;
@@ -372,9 +380,10 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
         // (RGB variants, Rgb = true: the fallback's lobe search differs -- other wavelengths, a coherence factor on every lobe --
         // and takes the generic path below)
-        const bool inside = inside_fn(valid && sane && lit, b, wi_f, wo_f, si.uv, wl);
+        if (Mode == kNeeFilter && valid && sane && lit) { push(st.shadow_q, st.counts + kCntScan, entry); return; }
+        const bool inside = Mode != kNeeFilter && inside_fn(valid && sane && lit, b, wi_f, wo_f, si.uv, wl);
         if (!valid) return;
-        if (sane) {
+        if (sane || Mode == kNeeScan) {
             if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
             float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
