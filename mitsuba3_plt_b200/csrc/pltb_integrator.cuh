@@ -240,16 +240,22 @@ struct PassState {
     float4 *p_prev;            // {prev_si.p, last_nd_pdf}
     uint32_t *p_flags;         // bit 0: prev_bsdf_delta
     // per vertex (depth-major)
-    float4 *v_w;               // replay weight w_i = wbsdf_weight(si_i, wo_i)
-    float4 *v_p_u, *v_n_v, *v_s_wix, *v_shn_wiy;   // {p, uv.x} {n, uv.y} {sh.s, wi.x} {sh.n, wi.y}
-    float4 *v_alpha;           // replayed throughput alpha_i
+    float4 *v_w;               // replay weight w_i = wbsdf_weight(si_i, wo_i); after the sample phase: [slot] {ds.p, +-ds.pdf} of the NEE steps
+    // NEE records: only the vertices that queue an NEE item have one, and they are stored DENSELY, indexed by the record slot the
+    // vertex reserved (one global counter, counts[kCntSlot]; a k_shade launch reserves a contiguous run, so the per-class queues
+    // hold runs of consecutive slots and the NEE kernels read and write full sectors -- indexed by depth * chunk + sample they
+    // touched half-used sectors: 304 B of DRAM per roughgrating item for 152 B of record)
+    float4 *v_p_u, *v_n_v, *v_s_wix, *v_shn_wiy;   // [slot] {p, uv.x} {n, uv.y} {sh.s, wi.x} {sh.n, wi.y}
+    float4 *v_alpha;           // [slot] replayed throughput alpha_i
+    float4 *v_emw;             // [slot] emitter weight between the NEE steps (k_nee_light -> k_nee_post -> k_nee_eval)
+    uint32_t *rec_entry;       // [slot] sample_local | depth << 27 of the vertex
     float4 *v_em;              // MIS-weighted emissive contribution alpha_i * Lem_i
     float4 *v_nee;             // NEE contribution (k_nee)
-    float2 *v_wiz_shape;       // {wi.z, shape id bits}
+    float2 *v_wiz_shape;       // [slot] {wi.z, shape id bits}
     // polarized variants only (PLTB_RENDER_POLARIZED; nullptr otherwise).  Component-major: [c][...] with c = Stokes component.
     float4 *pp_alpha;          // [4][chunk]   first column of the sample-phase throughput matrix
     float4 *pv_w;              // [16][nv]     replay weight W_i as 4 rows x 4 wavelengths: index (4 * wavelength + row) * nv + r
-    float4 *pv_alpha;          // [4][nv]      first column of the replayed throughput alpha_i (the NEE step reads it)
+    float4 *pv_alpha;          // [4][nv]      first column of the replayed throughput alpha_i, by record slot (the NEE step reads it)
     float4 *pv_em;             // [4][nv]      first column of alpha_i * Lem_i
     float *stokes_theta;       // [chunk]      angle of the final Stokes-frame rotation to the sensor's x axis (stokes.cpp:100-106)
     size_t nv;                 // chunk * max_depth slots
@@ -257,7 +263,7 @@ struct PassState {
     uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
     uint32_t *shade_q[kClasses];   // hits of the current bounce by material class (== BSDF plugin type, PLTB_BSDF_*); nullptr for
                                    // classes the scene does not contain
-    uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: entry = sample_local | depth << 27
+    uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: record slots
     uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee_post<1> -> k_nee_eval)
     uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>); after
                                // the shadow trace the array is reused as the scan list of k_nee_post<grating> (counts[kCntScan])
@@ -276,6 +282,7 @@ PLTB_HD int cnt_cursor(uint32_t i) { return kCountsStride * (int) i + 1; }
 PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCountsStride * (int) i + 2 + (int) c; }
 PLTB_HD int cnt_nee(uint32_t c) { return kCountsNee + (int) c; }
 constexpr int kCntEval = kCountsNee + kClasses, kCntShadow = kCountsNee + kClasses + 1, kCntShadowCursor = kCountsNee + kClasses + 2;
+constexpr int kCntSlot = kCountsNee + kClasses + 4;   // NEE record slots reserved so far (all classes)
 constexpr int kCntScan = kCountsNee + kClasses + 3;   // roughgrating NEE items whose lobe windows have to be scanned (k_nee_post<grating> -> k_nee_scan)
 
 struct PassParams {

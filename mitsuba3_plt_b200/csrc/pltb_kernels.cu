@@ -38,10 +38,11 @@ struct DevPush {
         if ((int) (threadIdx.x & 31) == t.leader) t.base = atomicAdd(count, (uint32_t) __popc(t.peers));
         return t;
     }
-    __device__ __forceinline__ void finish(uint32_t *list, const Ticket &t, uint32_t entry) const {
+    __device__ __forceinline__ uint32_t index(const Ticket &t) const {   // the position reserved for this lane
         const uint32_t base = __shfl_sync(t.peers, t.base, t.leader);
-        list[base + __popc(t.peers & ((1u << (threadIdx.x & 31)) - 1u))] = entry;
+        return base + __popc(t.peers & ((1u << (threadIdx.x & 31)) - 1u));
     }
+    __device__ __forceinline__ void finish(uint32_t *list, const Ticket &t, uint32_t entry) const { list[index(t)] = entry; }
 };
 
 struct DevFilm {
@@ -112,8 +113,7 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceSce
                 if (e < n) {
                     Ray ray;
                     if (Shadow) {
-                        const uint32_t entry = st.shadow_q[e];
-                        local = (size_t) (entry >> 27) * st.chunk + (entry & 0x7FFFFFFu);
+                        local = st.shadow_q[e];   // record slot
                         ray = nee_shadow_ray(st, local);
                     } else {
                         local = st.live[e];

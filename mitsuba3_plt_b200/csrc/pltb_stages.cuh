@@ -200,18 +200,21 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 
     // bounce record
     const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
-    typename Push::Ticket t_nee, t_live;   // both list reservations are issued before the record stores (DevPush::begin)
-    if (nee) t_nee = push.begin(st.counts + cnt_nee(Class));
+    typename Push::Ticket t_slot, t_nee, t_live;   // all reservations are issued before the record stores (DevPush::begin)
+    if (nee) { t_slot = push.begin(st.counts + kCntSlot); t_nee = push.begin(st.counts + cnt_nee(Class)); }
     if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
     st.v_em[r] = s4_to_f4(em);
     if (nee) {
-        st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
-        st.v_n_v[r] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
-        st.v_s_wix[r] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
-        st.v_shn_wiy[r] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
-        st.v_alpha[r] = s4_to_f4(ai);
+        const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
+        st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
+        st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
+        st.v_s_wix[slot] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
+        st.v_shn_wiy[slot] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
+        st.v_alpha[slot] = s4_to_f4(ai);
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
-        st.v_wiz_shape[r] = ws;
+        st.v_wiz_shape[slot] = ws;
+        st.rec_entry[slot] = local | (i << 27);
+        push.finish(st.queue[Class], t_nee, slot);
     } else {
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
@@ -224,7 +227,6 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = delta ? 1u : 0u;
     }
-    if (nee) push.finish(st.queue[Class], t_nee, local | (i << 27));
     if (active_next) {
         push.finish(st.live, t_live, local);
     } else {
@@ -238,13 +240,13 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 //   k_trace<true>    any-hit traversal of the shadow rays by persistent warps; an occluded sample gets ds.pdf = 0, which is
 //                    what scene.cpp:330-340 does
 //   stage_nee_post   wbsdf_eval / wbsdf_pdf, MIS weight, times the replayed throughput
-// Between the steps the vertex record carries {ds.p, +-ds.pdf (sign bit: ds.delta)} in v_w (free once the sample phase is
-// over) and the emitter weight in v_nee.
+// Between the steps the record slot carries {ds.p, +-ds.pdf (sign bit: ds.delta)} in v_w (free once the sample phase is
+// over) and the emitter weight in v_emw.
 template <class Push>
-PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_t entry, Push &push, uint32_t cnt[4]) {
-    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
-    PLTB_ASSERT(local < st.chunk && depth < st.max_depth);
-    const size_t r = (size_t) depth * st.chunk + local;
+PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_t slot, Push &push, uint32_t cnt[4]) {
+    const uint32_t entry = st.rec_entry[slot], local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    PLTB_ASSERT(local < st.chunk && depth < st.max_depth && slot < st.nv);
+    const size_t r = slot;   // NEE records and the scratch of the NEE steps are indexed by record slot
     const float4 a0 = st.v_p_u[r];
     const V3 p = mk3(a0.x, a0.y, a0.z);
     const S4 wl = f4_to_s4(st.wl[local]);
@@ -298,14 +300,14 @@ PLTB_HD void stage_nee_light(const DeviceScene &sc, const PassState &st, uint32_
     else if (em.type == PLTB_EMITTER_ENVMAP) em_val = envmap_eval_spectrum(sc, em, ds.uv, wl);   // ::eval_direction (:486-491)
     else em_val = tex_eval(sc, em.radiance, wl, ds.uv);
     const S4 em_weight = ds.pdf != 0.0f ? em_val / ds.pdf : s4(0.f);
-    st.v_nee[r] = s4_to_f4(em_weight);
+    st.v_emw[r] = s4_to_f4(em_weight);
     st.v_w[r] = mkf4(ds.p.x, ds.p.y, ds.p.z, ds.delta ? -ds.pdf : ds.pdf);
     if (ds.pdf != 0.f) {
         cnt[1]++;
 #if defined(__CUDA_ARCH__)
         if (st.n_shadow) atomicAdd(st.n_shadow + local, 1u);
 #endif
-        push(st.shadow_q, st.counts + kCntShadow, entry);
+        push(st.shadow_q, st.counts + kCntShadow, slot);
     }
 }
 
@@ -339,9 +341,9 @@ struct GratingInsideDirect {
 //   kNeeFull    everything in one call: the other material classes and the RGB variants
 enum { kNeeFull = 0, kNeeFilter = 1, kNeeScan = 2 };
 template <int Class, bool Rgb, int Mode, class Push, class Inside>
-PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t entry, bool valid, Push &push, Inside &&inside_fn) {
-    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
-    const size_t r = (size_t) depth * st.chunk + local;
+PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t slot, bool valid, Push &push, Inside &&inside_fn) {
+    const uint32_t entry = valid ? st.rec_entry[slot] : 0u, local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = slot, rv = (size_t) depth * st.chunk + local;   // record slot / vertex index (where the result goes)
     SI si;
     si.t = 0.f; si.uv = mk2(0.f, 0.f); si.wi = mk3(0.f, 0.f, 1.f);
     S4 wl = s4(0.f), em_weight = s4(0.f), a = s4(0.f);
@@ -361,7 +363,7 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         ds.delta = signbit_(w4.w);
         ds.pdf = fabsf(w4.w);            // 0 when the shadow ray was occluded
         ds.d = normalize(ds.p - si.p);
-        em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_nee[r]) : s4(0.f);
+        em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_emw[r]) : s4(0.f);
         wo = si.sh.to_local(ds.d);
         b = si_bsdf(sc, si.shape);
         a = f4_to_s4(st.v_alpha[r]);
@@ -380,16 +382,16 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
         const bool lit = em_weight.v[0] != 0.f || em_weight.v[1] != 0.f || em_weight.v[2] != 0.f || em_weight.v[3] != 0.f;
         // (RGB variants, Rgb = true: the fallback's lobe search differs -- other wavelengths, a coherence factor on every lobe --
         // and takes the generic path below)
-        if (Mode == kNeeFilter && valid && sane && lit) { push(st.shadow_q, st.counts + kCntScan, entry); return; }
+        if (Mode == kNeeFilter && valid && sane && lit) { push(st.shadow_q, st.counts + kCntScan, slot); return; }
         const bool inside = Mode != kNeeFilter && inside_fn(valid && sane && lit, b, wi_f, wo_f, si.uv, wl);
         if (!valid) return;
         if (sane || Mode == kNeeScan) {
-            if (!inside) { st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
+            if (!inside) { st.v_nee[rv] = mkf4(0.f, 0.f, 0.f, 0.f); return; }
             float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
             float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-            st.v_nee[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
+            st.v_emw[r] = s4_to_f4(em_weight * mis_em);    // finished by k_nee_eval
             st.v_w[r] = mkf4(wo.x, wo.y, wo.z, 0.f);
-            push(st.queue_eval, st.counts + kCntEval, entry);
+            push(st.queue_eval, st.counts + kCntEval, slot);
             return;
         }
     }
@@ -397,13 +399,13 @@ PLTB_HD void stage_nee_post(const DeviceScene &sc, const PassState &st, uint32_t
     S4 bsdf_val = wbsdf_eval<Class, Rgb>(sc, b, si.wi, si.uv, wl, wo);
     float bsdf_pdf = wbsdf_pdf<Class>(sc, b, si.wi, si.uv, wl, wo);
     float mis_em = ds.delta ? 1.0f : mis_weight(ds.pdf, bsdf_pdf);
-    st.v_nee[r] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
+    st.v_nee[rv] = s4_to_f4(((em_weight * mis_em) * bsdf_val) * a);
 }
 
 // second half of solve_replay_NEE for the roughgrating vertices whose light direction falls inside a lobe window
-PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t entry) {
-    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
-    const size_t r = (size_t) depth * st.chunk + local;
+PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t slot) {
+    const uint32_t entry = st.rec_entry[slot], local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = slot, rv = (size_t) depth * st.chunk + local;
     const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
     const float2 ws = st.v_wiz_shape[r];
     const V3 wi = mk3(a2.w, a3.w, ws.x), wo = mk3(w4.x, w4.y, w4.z);
@@ -411,7 +413,7 @@ PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t
     const S4 wl = f4_to_s4(st.wl[local]);
     const pltb_bsdf *b = si_bsdf(sc, (int32_t) f2u(ws.y));
     S4 bsdf_val = wbsdf_eval<PLTB_BSDF_ROUGHGRATING>(sc, b, wi, uv, wl, wo);
-    st.v_nee[r] = s4_to_f4((f4_to_s4(st.v_nee[r]) * bsdf_val) * f4_to_s4(st.v_alpha[r]));
+    st.v_nee[rv] = s4_to_f4((f4_to_s4(st.v_emw[r]) * bsdf_val) * f4_to_s4(st.v_alpha[r]));
 }
 
 // plt_solve_phase accumulation order (plt.py:191-216): emissive and NEE terms of every recorded vertex, in depth order

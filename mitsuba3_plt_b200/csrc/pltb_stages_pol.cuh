@@ -146,14 +146,17 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 
     const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
     if (nee) {
-        st.v_p_u[r] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
-        st.v_n_v[r] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
-        st.v_s_wix[r] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
-        st.v_shn_wiy[r] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
-        pol_store_col(st.pv_alpha, st.nv, r, ai);
+        typename Push::Ticket t_slot = push.begin(st.counts + kCntSlot), t_nee = push.begin(st.counts + cnt_nee(Class));
+        const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
+        st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
+        st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
+        st.v_s_wix[slot] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
+        st.v_shn_wiy[slot] = mkf4(si.sh.n.x, si.sh.n.y, si.sh.n.z, si.wi.y);
+        pol_store_col(st.pv_alpha, st.nv, slot, ai);
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
-        st.v_wiz_shape[r] = ws;
-        push(st.queue[Class], st.counts + cnt_nee(Class), local | (i << 27));
+        st.v_wiz_shape[slot] = ws;
+        st.rec_entry[slot] = local | (i << 27);
+        push.finish(st.queue[Class], t_nee, slot);
     } else {
         st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
@@ -174,9 +177,9 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 // solve_replay_NEE's BSDF half in a polarized variant.  em_weight is depolarizer(e), so ((e mis) * B) has only row 0,
 // (e mis) B(0, j), and its product with alpha contributes only to L(0, 0): sum_j X(0, j) alpha(j, 0) in fmadd order.
 template <int Class, bool Rgb>
-PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint32_t entry) {   // Rgb: see bsdf_eval_inner
-    const uint32_t local = entry & 0x7FFFFFFu, depth = entry >> 27;
-    const size_t r = (size_t) depth * st.chunk + local;
+PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint32_t slot) {   // Rgb: see bsdf_eval_inner
+    const uint32_t entry = st.rec_entry[slot], local = entry & 0x7FFFFFFu, depth = entry >> 27;
+    const size_t r = slot, rv = (size_t) depth * st.chunk + local;   // record slot / vertex index
     const float4 a0 = st.v_p_u[r], a1 = st.v_n_v[r], a2 = st.v_s_wix[r], a3 = st.v_shn_wiy[r], w4 = st.v_w[r];
     const float2 ws = st.v_wiz_shape[r];
     SI si;
@@ -191,7 +194,7 @@ PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint
     ds.delta = signbit_(w4.w);
     ds.pdf = fabsf(w4.w);            // 0 when the shadow ray was occluded
     ds.d = normalize(ds.p - si.p);
-    const S4 em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_nee[r]) : s4(0.f);
+    const S4 em_weight = ds.pdf != 0.0f ? f4_to_s4(st.v_emw[r]) : s4(0.f);
     const V3 wo = si.sh.to_local(ds.d);
     const pltb_bsdf *b = si_bsdf(sc, si.shape);
     V3 wi_f = si.wi, wo_f = wo;
@@ -212,7 +215,7 @@ PLTB_HD void stage_nee_post_pol(const DeviceScene &sc, const PassState &st, uint
         for (int j = 1; j < 4; ++j) v = fmadd(e * row[j], ai[k].v[j], v);
         out.v[k] = v;
     }
-    st.v_nee[r] = s4_to_f4(out);
+    st.v_nee[rv] = s4_to_f4(out);
 }
 
 }  // namespace pltb
