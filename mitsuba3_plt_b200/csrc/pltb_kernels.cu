@@ -65,7 +65,9 @@ __device__ __forceinline__ void flush_counters(const uint32_t cnt[4], unsigned l
     }
 }
 
-__global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+// (register budgets measured on cbox-grating, ms per 2^30 samples: k_raygen 72 regs 75.4, 64 regs 73.4, 48 regs 73.3; k_classify 80 regs 28.5,
+// 64 regs 29.4, 40 regs 30.2; k_gather 60 regs 18.0, 40 regs 20.2, 32 regs 32.0; k_nee_light 64 regs 27-28, 48 regs 30.8, 40 regs 33.6)
+__global__ void __launch_bounds__(128, 8) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                 const __grid_constant__ PassParams pp) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
@@ -89,8 +91,10 @@ __global__ void __launch_bounds__(128) k_raygen(const __grid_constant__ DeviceSc
 #ifndef PLTB_TRACE_INNER
 #define PLTB_TRACE_INNER 6   // inner-node steps per round before the leaf step
 #endif
+// register budgets: 64 for the closest-hit form (8 blocks of 128 threads per SM), 48 for the any-hit form (10 blocks, 58 B of spills):
+// k_trace 99.5 -> 96.0, k_trace<shadow> 75.3 -> 72.2 ms per 2^30 samples on cbox-grating (profiles/r02_ab_session16.txt)
 template <bool Shadow>
-__global__ void __launch_bounds__(128) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+__global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
     const uint32_t n = Shadow ? st.counts[kCntShadow] : st.counts[cnt_live(bounce)];
     uint32_t *cursor = Shadow ? st.counts + kCntShadowCursor : st.counts + cnt_cursor(bounce);
