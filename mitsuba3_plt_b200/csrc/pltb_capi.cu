@@ -345,6 +345,7 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.v_w, nv * sizeof(float4));
     rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.hit_cls, chunk * sizeof(uint8_t));
     for (int k = 0; k < kClasses; ++k) {
         st.shade_q[k] = st.queue[k] = nullptr;
         if (!(class_mask >> k & 1u)) continue;

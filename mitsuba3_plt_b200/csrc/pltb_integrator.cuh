@@ -261,6 +261,8 @@ struct PassState {
     size_t nv;                 // chunk * max_depth slots
     // work lists (path ids), filled with warp-aggregated atomics
     uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
+    uint8_t *hit_cls;          // [position in live] material class of what the ray hit, 0xFF = miss: k_trace -> k_classify (dense, so
+                               // the routing pass does not fetch the 16-byte hit records through the list)
     uint32_t *shade_q[kClasses];   // hits of the current bounce by material class (== BSDF plugin type, PLTB_BSDF_*); nullptr for
                                    // classes the scene does not contain
     uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: record slots

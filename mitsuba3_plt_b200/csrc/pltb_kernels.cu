@@ -104,6 +104,7 @@ __global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_con
     tr.done = true;
     bool active = false, exhausted = false;
     size_t local = 0;   // path id (closest hit) or vertex record index (shadow)
+    uint32_t epos = 0;  // position of the lane's ray in the live list
     for (;;) {
         __syncwarp();
         const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_con
                         local = st.shadow_q[e];   // record slot
                         ray = nee_shadow_ray(st, local);
                     } else {
-                        local = st.live[e];
+                        local = st.live[e]; epos = e;
                         float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
                         ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
                         cnt[0]++;
@@ -144,36 +145,40 @@ __global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_con
             }
             // results are written in place; k_classify walks the live list in order afterwards so that the shade / NEE work
             // lists stay (nearly) sorted by sample id and the per-sample state accesses of later kernels stay coalesced
-            st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.shape < 0 ? kHitMiss : (tr.best.prim | (tr.best.cls << kHitClsShift))));
+            if (tr.best.shape >= 0) {
+                st.p_hit[local] = mkf4(tr.best.t, tr.best.u, tr.best.v, u2f(tr.best.prim | (tr.best.cls << kHitClsShift)));
+                st.hit_cls[epos] = (uint8_t) tr.best.cls;
+            } else {
+                st.hit_cls[epos] = 0xFF;
+            }
             active = false;
         }
     }
     flush_counters(cnt, st.counters);
 }
 
-// Routes the results of k_trace: hits to the shade queue of their material class (carried in the hit record), misses finalised in
-// place.  The kernel is a chain of two dependent DRAM reads per entry (list entry -> hit record) followed by a list append, so a
-// warp takes 128 consecutive entries at a time: four independent load chains in flight per lane, appended in list order.
+// Routes the results of k_trace: hits to the shade queue of their material class, misses finalised in place.  k_trace leaves the
+// class (or 0xFF for a miss) in hit_cls[position in the live list], so this pass reads two dense arrays (4 + 1 bytes per ray) and
+// only the misses touch per-path state; a warp takes 128 consecutive entries at a time and appends in list order.
 __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                   uint32_t bounce) {
     const uint32_t n = st.counts[cnt_live(bounce)];
     const uint32_t lane = threadIdx.x & 31u, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     DevPush push;
     for (uint32_t base = warp * 128u; base < n; base += n_warps * 128u) {
-        uint32_t local[4]; float4 h4[4];
+        uint32_t local[4]; uint32_t cls[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { const uint32_t e = base + 32u * j + lane; local[j] = e < n ? st.live[e] : 0u; }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) if (base + 32u * j + lane < n) h4[j] = st.p_hit[local[j]];
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t e = base + 32u * j + lane;
+            local[j] = e < n ? st.live[e] : 0u; cls[j] = e < n ? (uint32_t) st.hit_cls[e] : 0u;
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             if (base + 32u * j + lane >= n) continue;
-            const uint32_t w = f2u(h4[j].w);
-            Hit h; h.t = h4[j].x; h.u = h4[j].y; h.v = h4[j].z; h.prim = w & kHitPrimMask; h.cls = (w >> kHitClsShift) & 7u; h.shape = -1;
+            Hit h; h.t = 0.f; h.u = h.v = 0.f; h.prim = 0; h.cls = cls[j] & 7u; h.shape = cls[j] == 0xFFu ? -1 : 0;
             PCG32 rng; rng.state = 0; rng.inc = 0;
-            if (w != kHitMiss) h.shape = 0;   // any valid shape: route_hit only needs hit / miss and the class here
-            else { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
-            route_hit(sc, st, local[j], bounce, h, rng, false, push);
+            if (h.shape < 0) { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
+            route_hit(sc, st, local[j], bounce, h, rng, false, push);   // any valid shape: only hit / miss and the class matter here
         }
     }
 }
