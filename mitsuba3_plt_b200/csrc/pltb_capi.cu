@@ -505,6 +505,8 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
                                                  std::max<uint64_t>(c->sm_count, (pass_samples + 511) / 512));
     const int nee_grid = wf_grid;
     const int do_splat = (prm->flags & PLTB_RENDER_NO_SPLAT) ? 0 : 1;
+    const int splat_nr = dev_scene.film.rfilter == PLTB_RFILTER_BOX ? 0 : (int) ceilf(dev_scene.film.radius - .5f);
+    const bool strip_splat = (splat_nr == 1 || splat_nr == 2) && !getenv("PLTB_SPLAT_DIRECT");   // as launch_splat decides
     for (uint64_t first = 0; first < total; first += st.chunk) {
         if (c->cancel.load()) {
             // with several ranks the peers are (or will be) waiting in the film reduce: take part in it before leaving, so that a
@@ -546,7 +548,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         launch_splat(dev_scene, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
-        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized && !rgb ? 2 : 0) + 1 + (do_splat ? 1 : 0);   // grating: + k_nee_scan, k_nee_eval
+        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized && !rgb ? 2 : 0) + 1 + (do_splat ? (stokes && strip_splat ? 4 : 1) : 0);   // grating: + k_nee_scan, k_nee_eval; Stokes film: one strip launch per float4 group
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0

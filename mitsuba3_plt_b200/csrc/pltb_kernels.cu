@@ -9,6 +9,7 @@
 // appends use warp-aggregated atomics (match_any + popc + one atomicAdd per group).
 #include <cuda_runtime.h>
 #include <cstdlib>
+#include <type_traits>
 
 #include "pltb_stages_pol.cuh"
 #include "pltb_launch.h"
@@ -50,6 +51,14 @@ struct DevFilm {
     __device__ __forceinline__ void add(size_t pixel, const float values[4], float w) {
         float4 v = make_float4(values[0] * w, values[1] * w, values[2] * w, values[3] * w);
         atomicAdd(reinterpret_cast<float4 *>(accum) + pixel, v);   // red.global.add.v4.f32 (sm_90+)
+    }
+};
+// one float4 group G of a 16-channel Stokes film (R G B W | S0.RGB S1.R | S1.GB S2.RG | S2.B S3.RGB)
+template <int G> struct DevFilmGroup {
+    float *accum;
+    __device__ __forceinline__ void add(size_t pixel, const float values[4], float w) {
+        float4 v = make_float4(values[0] * w, values[1] * w, values[2] * w, values[3] * w);
+        atomicAdd(reinterpret_cast<float4 *>(accum) + 4 * pixel + G, v);
     }
 };
 
@@ -319,7 +328,29 @@ __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceSce
 #define PLTB_SPLAT_S 32   // sample indices per warp (8: 49.2, 16: 46.1, 32: 45.0 ms of k_splat per 2^30 samples at 32 spp per pass)
 #endif
 constexpr int kSplatWarps = 4, kSplatS = PLTB_SPLAT_S;
-template <int NR>
+// G < 0: the RGBW film.  G = 0..3: float4 group G of the 16-channel Stokes film (k_gather_pol left the four Stokes components of L
+// in p_ray_o / p_ray_d / p_hit / p_prev): four launches of this kernel replace one thread per sample issuing 100 vector atomics
+// (k_splat_stokes: 61.6 of the 229 ms of a polarized cbox-grating render at 128 spp).
+template <int G> __device__ __forceinline__ void stokes_group_values(const DeviceScene &sc, const PassState &st, uint32_t local, const S4 &wl,
+                                                                     const S4 &sw, float values[4]) {
+    const float4 *comp[4] = { st.p_ray_o, st.p_ray_d, st.p_hit, st.p_prev };
+    if (G == 0) { splat_values(sc, f4_to_s4(comp[0][local]), wl, sw, values); return; }
+    // AOV i = spectrum_to_srgb(S_i / pdf_rgb_spectrum(wavelengths)) (stokes.cpp:108-121), RGB variants: S_i itself; flattened channels
+    // 3 i + c sit at film channel 4 + 3 i + c, i.e. group G holds flattened channels 4 (G - 1) .. 4 (G - 1) + 3
+    float aov[2][3];
+    constexpr int i0 = (4 * (G - 1)) / 3;          // first Stokes component this group touches (G = 1: 0, 2: 1, 3: 2)
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const S4 c = f4_to_s4(comp[i0 + k][local]);
+        if (sc.rgb) { aov[k][0] = c.v[0]; aov[k][1] = c.v[1]; aov[k][2] = c.v[2]; continue; }
+        S4 v;
+        for (int q = 0; q < 4; ++q) { const float pdf = pdf_rgb_spectrum(wl.v[q]); v.v[q] = c.v[q] * (pdf != 0.f ? rcp(pdf) : 0.f); }
+        spectrum_to_srgb(sc.cie_srgb, v, wl, aov[k]);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { const int f = 4 * (G - 1) + q, i = f / 3, c = f - 3 * i; values[q] = aov[i - i0][c]; }
+}
+template <int NR, int G = -1>
 __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_constant__ DeviceScene sc,
                                                                   const __grid_constant__ PassState st,
                                                                   const __grid_constant__ PassParams pp, float *accum,
@@ -336,7 +367,8 @@ __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_c
     const int x = (int) (pp.crop_x + (pix - row * pp.crop_w)), y = (int) (pp.crop_y + row);
     const int x0 = __shfl_sync(0xffffffffu, x, 0), y0 = __shfl_sync(0xffffffffu, y, 0);
     const bool same_row = valid_pix && y == y0;      // then x == x0 + lane
-    DevFilm film{ accum };
+    constexpr int kStride = G < 0 ? 1 : 4, kOff = G < 0 ? 0 : G;
+    typename std::conditional<(G < 0), DevFilm, DevFilmGroup<(G < 0 ? 0 : G)>>::type film{ accum };
     float4 acc[kTaps][kTaps];
 #pragma unroll
     for (int ys = 0; ys < kTaps; ++ys)
@@ -344,14 +376,16 @@ __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_c
         for (int xs = 0; xs < kTaps; ++xs) acc[ys][xs] = make_float4(0.f, 0.f, 0.f, 0.f);
     bool dirty = false;
     // per-sample inputs are fetched one iteration ahead: the loop is a chain of dependent DRAM reads otherwise
-    struct Fetch { bool in; float4 L, wl, sw; float2 pos; };
+    struct Fetch { bool in; uint32_t local; float4 L, wl, sw; float2 pos; };
     auto fetch = [&](uint32_t k) {
         Fetch f;
         const uint64_t w = (uint64_t) (s_first + k) * pp.n_pix + pix;
         f.in = k < (uint32_t) kSplatS && s_first + k <= s_hi && valid_pix && w >= pp.first && w < pp.first + pp.count;
         if (f.in) {
             const uint32_t local = (uint32_t) (w - pp.first);
-            f.L = st.p_ray_o[local]; f.wl = st.wl[local]; f.sw = st.sensor_w[local]; f.pos = st.film_pos[local];
+            f.local = local;
+            if (G < 0) f.L = st.p_ray_o[local];
+            f.wl = st.wl[local]; f.sw = st.sensor_w[local]; f.pos = st.film_pos[local];
         }
         return f;
     };
@@ -362,7 +396,8 @@ __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_c
         nxt = fetch(k + 1);
         if (!cur.in) continue;
         float values[4];
-        splat_values(sc, f4_to_s4(cur.L), f4_to_s4(cur.wl), f4_to_s4(cur.sw), values);
+        if (G < 0) splat_values(sc, f4_to_s4(cur.L), f4_to_s4(cur.wl), f4_to_s4(cur.sw), values);
+        else stokes_group_values<(G < 0 ? 0 : G)>(sc, st, cur.local, f4_to_s4(cur.wl), f4_to_s4(cur.sw), values);
         const float2 pos = cur.pos;
         if (!(same_row && (int) floorf(pos.x) == x && (int) floorf(pos.y) == y)) {
             splat_taps(sc, pp, values, pos, film);
@@ -409,7 +444,7 @@ __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_c
         if (xx < 0 || yy < 0 || xx >= W || yy >= H) continue;
         const float4 v = tile[i];
         if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)   // NaN != 0: poisoned taps reach the film as before
-            atomicAdd(reinterpret_cast<float4 *>(accum) + ((size_t) yy * W + xx), v);
+            atomicAdd(reinterpret_cast<float4 *>(accum) + kStride * ((size_t) yy * W + xx) + kOff, v);
     }
 }
 
@@ -587,19 +622,24 @@ void launch_splat(const DeviceScene &sc, const PassState &st, const PassParams &
                                                         (dump_wl || dump_L || dump_rays) ? dump_cap : 0);
     PLTB_AFTER(PLTB_K_GATHER);
     if (!do_splat) return;
-    if (stokes) {
-        k_splat_stokes<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
-        return;
-    }
     // separable filters with 3x3 (tent, r = 1) or 5x5 (gaussian, r = 2) taps go through the register tiles / shared strips
     const int nr = sc.film.rfilter == PLTB_RFILTER_BOX ? 0 : (int) ceilf(sc.film.radius - .5f);
     if ((nr == 1 || nr == 2) && !getenv("PLTB_SPLAT_DIRECT")) {
         const uint32_t s_lo = (uint32_t) (pp.first / pp.n_pix), s_hi = (uint32_t) ((pp.first + pp.count - 1) / pp.n_pix);
         const uint32_t n_strips = (pp.n_pix + 31) / 32, n_chunks = (s_hi - s_lo) / kSplatS + 1;
         const uint32_t n_warps = n_strips * n_chunks, grid = (n_warps + kSplatWarps - 1) / kSplatWarps;
-        if (nr == 1) k_splat_strip<1><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
-        else k_splat_strip<2><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps);
+#define PLTB_STRIP(NR, G) k_splat_strip<NR, G><<<grid, 32 * kSplatWarps, 0, s>>>(sc, st, pp, accum, s_lo, s_hi, n_strips, n_warps)
+        if (stokes) {   // one launch per float4 group of the 16-channel film
+            if (nr == 1) { PLTB_STRIP(1, 0); PLTB_STRIP(1, 1); PLTB_STRIP(1, 2); PLTB_STRIP(1, 3); }
+            else { PLTB_STRIP(2, 0); PLTB_STRIP(2, 1); PLTB_STRIP(2, 2); PLTB_STRIP(2, 3); }
+        } else if (nr == 1) PLTB_STRIP(1, -1);
+        else PLTB_STRIP(2, -1);
+#undef PLTB_STRIP
         PLTB_AFTER(PLTB_K_SPLAT);
+        return;
+    }
+    if (stokes) {
+        k_splat_stokes<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
         return;
     }
     k_splat<<<(pp.count + 255) / 256, 256, 0, s>>>(sc, st, pp, accum); PLTB_AFTER(PLTB_K_SPLAT);
