@@ -33,11 +33,27 @@ PLTB_HD float stokes_rotation_angle(const pltb_sensor &sn, V3 ray_d, bool batch)
     return theta;
 }
 
-// first column of W_0 (W_1 (... (W_{i-1} I))) from the stored replay weights (replay_path, plt.py:440-470)
-PLTB_HD void pol_replay_column(const PassState &st, uint32_t local, uint32_t i, C4 ai[4]) {
+// first column of W_0 (W_1 (... (W_{i-1} I))) from the stored replay weights (replay_path, plt.py:440-470).
+// `flags` = p_flags of the path: bit 1 + j says that W_j is a scaled identity (the replay weight of `diffuse`, diffuse.cpp:182-200),
+// stored as ONE float4 of the four per-wavelength factors instead of sixteen: for finite operands diag(s) * a is s * a component by
+// component (the fmadd chain of f44_apply only adds exact zeros), and a closed box is mostly diffuse walls -- the O(depth^2) re-read
+// of the weights was the largest stream of the polarized shading kernel (256 B per earlier vertex).
+PLTB_HD void pol_replay_column(const PassState &st, uint32_t local, uint32_t i, uint32_t flags, C4 ai[4]) {
     for (int k = 0; k < 4; ++k) { ai[k].v[0] = 1.f; ai[k].v[1] = ai[k].v[2] = ai[k].v[3] = 0.f; }
     for (int j = (int) i - 1; j >= 0; --j) {
         const size_t rj = (size_t) j * st.chunk + local;
+        if (flags >> (1 + j) & 1u) {
+            const float4 s = st.pv_w[rj];
+            const float sv[4] = { s.x, s.y, s.z, s.w };
+            float fsum = 0.f;
+            for (int k = 0; k < 4; ++k) fsum += (ai[k].v[0] + ai[k].v[1]) + (ai[k].v[2] + ai[k].v[3]);
+            if (finite_(fsum)) {
+                for (int k = 0; k < 4; ++k) for (int c = 0; c < 4; ++c) ai[k].v[c] = sv[k] * ai[k].v[c];
+            } else {   // 0 * inf / NaN terms of the full product must show up as they do in the reference
+                for (int k = 0; k < 4; ++k) ai[k] = f44_apply(f44_diag(sv[k]), ai[k]);
+            }
+            continue;
+        }
         for (int k = 0; k < 4; ++k) {
             F44 W;
             for (int row = 0; row < 4; ++row) {
@@ -57,7 +73,7 @@ PLTB_NI void pol_miss_record(const DeviceScene &sc, const PassState &st, uint32_
     if (sc.env >= 0) {
         const S4 Lem = env_miss_lem(sc, st, local, i);
         C4 ai[4];
-        pol_replay_column(st, local, i, ai);
+        pol_replay_column(st, local, i, i > 0 ? st.p_flags[local] : 0u, ai);
         for (int k = 0; k < 4; ++k) for (int c = 0; c < 4; ++c) em[k].v[c] = ai[k].v[c] * Lem.v[k];
     }
     pol_store_col(st.pv_em, st.nv, r, em);
@@ -76,12 +92,14 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
     float eta = 1.f, last_nd_pdf = 1.f;
     bool prev_bsdf_delta = true;
     V3 prev_p = mk3(0.f, 0.f, 0.f);
+    uint32_t flags = 0u;   // bit 0: prev_bsdf_delta; bit 1 + j: the replay weight of vertex j is a scaled identity (pol_replay_column)
     if (i > 0) {
         pol_load_col(st.pp_alpha, st.chunk, local, alpha);
         float4 pv = st.p_prev[local];
         prev_p = mk3(pv.x, pv.y, pv.z); last_nd_pdf = pv.w;
         eta = d4.w;
-        prev_bsdf_delta = (st.p_flags[local] & 1u) != 0;
+        flags = st.p_flags[local];
+        prev_bsdf_delta = (flags & 1u) != 0;
     }
     SI si = make_si(sc, ray, h);
     bool active_next = (i + 1 < st.max_depth);
@@ -96,7 +114,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 
     // replay_path: first column of W_0 (W_1 (... (W_{i-1} I)))
     C4 ai[4];
-    pol_replay_column(st, local, i, ai);
+    pol_replay_column(st, local, i, flags, ai);
     // solve_replay_emissive: Li = alpha * (mis_bsdf * depolarizer(Le)): first column = alpha[:, 0] * (mis * Le)
     const size_t r = (size_t) i * st.chunk + local;
     C4 em[4];
@@ -122,12 +140,18 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         }
     }
     pol_store_col(st.pv_em, st.nv, r, em);
-    if (active_next)
-        for (int k = 0; k < 4; ++k) {
-            const F44 W = pol_replay_weight(pv, k);
-            for (int row = 0; row < 4; ++row)
-                st.pv_w[(size_t) (4 * k + row) * st.nv + r] = mkf4(W.m[row][0], W.m[row][1], W.m[row][2], W.m[row][3]);
+    if (active_next) {
+        if (pv.type == PLTB_BSDF_DIFFUSE) {   // diag(reflectance): the four factors, flagged in p_flags
+            st.pv_w[r] = s4_to_f4(pv.refl);
+            flags |= 1u << (1 + i);
+        } else {
+            for (int k = 0; k < 4; ++k) {
+                const F44 W = pol_replay_weight(pv, k);
+                for (int row = 0; row < 4; ++row)
+                    st.pv_w[(size_t) (4 * k + row) * st.nv + r] = mkf4(W.m[row][0], W.m[row][1], W.m[row][2], W.m[row][3]);
+            }
         }
+    }
     cnt[2]++;
     if (Class == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
 
@@ -167,7 +191,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
         pol_store_col(st.pp_alpha, st.chunk, local, alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
-        st.p_flags[local] = delta ? 1u : 0u;
+        st.p_flags[local] = (flags & ~1u) | (delta ? 1u : 0u);
         push(st.live, st.counts + cnt_live(i + 1), local);
     } else {
         st.n_vertices[local] = i + 1;
