@@ -342,7 +342,8 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.p_hit, chunk * sizeof(float4));
     rc |= alloc((void **) &st.p_alpha, chunk * sizeof(float4));
     rc |= alloc((void **) &st.p_prev, chunk * sizeof(float4));
-    rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint32_t));
+    rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint64_t));
+    rc |= alloc((void **) &st.v_mask, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.v_w, nv * sizeof(float4));
     rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.hit_cls, chunk * sizeof(uint8_t));
@@ -433,7 +434,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b) {
             // polarized: + 64 B per sample (throughput column) + 384 B per vertex slot (16-float4 weight, two 4-float4 columns)
-            const uint64_t per_sample = 156ull + 172ull * prm->max_depth + (polarized ? 68ull + 384ull * prm->max_depth : 0ull);
+            const uint64_t per_sample = 164ull + 172ull * prm->max_depth + (polarized ? 68ull + 384ull * prm->max_depth : 0ull);
             while (chunk_log2 > 20 && (per_sample << chunk_log2) > (uint64_t) (0.3 * (double) total_b)) --chunk_log2;
         }
     }

@@ -238,7 +238,11 @@ struct PassState {
     float4 *p_hit;             // {t, u, v, prim id bits} of the closest hit found by k_trace
     float4 *p_alpha;           // sample-phase throughput alpha
     float4 *p_prev;            // {prev_si.p, last_nd_pdf}
-    uint32_t *p_flags;         // bit 0: prev_bsdf_delta
+    uint64_t *p_flags;         // bit 0: prev_bsdf_delta; bits 1 + j: (polarized) the replay weight of vertex j is a scaled identity;
+                               // bits 17 + j / 33 + j: vertex j has an emissive / an NEE term (kFlagEm / kFlagNee)
+    uint32_t *v_mask;          // per sample, written when the path ends: bit j: vertex j has an emissive term (v_em / pv_em written),
+                               // bit 16 + j: an NEE term (v_nee written).  Most terms are exact zeros (only emitter hits have an
+                               // emissive term, only smooth BSDFs queue NEE): they are neither stored nor summed
     // per vertex (depth-major)
     float4 *v_w;               // replay weight w_i = wbsdf_weight(si_i, wo_i); after the sample phase: [slot] {ds.p, +-ds.pdf} of the NEE steps
     // NEE records: only the vertices that queue an NEE item have one, and they are stored DENSELY, indexed by the record slot the
@@ -284,6 +288,8 @@ PLTB_HD int cnt_cursor(uint32_t i) { return kCountsStride * (int) i + 1; }
 PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCountsStride * (int) i + 2 + (int) c; }
 PLTB_HD int cnt_nee(uint32_t c) { return kCountsNee + (int) c; }
 constexpr int kCntEval = kCountsNee + kClasses, kCntShadow = kCountsNee + kClasses + 1, kCntShadowCursor = kCountsNee + kClasses + 2;
+constexpr int kFlagEm = 17, kFlagNee = 33;   // first bit of the two presence masks in PassState::p_flags
+PLTB_HD uint32_t pack_mask(uint64_t flags) { return (uint32_t) ((flags >> kFlagEm) & 0xFFFFull) | ((uint32_t) ((flags >> kFlagNee) & 0xFFFFull) << 16); }
 constexpr int kCntSlot = kCountsNee + kClasses + 4;   // NEE record slots reserved so far (all classes)
 constexpr int kCntScan = kCountsNee + kClasses + 3;   // roughgrating NEE items whose lobe windows have to be scanned (k_nee_post<grating> -> k_nee_scan)
 

@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassStat
                                                 float *dump_wl, float *dump_L, uint32_t *dump_rays, uint64_t dump_cap) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= pp.count) return;
-    const uint32_t n = st.n_vertices[local];
+    const uint32_t n = st.n_vertices[local], m = st.v_mask[local];   // m: the terms that exist (the others are exact zeros)
     S4 L = s4(0.f);
     for (uint32_t base = 0; base < n; base += 4) {
         float4 em[4], ne[4];
@@ -285,11 +285,15 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassStat
         for (uint32_t j = 0; j < 4; ++j)
             if (base + j < n) {
                 const size_t r = (size_t) (base + j) * st.chunk + local;
-                em[j] = st.v_em[r]; ne[j] = st.v_nee[r];
+                if (m >> (base + j) & 1u) em[j] = st.v_em[r];
+                if (m >> (16 + base + j) & 1u) ne[j] = st.v_nee[r];
             }
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j)
-            if (base + j < n) { L = L + f4_to_s4(em[j]); L = L + f4_to_s4(ne[j]); }
+            if (base + j < n) {
+                if (m >> (base + j) & 1u) L = L + f4_to_s4(em[j]);
+                if (m >> (16 + base + j) & 1u) L = L + f4_to_s4(ne[j]);
+            }
     }
     st.p_ray_o[local] = s4_to_f4(L);
     if (dump_cap) {
@@ -484,12 +488,12 @@ __global__ void __launch_bounds__(256) k_gather_pol(const __grid_constant__ Pass
                                                     float *dump_wl, float *dump_L, uint32_t *dump_rays, float *dump_stokes, uint64_t dump_cap) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= pp.count) return;
-    const uint32_t n = st.n_vertices[local];
+    const uint32_t n = st.n_vertices[local], m = st.v_mask[local];   // m: the terms that exist (the others are exact zeros)
     S4 L[4] = { s4(0.f), s4(0.f), s4(0.f), s4(0.f) };
     for (uint32_t i = 0; i < n; ++i) {
         const size_t r = (size_t) i * st.chunk + local;
-        for (int c = 0; c < 4; ++c) L[c] = L[c] + f4_to_s4(st.pv_em[(size_t) c * st.nv + r]);
-        L[0] = L[0] + f4_to_s4(st.v_nee[r]);
+        if (m >> i & 1u) for (int c = 0; c < 4; ++c) L[c] = L[c] + f4_to_s4(st.pv_em[(size_t) c * st.nv + r]);
+        if (m >> (16 + i) & 1u) L[0] = L[0] + f4_to_s4(st.v_nee[r]);
     }
     if (stokes) {
         const float theta = st.stokes_theta[local];

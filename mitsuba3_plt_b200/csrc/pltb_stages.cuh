@@ -84,9 +84,13 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
         for (int k = 0; k < 6; ++k) rng.state = rng.state * 0x5851f42d4c957f2dULL + rng.inc;
         st.rng_state[local] = rng.state; st.rng_inc[local] = rng.inc;
         const size_t r = (size_t) i * st.chunk + local;
-        if (st.pv_em) pol_miss_record(sc, st, local, i);
-        else st.v_em[r] = sc.env >= 0 ? s4_to_f4(env_miss_emission(sc, st, local, i)) : mkf4(0.f, 0.f, 0.f, 0.f);
-        st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
+        uint64_t flags = i > 0 ? st.p_flags[local] : 0ull;
+        if (sc.env >= 0) {   // the escaped ray sees the environment: an emissive term at this vertex
+            if (st.pv_em) pol_miss_record(sc, st, local, i);
+            else st.v_em[r] = s4_to_f4(env_miss_emission(sc, st, local, i));
+            flags |= 1ull << (kFlagEm + i);
+        }
+        st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
     }
 }
@@ -147,12 +151,14 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     float eta = 1.f, last_nd_pdf = 1.f;
     bool prev_bsdf_delta = true;
     V3 prev_p = mk3(0.f, 0.f, 0.f);
+    uint64_t flags = 0ull;   // PassState::p_flags
     if (i > 0) {
         alpha = f4_to_s4(st.p_alpha[local]);
         float4 pv = st.p_prev[local];
         prev_p = mk3(pv.x, pv.y, pv.z); last_nd_pdf = pv.w;
         eta = d4.w;
-        prev_bsdf_delta = (st.p_flags[local] & 1u) != 0;
+        flags = st.p_flags[local];
+        prev_bsdf_delta = (flags & 1ull) != 0;
     }
     SI si = make_si(sc, ray, h);
     bool active_next = (i + 1 < st.max_depth);   // si is valid here; depth == i on entry
@@ -203,8 +209,9 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     typename Push::Ticket t_slot, t_nee, t_live;   // all reservations are issued before the record stores (DevPush::begin)
     if (nee) { t_slot = push.begin(st.counts + kCntSlot); t_nee = push.begin(st.counts + cnt_nee(Class)); }
     if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
-    st.v_em[r] = s4_to_f4(em);
+    if (em_id >= 0) { st.v_em[r] = s4_to_f4(em); flags |= 1ull << (kFlagEm + i); }   // other vertices have no emissive term
     if (nee) {
+        flags |= 1ull << (kFlagNee + i);   // the NEE steps write v_nee[r]
         const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
         st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
         st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
@@ -215,8 +222,6 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.v_wiz_shape[slot] = ws;
         st.rec_entry[slot] = local | (i << 27);
         push.finish(st.queue[Class], t_nee, slot);
-    } else {
-        st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
     st.rng_state[local] = rng.state;
     if (active_next) {
@@ -225,11 +230,12 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
         st.p_alpha[local] = s4_to_f4(alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
-        st.p_flags[local] = delta ? 1u : 0u;
+        st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
     }
     if (active_next) {
         push.finish(st.live, t_live, local);
     } else {
+        st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
     }
 }
@@ -419,10 +425,11 @@ PLTB_HD void stage_nee_eval(const DeviceScene &sc, const PassState &st, uint32_t
 // plt_solve_phase accumulation order (plt.py:191-216): emissive and NEE terms of every recorded vertex, in depth order
 PLTB_HD S4 splat_gather(const PassState &st, uint32_t local, uint32_t n) {
     S4 L = s4(0.f);
+    const uint32_t m = st.v_mask[local];   // terms that exist; the others are exact zeros
     for (uint32_t i = 0; i < n; ++i) {
         const size_t r = (size_t) i * st.chunk + local;
-        L = L + f4_to_s4(st.v_em[r]);
-        L = L + f4_to_s4(st.v_nee[r]);
+        if (m >> i & 1u) L = L + f4_to_s4(st.v_em[r]);
+        if (m >> (16 + i) & 1u) L = L + f4_to_s4(st.v_nee[r]);
     }
     return L;
 }

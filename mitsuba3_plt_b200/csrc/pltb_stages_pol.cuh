@@ -67,15 +67,12 @@ PLTB_HD void pol_replay_column(const PassState &st, uint32_t local, uint32_t i, 
 
 // bounce record of a path that left the scene at bounce i: nothing, or the environment's emission alpha_i * depolarizer(mis * Le)
 PLTB_NI void pol_miss_record(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
-    const size_t r = (size_t) i * st.chunk + local;
+    const size_t r = (size_t) i * st.chunk + local;   // (only called when the scene has an environment emitter)
     C4 em[4];
-    for (int k = 0; k < 4; ++k) for (int c = 0; c < 4; ++c) em[k].v[c] = 0.f;
-    if (sc.env >= 0) {
-        const S4 Lem = env_miss_lem(sc, st, local, i);
-        C4 ai[4];
-        pol_replay_column(st, local, i, i > 0 ? st.p_flags[local] : 0u, ai);
-        for (int k = 0; k < 4; ++k) for (int c = 0; c < 4; ++c) em[k].v[c] = ai[k].v[c] * Lem.v[k];
-    }
+    const S4 Lem = env_miss_lem(sc, st, local, i);
+    C4 ai[4];
+    pol_replay_column(st, local, i, i > 0 ? (uint32_t) st.p_flags[local] : 0u, ai);
+    for (int k = 0; k < 4; ++k) for (int c = 0; c < 4; ++c) em[k].v[c] = ai[k].v[c] * Lem.v[k];
     pol_store_col(st.pv_em, st.nv, r, em);
 }
 
@@ -92,14 +89,14 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
     float eta = 1.f, last_nd_pdf = 1.f;
     bool prev_bsdf_delta = true;
     V3 prev_p = mk3(0.f, 0.f, 0.f);
-    uint32_t flags = 0u;   // bit 0: prev_bsdf_delta; bit 1 + j: the replay weight of vertex j is a scaled identity (pol_replay_column)
+    uint64_t flags = 0ull;   // PassState::p_flags: bit 0 prev_bsdf_delta, bits 1 + j scaled-identity replay weights (pol_replay_column), presence masks
     if (i > 0) {
         pol_load_col(st.pp_alpha, st.chunk, local, alpha);
         float4 pv = st.p_prev[local];
         prev_p = mk3(pv.x, pv.y, pv.z); last_nd_pdf = pv.w;
         eta = d4.w;
         flags = st.p_flags[local];
-        prev_bsdf_delta = (flags & 1u) != 0;
+        prev_bsdf_delta = (flags & 1ull) != 0;
     }
     SI si = make_si(sc, ray, h);
     bool active_next = (i + 1 < st.max_depth);
@@ -114,7 +111,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 
     // replay_path: first column of W_0 (W_1 (... (W_{i-1} I)))
     C4 ai[4];
-    pol_replay_column(st, local, i, flags, ai);
+    pol_replay_column(st, local, i, (uint32_t) flags, ai);
     // solve_replay_emissive: Li = alpha * (mis_bsdf * depolarizer(Le)): first column = alpha[:, 0] * (mis * Le)
     const size_t r = (size_t) i * st.chunk + local;
     C4 em[4];
@@ -139,11 +136,11 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
             }
         }
     }
-    pol_store_col(st.pv_em, st.nv, r, em);
+    if (em_id >= 0) { pol_store_col(st.pv_em, st.nv, r, em); flags |= 1ull << (kFlagEm + i); }   // other vertices have no emissive term
     if (active_next) {
         if (pv.type == PLTB_BSDF_DIFFUSE) {   // diag(reflectance): the four factors, flagged in p_flags
             st.pv_w[r] = s4_to_f4(pv.refl);
-            flags |= 1u << (1 + i);
+            flags |= 1ull << (1 + i);
         } else {
             for (int k = 0; k < 4; ++k) {
                 const F44 W = pol_replay_weight(pv, k);
@@ -170,6 +167,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
 
     const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
     if (nee) {
+        flags |= 1ull << (kFlagNee + i);
         typename Push::Ticket t_slot = push.begin(st.counts + kCntSlot), t_nee = push.begin(st.counts + cnt_nee(Class));
         const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
         st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
@@ -181,8 +179,6 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         st.v_wiz_shape[slot] = ws;
         st.rec_entry[slot] = local | (i << 27);
         push.finish(st.queue[Class], t_nee, slot);
-    } else {
-        st.v_nee[r] = mkf4(0.f, 0.f, 0.f, 0.f);
     }
     st.rng_state[local] = rng.state;
     if (active_next) {
@@ -191,9 +187,10 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
         pol_store_col(st.pp_alpha, st.chunk, local, alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
-        st.p_flags[local] = (flags & ~1u) | (delta ? 1u : 0u);
+        st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
         push(st.live, st.counts + cnt_live(i + 1), local);
     } else {
+        st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
     }
 }
