@@ -128,10 +128,12 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
         for (int k = 0; k < 4; ++k) u[k] = rng.next_float32();
         if (sc.rgb) st.wl[local] = mkf4(u[0] * 680.f, u[1] * 680.f, u[2] * 680.f, u[2] * 680.f);
     }
-    st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-    st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
     Hit h = bvh_intersect<false>(sc, ray);
     cnt[0]++;
+    if (h.shape >= 0 || sc.env >= 0) {   // a primary ray that leaves a scene without environment is never looked at again
+        st.p_ray_o[local] = mkf4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+        st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
+    }
     route_hit(sc, st, local, 0, h, rng, true, push);
 }
 

@@ -166,6 +166,8 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
     active_next = active_next && (!rr_active || rr_continue);
 
     const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
+    typename Push::Ticket t_live;   // all list reservations in flight before the record stores (DevPush::begin)
+    if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
     if (nee) {
         flags |= 1ull << (kFlagNee + i);
         typename Push::Ticket t_slot = push.begin(st.counts + kCntSlot), t_nee = push.begin(st.counts + cnt_nee(Class));
@@ -188,7 +190,7 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         pol_store_col(st.pp_alpha, st.chunk, local, alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
-        push(st.live, st.counts + cnt_live(i + 1), local);
+        push.finish(st.live, t_live, local);
     } else {
         st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
