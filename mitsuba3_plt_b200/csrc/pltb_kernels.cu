@@ -100,15 +100,27 @@ __global__ void __launch_bounds__(128, 8) k_raygen(const __grid_constant__ Devic
 #ifndef PLTB_TRACE_INNER
 #define PLTB_TRACE_INNER 6   // inner-node steps per round before the leaf step
 #endif
-// register budgets: 64 for the closest-hit form (8 blocks of 128 threads per SM), 48 for the any-hit form (10 blocks, 58 B of spills):
-// k_trace 99.5 -> 96.0, k_trace<shadow> 75.3 -> 72.2 ms per 2^30 samples on cbox-grating (profiles/r02_ab_session16.txt)
+#ifndef PLTB_TRACE_MINB
+#define PLTB_TRACE_MINB 8
+#endif
+#ifndef PLTB_TRACE_MINB_SHADOW
+#define PLTB_TRACE_MINB_SHADOW 8
+#endif
+// register budgets: 64 for both forms (8 blocks of 128 threads per SM).  With the traversal state in registers (the stack array
+// outside the Traversal struct) k_trace 95.7 -> 81.3, k_trace<shadow> 72.3 -> 61.2 ms per 2^30 samples on cbox-grating; closest hit at
+// 80 / 48 registers 89.7 / 88.2, any hit at 48 / 40 registers 63.7 / 75.9 (profiles/r02_ab_session17.txt).
+// Measured and rejected on top of that: stack entries 0..7 / 0..11 in shared memory (82.6, any hit 67.0); inner steps while at
+// least as many lanes want one as wait at a leaf (83.7 / 66.8); 4 or 8 inner steps per round (86.6 / 84.1); reserving 64 or 128
+// list positions per atomicAdd and handing them out by shuffle (82.5 / 87.8); requesting a leaf's next primitive before the
+// current one is tested (85.8).
 template <bool Shadow>
-__global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+__global__ void __launch_bounds__(128, Shadow ? PLTB_TRACE_MINB_SHADOW : PLTB_TRACE_MINB) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
     const uint32_t n = Shadow ? st.counts[kCntShadow] : st.counts[cnt_live(bounce)];
     uint32_t *cursor = Shadow ? st.counts + kCntShadowCursor : st.counts + cnt_cursor(bounce);
     const unsigned lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
+    unsigned long long stack_mem[kBvhStack];
     Traversal tr;
     tr.done = true;
     bool active = false, exhausted = false;
@@ -135,7 +147,7 @@ __global__ void __launch_bounds__(128, Shadow ? 10 : 8) k_trace(const __grid_con
                         ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
                         cnt[0]++;
                     }
-                    tr.begin(sc, ray);
+                    tr.begin(sc, ray, stack_mem);
                     active = true;
                 }
             }

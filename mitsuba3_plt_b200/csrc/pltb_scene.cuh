@@ -96,10 +96,14 @@ struct Traversal {
     int sp;
     bool done;
     Hit best;
-    unsigned long long stack[kBvhStack];   // key << 32 | child reference
+    // key << 32 | child reference.  The array lives outside the struct (the caller's local array): a dynamically indexed member
+    // keeps the whole struct -- ray, node, best hit -- in local memory, and k_trace is bound by the L1 data pipe.
+    unsigned long long *stack;
 
-    PLTB_HD void begin(const DeviceScene &sc, const Ray &r) {
-        ray = r;
+    PLTB_HD void push(unsigned long long e) { stack[sp++] = e; }
+    PLTB_HD unsigned long long top_pop() { return stack[--sp]; }
+    PLTB_HD void begin(const DeviceScene &sc, const Ray &r, unsigned long long *stack_mem) {
+        ray = r; stack = stack_mem;
         best.t = inf_f(); best.u = best.v = 0.f; best.prim = 0; best.shape = -1; best.cls = 0;
         sp = 0; node = 0;
         // A ray with a NaN component (the reference lets paths continue with alpha = inf * 0, DESIGN.md "quirks") fails every
@@ -110,7 +114,7 @@ struct Traversal {
     }
     PLTB_HD void pop() {
         while (sp > 0) {
-            const unsigned long long e = stack[--sp];
+            const unsigned long long e = top_pop();
             // the key holds the entry distance rounded down: a subtree that starts behind the closest hit cannot improve it
             if (u2f((uint32_t) (e >> 32) & ~3u) <= ray.maxt) { node = (int32_t) (uint32_t) e; return; }
         }
@@ -144,9 +148,9 @@ struct Traversal {
         t = umin_(k1, k2); k2 = umax_(k1, k2); k1 = t;
         if (k0 == 0xFFFFFFFFu) { pop(); return; }
         PLTB_ASSERT(sp + 3 <= kBvhStack);
-        if (k3 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k3 << 32) | child_ref(ch, k3);
-        if (k2 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k2 << 32) | child_ref(ch, k2);
-        if (k1 != 0xFFFFFFFFu) stack[sp++] = ((unsigned long long) k1 << 32) | child_ref(ch, k1);
+        if (k3 != 0xFFFFFFFFu) push(((unsigned long long) k3 << 32) | child_ref(ch, k3));
+        if (k2 != 0xFFFFFFFFu) push(((unsigned long long) k2 << 32) | child_ref(ch, k2));
+        if (k1 != 0xFFFFFFFFu) push(((unsigned long long) k1 << 32) | child_ref(ch, k1));
         node = (int32_t) child_ref(ch, k0);
     }
     PLTB_HD static uint32_t child_ref(const float4 &ch, uint32_t key) {
@@ -196,8 +200,9 @@ struct Traversal {
 
 // one-ray-per-thread form (coherent primary rays in k_raygen): the same steps, run to completion
 template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray) {
+    unsigned long long stack_mem[kBvhStack];
     Traversal tr;
-    tr.begin(sc, ray);
+    tr.begin(sc, ray, stack_mem);
     while (!tr.done) tr.template step<AnyHit>(sc);
     return tr.best;
 }

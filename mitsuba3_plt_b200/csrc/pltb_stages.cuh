@@ -211,9 +211,22 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     typename Push::Ticket t_slot, t_nee, t_live;   // all reservations are issued before the record stores (DevPush::begin)
     if (nee) { t_slot = push.begin(st.counts + kCntSlot); t_nee = push.begin(st.counts + cnt_nee(Class)); }
     if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
+    // the stores that need no reservation go first: they cover the round trips of the atomics
     if (em_id >= 0) { st.v_em[r] = s4_to_f4(em); flags |= 1ull << (kFlagEm + i); }   // other vertices have no emissive term
+    if (nee) flags |= 1ull << (kFlagNee + i);   // the NEE steps write v_nee[r]
+    st.rng_state[local] = rng.state;
+    if (active_next) {
+        const bool delta = (so.type & F_Delta) != 0;
+        st.p_ray_o[local] = mkf4(next.o.x, next.o.y, next.o.z, next.maxt);
+        st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
+        st.p_alpha[local] = s4_to_f4(alpha);
+        st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
+        st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
+    } else {
+        st.v_mask[local] = pack_mask(flags);
+        st.n_vertices[local] = i + 1;
+    }
     if (nee) {
-        flags |= 1ull << (kFlagNee + i);   // the NEE steps write v_nee[r]
         const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
         st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
         st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
@@ -225,21 +238,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.rec_entry[slot] = local | (i << 27);
         push.finish(st.queue[Class], t_nee, slot);
     }
-    st.rng_state[local] = rng.state;
-    if (active_next) {
-        const bool delta = (so.type & F_Delta) != 0;
-        st.p_ray_o[local] = mkf4(next.o.x, next.o.y, next.o.z, next.maxt);
-        st.p_ray_d[local] = mkf4(next.d.x, next.d.y, next.d.z, eta);
-        st.p_alpha[local] = s4_to_f4(alpha);
-        st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
-        st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
-    }
-    if (active_next) {
-        push.finish(st.live, t_live, local);
-    } else {
-        st.v_mask[local] = pack_mask(flags);
-        st.n_vertices[local] = i + 1;
-    }
+    if (active_next) push.finish(st.live, t_live, local);
 }
 
 // solve_replay_NEE (plt.py:221-300) for one queued vertex, in three steps so that every step runs in dense warps:

@@ -42,11 +42,12 @@ int main(int argc, char **argv) {
         if (r % 7 == 0) ray.d.y = 0.f;   // axis-aligned components: infinite reciprocals
         ray.maxt = r % 3 ? kLargest : 1.5f;
         // brute force over the leaf-ordered records with the same primitive test
-        Traversal bf; bf.begin(sc, ray); bf.done = false;
+        unsigned long long stk_bf[kBvhStack], stk_tr[kBvhStack], stk_sh[kBvhStack];
+        Traversal bf; bf.begin(sc, ray, stk_bf); bf.done = false;
         for (uint32_t i = 0; i < bvh.n_prims; ++i) { bf.node = (int32_t) ~(i | (1u << 24)); bf.sp = 0; bf.leaf_step<false>(sc); bf.done = false; }
-        Traversal tr; tr.begin(sc, ray);
+        Traversal tr; tr.begin(sc, ray, stk_tr);
         while (!tr.done) { tr.step<false>(sc); steps++; if (tr.sp > max_sp) max_sp = tr.sp; }
-        Traversal sh; sh.begin(sc, ray);
+        Traversal sh; sh.begin(sc, ray, stk_sh);
         while (!sh.done) sh.step<true>(sc);
         const bool same = tr.best.shape == bf.best.shape && (bf.best.shape < 0 || (tr.best.t == bf.best.t && tr.best.prim == bf.best.prim));
         const bool occl = (sh.best.shape >= 0) == (bf.best.shape >= 0);
