@@ -348,10 +348,9 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.hit_cls, chunk * sizeof(uint8_t));
     for (int k = 0; k < kClasses; ++k) {
-        st.shade_q[k] = st.queue[k] = nullptr;
+        st.shade_q[k] = nullptr;
         if (!(class_mask >> k & 1u)) continue;
         rc |= alloc((void **) &st.shade_q[k], chunk * sizeof(uint32_t));
-        rc |= alloc((void **) &st.queue[k], nv * sizeof(uint32_t));
     }
     rc |= alloc((void **) &st.v_p_u, nv * sizeof(float4));
     rc |= alloc((void **) &st.v_n_v, nv * sizeof(float4));
@@ -538,9 +537,11 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         nvtxRangePop();
         PROF();
         nvtxRangePushA("pltb:solve_nee");
-        launch_nee_light(dev_scene, st, cm, nee_grid, s);
+        const uint32_t nm = cm & kSmoothClassMask;   // the classes whose vertices can queue NEE items
+        const int n_nee = __builtin_popcount(nm);
+        launch_nee_light(dev_scene, st, nm, nee_grid, s);
         for (int cls = kClasses - 1; cls >= 0; --cls)
-            if ((cm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(dev_scene, st, cls, nee_grid, s);
+            if ((nm >> cls & 1u) && cls != PLTB_BSDF_ROUGHGRATING) launch_nee_post(dev_scene, st, cls, nee_grid, s);
         PROF();
         if (has_grating) launch_nee_post(dev_scene, st, PLTB_BSDF_ROUGHGRATING, nee_grid, s);
         nvtxRangePop();
@@ -549,7 +550,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
         launch_splat(dev_scene, st, pp, c->accum, do_splat, d_wl, d_L, d_rays, d_stokes, stokes ? 1 : 0, dcap, s);
         PROF();
         // raygen, k_nee_light per class, shadow trace, k_nee_post per class (+ k_nee_eval for the grating), gather (+ splat)
-        launches += 1 + n_cls + 1 + n_cls + (has_grating && !polarized && !rgb ? 2 : 0) + 1 + (do_splat ? (stokes && strip_splat ? 4 : 1) : 0);   // grating: + k_nee_scan, k_nee_eval; Stokes film: one strip launch per float4 group
+        launches += 1 + n_nee + 1 + n_nee + (has_grating && !polarized && !rgb ? 2 : 0) + 1 + (do_splat ? (stokes && strip_splat ? 4 : 1) : 0);   // grating: + k_nee_scan, k_nee_eval; Stokes film: one strip launch per float4 group
     }
     CU(cudaGetLastError());
     PROF();   // tail event 0

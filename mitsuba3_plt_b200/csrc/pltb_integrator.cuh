@@ -245,14 +245,18 @@ struct PassState {
                                // emissive term, only smooth BSDFs queue NEE): they are neither stored nor summed
     // per vertex (depth-major)
     float4 *v_w;               // replay weight w_i = wbsdf_weight(si_i, wo_i); after the sample phase: [slot] {ds.p, +-ds.pdf} of the NEE steps
-    // NEE records: only the vertices that queue an NEE item have one, and they are stored DENSELY, indexed by the record slot the
-    // vertex reserved (one global counter, counts[kCntSlot]; a k_shade launch reserves a contiguous run, so the per-class queues
-    // hold runs of consecutive slots and the NEE kernels read and write full sectors -- indexed by depth * chunk + sample they
-    // touched half-used sectors: 304 B of DRAM per roughgrating item for 152 B of record)
+    // NEE records are stored DENSELY, indexed by record slot: the vertex k_shade<c> shades at bounce i from position e of
+    // shade_q[c] owns slot  slot_base(i, c) + e,  slot_base = the number of vertices shaded by earlier launches of the pass (the sum
+    // of the shade-queue counts of the (bounce, class) pairs before (i, c), warp_slot_prefix in pltb_kernels.cu).  No counter is
+    // involved: a slot costs k_shade no atomic, and the NEE work list of a class is implicit -- its kernels walk the slot runs of
+    // that class, bounce by bounce.  Vertices that queue no NEE item (delta samples) leave rec_entry[slot] = kNoRecord.
+    // (Indexed by depth * chunk + sample the records touched half-used sectors: 304 B of DRAM per roughgrating item for 152 B of
+    // record; slots handed out by one atomic counter plus one per-class queue counter cost k_shade three same-line atomics per
+    // warp: 39 % of its stall samples at bounce 0 of veach-mis, profiles/r02_ab_session17.txt.)
     float4 *v_p_u, *v_n_v, *v_s_wix, *v_shn_wiy;   // [slot] {p, uv.x} {n, uv.y} {sh.s, wi.x} {sh.n, wi.y}
     float4 *v_alpha;           // [slot] replayed throughput alpha_i
     float4 *v_emw;             // [slot] emitter weight between the NEE steps (k_nee_light -> k_nee_post -> k_nee_eval)
-    uint32_t *rec_entry;       // [slot] sample_local | depth << 27 of the vertex
+    uint32_t *rec_entry;       // [slot] sample_local | depth << 27 of the vertex, or kNoRecord
     float4 *v_em;              // MIS-weighted emissive contribution alpha_i * Lem_i
     float4 *v_nee;             // NEE contribution (k_nee)
     float2 *v_wiz_shape;       // [slot] {wi.z, shape id bits}
@@ -263,13 +267,16 @@ struct PassState {
     float4 *pv_em;             // [4][nv]      first column of alpha_i * Lem_i
     float *stokes_theta;       // [chunk]      angle of the final Stokes-frame rotation to the sensor's x axis (stokes.cpp:100-106)
     size_t nv;                 // chunk * max_depth slots
-    // work lists (path ids), filled with warp-aggregated atomics
-    uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1)
+    // work lists (path ids)
+    uint32_t *live;            // paths whose next ray must be traced (written by k_shade of bounce i, read by k_trace i+1).  Like a
+                               // record slot, the position is implicit: the vertex at position e of shade_q[c] writes position
+                               // (number of vertices of the classes below c at this bounce) + e -- its path id, or kNoPath if the
+                               // path ended; the list of bounce i+1 has as many positions as bounce i shaded vertices
+                               // (live_count).  The other lists are filled with warp-aggregated atomics.
     uint8_t *hit_cls;          // [position in live] material class of what the ray hit, 0xFF = miss: k_trace -> k_classify (dense, so
                                // the routing pass does not fetch the 16-byte hit records through the list)
     uint32_t *shade_q[kClasses];   // hits of the current bounce by material class (== BSDF plugin type, PLTB_BSDF_*); nullptr for
                                    // classes the scene does not contain
-    uint32_t *queue[kClasses];     // NEE work items of the whole pass per class: record slots
     uint32_t *queue_eval;      // roughgrating NEE items that reached a lobe window (k_nee_post<1> -> k_nee_eval)
     uint32_t *shadow_q;        // NEE items of both classes whose light sample has a non-zero pdf (k_nee_light -> k_trace<true>); after
                                // the shadow trace the array is reused as the scan list of k_nee_post<grating> (counts[kCntScan])
@@ -278,20 +285,29 @@ struct PassState {
     // statistics
     unsigned long long *counters;  // closest, shadow, vertices, grating vertices, nee_other, nee_grating
 };
-// layout of PassState::counts: per bounce i a block of kCountsStride words {live count, trace cursor, shade_q[c] counts}; then the NEE
-// queue counts per class, the queue_eval count, the shadow_q count and the shadow-ray cursor
+// layout of PassState::counts: per bounce i a block of kCountsStride counters {unused, trace cursor, shade_q[c] counts}; then (after
+// kClasses unused ones) the queue_eval count, the shadow_q count, the shadow-ray cursor and the scan-list count
+// Every counter sits in its own 128-byte line (kCntPad words apart): atomics on words of one line queue up in the same L2 slice
+// (veach-mis 917 -> 963 Msamples/s when k_shade still appended to three lists per item, profiles/r02_ab_session17.txt).
+#ifndef PLTB_CNT_PAD
+#define PLTB_CNT_PAD 32
+#endif
+constexpr int kCntPad = PLTB_CNT_PAD;
 constexpr int kCountsStride = 2 + kClasses + 3;   // 12
 constexpr int kCountsNee = kCountsStride * (PLTB_MAX_DEPTH + 1);
-constexpr int kCountsTotal = kCountsNee + kClasses + 5;
-PLTB_HD int cnt_live(uint32_t i) { return kCountsStride * (int) i; }
-PLTB_HD int cnt_cursor(uint32_t i) { return kCountsStride * (int) i + 1; }
-PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCountsStride * (int) i + 2 + (int) c; }
-PLTB_HD int cnt_nee(uint32_t c) { return kCountsNee + (int) c; }
-constexpr int kCntEval = kCountsNee + kClasses, kCntShadow = kCountsNee + kClasses + 1, kCntShadowCursor = kCountsNee + kClasses + 2;
+constexpr int kCountsTotal = (kCountsNee + kClasses + 5) * kCntPad;
+PLTB_HD int cnt_cursor(uint32_t i) { return kCntPad * (kCountsStride * (int) i + 1); }
+PLTB_HD int cnt_shade(uint32_t i, uint32_t c) { return kCntPad * (kCountsStride * (int) i + 2 + (int) c); }
+constexpr int kCntEval = kCntPad * (kCountsNee + kClasses), kCntShadow = kCntPad * (kCountsNee + kClasses + 1),
+              kCntShadowCursor = kCntPad * (kCountsNee + kClasses + 2);
 constexpr int kFlagEm = 17, kFlagNee = 33;   // first bit of the two presence masks in PassState::p_flags
 PLTB_HD uint32_t pack_mask(uint64_t flags) { return (uint32_t) ((flags >> kFlagEm) & 0xFFFFull) | ((uint32_t) ((flags >> kFlagNee) & 0xFFFFull) << 16); }
-constexpr int kCntSlot = kCountsNee + kClasses + 4;   // NEE record slots reserved so far (all classes)
-constexpr int kCntScan = kCountsNee + kClasses + 3;   // roughgrating NEE items whose lobe windows have to be scanned (k_nee_post<grating> -> k_nee_scan)
+constexpr uint32_t kNoRecord = 0xFFFFFFFFu;   // rec_entry of a vertex without NEE item
+constexpr uint32_t kNoPath = 0xFFFFFFFFu;     // live-list position of a path that ended at the previous bounce
+// material classes whose samples can be smooth (diffuse, roughconductor, roughgrating, principled): only they run the NEE kernels
+constexpr uint32_t kSmoothClassMask = (1u << PLTB_BSDF_DIFFUSE) | (1u << PLTB_BSDF_ROUGHCONDUCTOR) | (1u << PLTB_BSDF_ROUGHGRATING) |
+                                      (1u << PLTB_BSDF_PRINCIPLED);
+constexpr int kCntScan = kCntPad * (kCountsNee + kClasses + 3);   // roughgrating NEE items whose lobe windows have to be scanned (k_nee_post<grating> -> k_nee_scan)
 
 struct PassParams {
     uint32_t seed, spp, spp_begin, spp_count;

@@ -2,11 +2,12 @@
 //   k_raygen : ray generation + bounce-0 closest hit, one thread per Monte-Carlo sample
 //   k_shade<c>(i) / k_trace(i) : the sample-phase loop unrolled over bounces as dense wavefronts (grid-stride over device-side
 //              work lists; one material class per k_shade launch)
-//   k_nee<c> : next-event estimation, grid-stride over the NEE work queues filled by k_shade
+//   k_nee<c> : next-event estimation, grid-stride over the record-slot runs of a material class
 //   k_splat  : stage 3 (ordered accumulation, spectrum -> sRGB, film splat with vector atomics)
 //   k_develop: HDRFilm::develop weight division
-// Path state lives in SoA arrays indexed depth-major (pltb_integrator.cuh) so warp accesses are coalesced float4s; queue
-// appends use warp-aggregated atomics (match_any + popc + one atomicAdd per group).
+// Path state lives in SoA arrays indexed depth-major (pltb_integrator.cuh) so warp accesses are coalesced float4s.  k_shade
+// appends nothing with atomics: record slots and next-bounce list positions follow from the position in the shade list
+// (warp_slot_prefix); the routing and NEE lists use warp-aggregated atomics (match_any + popc + one atomicAdd per group).
 #include <cuda_runtime.h>
 #include <cstdlib>
 #include <type_traits>
@@ -27,23 +28,6 @@ struct DevPush {
         base = __shfl_sync(peers, base, leader);
         list[base + __popc(peers & ((1u << lane) - 1u))] = entry;
     }
-    // The same append in two halves, so that a stage which appends to two lists (k_shade: NEE queue and live list) has both
-    // reservations in flight at once and spends the round trips of the atomics on its record stores instead of waiting twice.
-    // begin() and finish() of one ticket must sit under the same predicate (the peers meet again in finish()).
-    struct Ticket { unsigned peers; uint32_t base; int leader; };
-    __device__ __forceinline__ Ticket begin(uint32_t *count) const {
-        Ticket t;
-        t.peers = __match_any_sync(__activemask(), (unsigned long long) count);
-        t.leader = __ffs(t.peers) - 1;
-        t.base = 0;
-        if ((int) (threadIdx.x & 31) == t.leader) t.base = atomicAdd(count, (uint32_t) __popc(t.peers));
-        return t;
-    }
-    __device__ __forceinline__ uint32_t index(const Ticket &t) const {   // the position reserved for this lane
-        const uint32_t base = __shfl_sync(t.peers, t.base, t.leader);
-        return base + __popc(t.peers & ((1u << (threadIdx.x & 31)) - 1u));
-    }
-    __device__ __forceinline__ void finish(uint32_t *list, const Ticket &t, uint32_t entry) const { list[index(t)] = entry; }
 };
 
 struct DevFilm {
@@ -72,6 +56,69 @@ __device__ __forceinline__ void flush_counters(const uint32_t cnt[4], unsigned l
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         if ((threadIdx.x & 31) == 0 && v) atomicAdd(counters + k, (unsigned long long) v);
     }
+}
+
+// Record slots (PassState): the vertices shaded at bounce b by class c own the run [slot_base(b, c), + counts[cnt_shade(b, c)]),
+// the runs laid out in launch order (bounce-major, then class).  One warp computes the exclusive prefix over the (b, c) pairs
+// of bounces [0, nb) -- kClasses * nb <= 112 shade-queue counts, every lane a few loads and a shuffle scan -- and hands each pair
+// to `f(b, c, base, count)` (called by the lane that holds the pair).
+template <class F> __device__ __forceinline__ void warp_slot_prefix(const PassState &st, uint32_t nb, F &&f) {
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t carry = 0;
+    for (uint32_t k0 = 0; k0 < nb * kClasses; k0 += 32u) {
+        const uint32_t k = k0 + lane, b = k / kClasses, c = k % kClasses;
+        const uint32_t v = k < nb * kClasses ? st.counts[cnt_shade(b, c)] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int) lane >= o) incl += t;
+        }
+        if (k < nb * kClasses) f(b, c, carry + incl - v, v);
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+// slot_base(bounce, Class) for a k_shade launch and the first position of the class in the next bounce's live list, block-wide
+// (contains a barrier)
+__device__ __forceinline__ void block_slot_base(const PassState &st, uint32_t bounce, uint32_t cls, uint32_t &slot_base, uint32_t &live_base) {
+    __shared__ uint32_t s_base[2];
+    if (threadIdx.x < 32)
+        warp_slot_prefix(st, bounce + 1, [&](uint32_t b, uint32_t c, uint32_t base, uint32_t) {
+            if (b == bounce && c == cls) s_base[0] = base;
+            if (b == bounce && c == 0) s_base[1] = base;
+        });
+    __syncthreads();
+    slot_base = s_base[0]; live_base = s_base[0] - s_base[1];
+}
+// number of positions of the live list of bounce >= 1: the vertices shaded at the bounce before (PassState::live)
+__device__ __forceinline__ uint32_t live_count(const PassState &st, uint32_t bounce) {
+    uint32_t n = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < kClasses; ++c) n += st.counts[cnt_shade(bounce - 1, c)];
+    return n;
+}
+// The NEE work list of one class: its slot runs, bounce by bounce.  start[b] = number of list positions before bounce b.
+struct ClassRuns {
+    uint32_t start[PLTB_MAX_DEPTH + 1], base[PLTB_MAX_DEPTH];
+    __device__ __forceinline__ uint32_t slot(uint32_t x) const {
+        uint32_t b = 0;
+        while (x >= start[b + 1]) ++b;
+        return base[b] + (x - start[b]);
+    }
+};
+__device__ __forceinline__ uint32_t block_class_runs(const PassState &st, uint32_t cls, ClassRuns &runs) {   // contains barriers; returns the list size
+    if (threadIdx.x < 32) {
+        warp_slot_prefix(st, st.max_depth, [&](uint32_t b, uint32_t c, uint32_t base, uint32_t count) {
+            if (c == cls) { runs.base[b] = base; runs.start[b + 1] = count; }
+        });
+        __syncwarp();
+        if (threadIdx.x == 0) {
+            runs.start[0] = 0;
+            for (uint32_t b = 0; b < st.max_depth; ++b) runs.start[b + 1] += runs.start[b];
+        }
+    }
+    __syncthreads();
+    return runs.start[st.max_depth];
 }
 
 // (register budgets measured on cbox-grating, ms per 2^30 samples: k_raygen 72 regs 75.4, 64 regs 73.4, 48 regs 73.3; k_classify 80 regs 28.5,
@@ -116,7 +163,7 @@ __global__ void __launch_bounds__(128, 8) k_raygen(const __grid_constant__ Devic
 template <bool Shadow>
 __global__ void __launch_bounds__(128, Shadow ? PLTB_TRACE_MINB_SHADOW : PLTB_TRACE_MINB) k_trace(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                uint32_t bounce) {
-    const uint32_t n = Shadow ? st.counts[kCntShadow] : st.counts[cnt_live(bounce)];
+    const uint32_t n = Shadow ? st.counts[kCntShadow] : live_count(st, bounce);
     uint32_t *cursor = Shadow ? st.counts + kCntShadowCursor : st.counts + cnt_cursor(bounce);
     const unsigned lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
@@ -138,22 +185,31 @@ __global__ void __launch_bounds__(128, Shadow ? PLTB_TRACE_MINB_SHADOW : PLTB_TR
                 const uint32_t e = base + __popc(need & lt_mask);
                 if (e < n) {
                     Ray ray;
+                    bool have = true;
                     if (Shadow) {
                         local = st.shadow_q[e];   // record slot
                         ray = nee_shadow_ray(st, local);
                     } else {
                         local = st.live[e]; epos = e;
-                        float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
-                        ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
-                        cnt[0]++;
+                        have = local != kNoPath;   // else the path ended at the previous bounce: the lane asks again next round
+                        if (have) {
+                            float4 o = st.p_ray_o[local], d = st.p_ray_d[local];
+                            ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
+                            cnt[0]++;
+                        }
                     }
-                    tr.begin(sc, ray, stack_mem);
-                    active = true;
+                    if (have) {
+                        tr.begin(sc, ray, stack_mem);
+                        active = true;
+                    }
                 }
             }
             exhausted = base + __popc(need) >= n;   // warp-uniform
         }
-        if (__ballot_sync(0xffffffffu, active) == 0) break;
+        if (__ballot_sync(0xffffffffu, active) == 0) {   // warp-uniform
+            if (exhausted) break;
+            continue;   // a refill that met ended paths only
+        }
 #pragma unroll 1
         for (int k = 0; k < PLTB_TRACE_INNER; ++k)
             if (active && !tr.done && tr.node >= 0) tr.inner_step(sc);
@@ -183,7 +239,7 @@ __global__ void __launch_bounds__(128, Shadow ? PLTB_TRACE_MINB_SHADOW : PLTB_TR
 // only the misses touch per-path state; a warp takes 128 consecutive entries at a time and appends in list order.
 __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                   uint32_t bounce) {
-    const uint32_t n = st.counts[cnt_live(bounce)];
+    const uint32_t n = live_count(st, bounce);
     const uint32_t lane = threadIdx.x & 31u, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
     DevPush push;
     for (uint32_t base = warp * 128u; base < n; base += n_warps * 128u) {
@@ -195,7 +251,7 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            if (base + 32u * j + lane >= n) continue;
+            if (base + 32u * j + lane >= n || local[j] == kNoPath) continue;
             Hit h; h.t = 0.f; h.u = h.v = 0.f; h.prim = 0; h.cls = cls[j] & 7u; h.shape = cls[j] == 0xFFu ? -1 : 0;
             PCG32 rng; rng.state = 0; rng.inc = 0;
             if (h.shape < 0) { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
@@ -216,41 +272,32 @@ __global__ void __launch_bounds__(128, PLTB_SHADE_MINBLOCKS) k_shade(const __gri
     const uint32_t *list = st.shade_q[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     DevPush push;
-#ifdef PLTB_SHADE_PREFETCH
-    // software pipeline over the grid-stride loop: the queue entry of the item after next is loaded two iterations ahead, and the
-    // per-path state lines of the next item are pulled towards L2 while the current one is shaded (the item is a chain of
-    // dependent DRAM reads otherwise: entry -> state -> scene tables)
-    const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t cur = e < n ? list[e] : 0u, nxt = e + stride < n ? list[e + stride] : 0u;
-    for (; e < n; e += stride) {
-        const uint32_t nn = e + 2 * stride < n ? list[e + 2 * stride] : 0u;
-        if (e + stride < n) {
-            prefetch_l2(st.p_ray_o + nxt); prefetch_l2(st.p_ray_d + nxt); prefetch_l2(st.p_hit + nxt); prefetch_l2(st.wl + nxt);
-            prefetch_l2(st.rng_state + nxt); prefetch_l2(st.rng_inc + nxt);
-            if (bounce > 0) { prefetch_l2(st.p_alpha + nxt); prefetch_l2(st.p_prev + nxt); prefetch_l2(st.p_flags + nxt); }
-        }
-        stage_shade<Class>(sc, st, cur, bounce, push, cnt);
-        cur = nxt; nxt = nn;
-    }
-#else
+    uint32_t slot_base, live_base;   // record slot / next live-list position of list position e: base + e
+    block_slot_base(st, bounce, Class, slot_base, live_base);
+    // (measured and rejected: pulling the next item's path state towards L2 while the current one is shaded)
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_shade<Class>(sc, st, list[e], bounce, push, cnt);
-#endif
+        stage_shade<Class>(sc, st, list[e], bounce, slot_base + e, live_base + e, push, cnt);
     flush_counters(cnt, st.counters);
 }
 
 // NEE step 1 for the queue of one material class (the stage itself is class-independent)
 __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                    int cls) {
-    const uint32_t n = st.counts[cnt_nee(cls)];
-    const uint32_t *queue = st.queue[cls];
+    __shared__ ClassRuns runs;
+    const uint32_t n = block_class_runs(st, (uint32_t) cls, runs);
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    if (blockIdx.x == 0 && threadIdx.x == 0 && n)   // queue sizes: roughgrating / everything else
-        atomicAdd(st.counters + (cls == PLTB_BSDF_ROUGHGRATING ? 5 : 4), (unsigned long long) n);
+    uint32_t items = 0;   // queue sizes: roughgrating / everything else
     DevPush push;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_light(sc, st, queue[e], push, cnt);
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t slot = runs.slot(e);
+        if (st.rec_entry[slot] == kNoRecord) continue;
+        items++;
+        stage_nee_light(sc, st, slot, push, cnt);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) items += __shfl_xor_sync(0xffffffffu, items, o);
+    if ((threadIdx.x & 31) == 0 && items) atomicAdd(st.counters + (cls == PLTB_BSDF_ROUGHGRATING ? 5 : 4), (unsigned long long) items);
     flush_counters(cnt, st.counters);
 }
 
@@ -261,12 +308,15 @@ __global__ void __launch_bounds__(256) k_nee_light(const __grid_constant__ Devic
 template <int Class, bool Rgb>
 __global__ void __launch_bounds__(128) k_nee_post(const __grid_constant__ DeviceScene sc,
                                                                       const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[cnt_nee(Class)];
-    const uint32_t *queue = st.queue[Class];
+    __shared__ ClassRuns runs;
+    const uint32_t n = block_class_runs(st, (uint32_t) Class, runs);
     DevPush push;
     constexpr int kMode = (Class == PLTB_BSDF_ROUGHGRATING && !Rgb) ? kNeeFilter : kNeeFull;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post<Class, Rgb, kMode>(sc, st, queue[e], true, push, GratingInsideDirect());
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t slot = runs.slot(e);
+        if (st.rec_entry[slot] == kNoRecord) continue;
+        stage_nee_post<Class, Rgb, kMode>(sc, st, slot, true, push, GratingInsideDirect());
+    }
 }
 
 __global__ void __launch_bounds__(128) k_nee_scan(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
@@ -481,17 +531,22 @@ __global__ void __launch_bounds__(128) k_shade_pol(const __grid_constant__ Devic
     const uint32_t *list = st.shade_q[Class];
     uint32_t cnt[4] = { 0, 0, 0, 0 };
     DevPush push;
+    uint32_t slot_base, live_base;
+    block_slot_base(st, bounce, Class, slot_base, live_base);
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_shade_pol<Class>(sc, st, list[e], bounce, push, cnt);
+        stage_shade_pol<Class>(sc, st, list[e], bounce, slot_base + e, live_base + e, push, cnt);
     flush_counters(cnt, st.counters);
 }
 
 template <int Class, bool Rgb>
 __global__ void __launch_bounds__(128) k_nee_post_pol(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st) {
-    const uint32_t n = st.counts[cnt_nee(Class)];
-    const uint32_t *queue = st.queue[Class];
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x)
-        stage_nee_post_pol<Class, Rgb>(sc, st, queue[e]);
+    __shared__ ClassRuns runs;
+    const uint32_t n = block_class_runs(st, (uint32_t) Class, runs);
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t slot = runs.slot(e);
+        if (st.rec_entry[slot] == kNoRecord) continue;
+        stage_nee_post_pol<Class, Rgb>(sc, st, slot);
+    }
 }
 
 // plt_solve_phase accumulation for the first column of L, then StokesIntegrator::sample's rotation to the sensor frame

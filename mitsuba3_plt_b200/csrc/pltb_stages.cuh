@@ -140,7 +140,7 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
 // One iteration of the sample-phase loop (plt.py:93-168) for a path that hit a surface of material class `Class`, fused with
 // the parts of the solve phase that only depend on vertices 0..i (replay_path :408-472, solve_replay_emissive :315-405).
 template <int Class, class Push>
-PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
+PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, uint32_t slot, uint32_t live_pos, Push &push, uint32_t cnt[4]) {
     PLTB_ASSERT(local < st.chunk && i < st.max_depth);
     const float4 o4 = st.p_ray_o[local], d4 = st.p_ray_d[local], h4 = st.p_hit[local];
     Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
@@ -207,11 +207,9 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
     active_next = active_next && (!rr_active || rr_continue);
 
     // bounce record
-    const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
-    typename Push::Ticket t_slot, t_nee, t_live;   // all reservations are issued before the record stores (DevPush::begin)
-    if (nee) { t_slot = push.begin(st.counts + kCntSlot); t_nee = push.begin(st.counts + cnt_nee(Class)); }
-    if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
-    // the stores that need no reservation go first: they cover the round trips of the atomics
+    constexpr bool kSmoothClass = (kSmoothClassMask >> Class & 1u) != 0;
+    PLTB_ASSERT(kSmoothClass || (so.type & F_Smooth) == 0);
+    const bool nee = kSmoothClass && (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
     if (em_id >= 0) { st.v_em[r] = s4_to_f4(em); flags |= 1ull << (kFlagEm + i); }   // other vertices have no emissive term
     if (nee) flags |= 1ull << (kFlagNee + i);   // the NEE steps write v_nee[r]
     st.rng_state[local] = rng.state;
@@ -226,8 +224,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
     }
-    if (nee) {
-        const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
+    if (nee) {   // NEE record, dense (PassState)
         st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
         st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
         st.v_s_wix[slot] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
@@ -236,9 +233,10 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
         st.v_wiz_shape[slot] = ws;
         st.rec_entry[slot] = local | (i << 27);
-        push.finish(st.queue[Class], t_nee, slot);
+    } else if (kSmoothClass && sc.n_emitters > 0) {
+        st.rec_entry[slot] = kNoRecord;
     }
-    if (active_next) push.finish(st.live, t_live, local);
+    if (i + 1 < st.max_depth) st.live[live_pos] = active_next ? local : kNoPath;   // the next bounce's ray list (PassState::live)
 }
 
 // solve_replay_NEE (plt.py:221-300) for one queued vertex, in three steps so that every step runs in dense warps:

@@ -77,7 +77,7 @@ PLTB_NI void pol_miss_record(const DeviceScene &sc, const PassState &st, uint32_
 }
 
 template <int Class, class Push>
-PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, Push &push, uint32_t cnt[4]) {
+PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i, uint32_t slot, uint32_t live_pos, Push &push, uint32_t cnt[4]) {
     const float4 o4 = st.p_ray_o[local], d4 = st.p_ray_d[local], h4 = st.p_hit[local];
     Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
     Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.prim = f2u(h4.w) & kHitPrimMask; h.cls = (uint32_t) Class;
@@ -165,13 +165,10 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
     bool rr_continue = rng.next_float32() < rr_prob;
     active_next = active_next && (!rr_active || rr_continue);
 
-    const bool nee = (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
-    typename Push::Ticket t_live;   // all list reservations in flight before the record stores (DevPush::begin)
-    if (active_next) t_live = push.begin(st.counts + cnt_live(i + 1));
+    constexpr bool kSmoothClass = (kSmoothClassMask >> Class & 1u) != 0;
+    const bool nee = kSmoothClass && (so.type & F_Smooth) != 0 && sc.n_emitters > 0;
     if (nee) {
         flags |= 1ull << (kFlagNee + i);
-        typename Push::Ticket t_slot = push.begin(st.counts + kCntSlot), t_nee = push.begin(st.counts + cnt_nee(Class));
-        const uint32_t slot = push.index(t_slot);   // NEE record, dense (PassState)
         st.v_p_u[slot] = mkf4(si.p.x, si.p.y, si.p.z, si.uv.x);
         st.v_n_v[slot] = mkf4(si.n.x, si.n.y, si.n.z, si.uv.y);
         st.v_s_wix[slot] = mkf4(si.sh.s.x, si.sh.s.y, si.sh.s.z, si.wi.x);
@@ -180,7 +177,8 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         float2 ws; ws.x = si.wi.z; ws.y = u2f((uint32_t) si.shape);
         st.v_wiz_shape[slot] = ws;
         st.rec_entry[slot] = local | (i << 27);
-        push.finish(st.queue[Class], t_nee, slot);
+    } else if (kSmoothClass && sc.n_emitters > 0) {
+        st.rec_entry[slot] = kNoRecord;
     }
     st.rng_state[local] = rng.state;
     if (active_next) {
@@ -190,11 +188,11 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
         pol_store_col(st.pp_alpha, st.chunk, local, alpha);
         st.p_prev[local] = mkf4(si.p.x, si.p.y, si.p.z, delta ? last_nd_pdf : so.pdf);
         st.p_flags[local] = (flags & ~1ull) | (delta ? 1ull : 0ull);
-        push.finish(st.live, t_live, local);
     } else {
         st.v_mask[local] = pack_mask(flags);
         st.n_vertices[local] = i + 1;
     }
+    if (i + 1 < st.max_depth) st.live[live_pos] = active_next ? local : kNoPath;
 }
 
 // solve_replay_NEE's BSDF half in a polarized variant.  em_weight is depolarizer(e), so ((e mis) * B) has only row 0,
