@@ -50,7 +50,7 @@ for step in "$@"; do
       timeout 1500 python tools/config_bench.py ${only:+--only $only} 2> ${O}_configs.err | tee ${O}_configs.jsonl ;;
     anim) timeout 600 python tools/anim_bench.py 2> ${O}_anim.err | tee ${O}_anim.jsonl ;;
     debugchecks)   # the GPU test-suite against a build with device-side assertions (-DPLTB_DEBUG_CHECKS); stands in for compute-sanitizer
-      bash tools/build_variant.sh dbg -DPLTB_DEBUG_CHECKS > ${O}_debugchecks_build.log 2>&1
+      [ -f mitsuba3_plt_b200/libpltb200_dbg.so ] || bash tools/build_variant.sh dbg -DPLTB_DEBUG_CHECKS > ${O}_debugchecks_build.log 2>&1   # (build it before the call: box time is GPU budget)
       PLTB200_LIB=mitsuba3_plt_b200/libpltb200_dbg.so timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -5 | tee ${O}_debugchecks.log ;;
     sanitize)
       for tool in memcheck racecheck initcheck; do

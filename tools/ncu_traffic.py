@@ -13,7 +13,7 @@ NAMES = [(r"k_raygen", "k_raygen"), (r"k_shade(_pol)?<\(int\)5>|k_shade(_pol)?<5
          (r"k_shade(_pol)?<", "k_shade<other>"), (r"k_trace<0>|k_trace<\(bool\)0>|k_trace<false>", "k_trace"),
          (r"k_trace<1>|k_trace<\(bool\)1>|k_trace<true>", "k_trace<shadow>"), (r"k_classify", "k_classify"),
          (r"k_nee_light", "k_nee_light"), (r"k_nee_post(_pol)?<\(int\)5|k_nee_post(_pol)?<5", "k_nee_post<grating>"),
-         (r"k_nee_post(_pol)?<", "k_nee_post<other>"), (r"k_nee_eval", "k_nee_eval"),
+         (r"k_nee_post(_pol)?<", "k_nee_post<other>"), (r"k_nee_scan", "k_nee_scan"), (r"k_nee_eval", "k_nee_eval"),
          (r"k_gather", "k_gather"), (r"k_splat", "k_splat"), (r"k_develop", "k_develop")]
 COLS = {"t": "gpu__time_duration.sum", "rd": "dram__bytes_read.sum", "wr": "dram__bytes_write.sum",
         "issue": "smsp__issue_active.avg.pct_of_peak_sustained_active",
