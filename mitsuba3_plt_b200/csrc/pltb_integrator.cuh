@@ -287,10 +287,11 @@ struct PassState {
 };
 // layout of PassState::counts: per bounce i a block of kCountsStride counters {unused, trace cursor, shade_q[c] counts}; then (after
 // kClasses unused ones) the queue_eval count, the shadow_q count, the shadow-ray cursor and the scan-list count
-// Every counter sits in its own 128-byte line (kCntPad words apart): atomics on words of one line queue up in the same L2 slice
+// Every counter sits in its own 256-byte block (kCntPad words apart; 128 B apart they still collide in pairs: k_classify 21.8 ->
+// 19.0 ms per 2^30 samples on cbox-grating): atomics on words of one line queue up in the same L2 slice
 // (veach-mis 917 -> 963 Msamples/s when k_shade still appended to three lists per item, profiles/r02_ab_session17.txt).
 #ifndef PLTB_CNT_PAD
-#define PLTB_CNT_PAD 32
+#define PLTB_CNT_PAD 64
 #endif
 constexpr int kCntPad = PLTB_CNT_PAD;
 constexpr int kCountsStride = 2 + kClasses + 3;   // 12

@@ -123,14 +123,40 @@ __device__ __forceinline__ uint32_t block_class_runs(const PassState &st, uint32
 
 // (register budgets measured on cbox-grating, ms per 2^30 samples: k_raygen 72 regs 75.4, 64 regs 73.4, 48 regs 73.3; k_classify 80 regs 28.5,
 // 64 regs 29.4, 40 regs 30.2; k_gather 60 regs 18.0, 40 regs 20.2, 32 regs 32.0; k_nee_light 64 regs 27-28, 48 regs 30.8, 40 regs 33.6)
-__global__ void __launch_bounds__(128, 8) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
+#ifndef PLTB_RAYGEN_THREADS
+#define PLTB_RAYGEN_THREADS 128
+#endif
+// a list append that does nothing: k_raygen appends the hits of a whole block at once
+struct NoPush { __device__ __forceinline__ void operator()(uint32_t *, uint32_t *, uint32_t) const {} };
+// The block's hits go to the shade queues as ONE run per class (counted per warp in shared memory, one atomicAdd per class and
+// block): a k_shade warp then reads the path state of consecutive samples -- appended warp by warp, the 16 or so entries a warp
+// contributes to a class sat between those of unrelated warps.
+__global__ void __launch_bounds__(PLTB_RAYGEN_THREADS, 1024 / PLTB_RAYGEN_THREADS) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                 const __grid_constant__ PassParams pp) {
-    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    constexpr uint32_t kWarps = PLTB_RAYGEN_THREADS / 32;
+    __shared__ uint32_t s_cnt[kWarps][kClasses + 1];
+    __shared__ uint32_t s_base[kClasses];
+    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
+    for (uint32_t k = threadIdx.x; k < kWarps * (kClasses + 1); k += blockDim.x) (&s_cnt[0][0])[k] = 0u;
+    int cls = -1;
     if (local < pp.count) {
-        DevPush push;
-        stage_raygen(sc, st, pp, local, push, cnt);
+        NoPush push;
+        cls = stage_raygen(sc, st, pp, local, push, cnt);
     }
+    __syncthreads();
+    const unsigned peers = __match_any_sync(0xffffffffu, cls >= 0 ? (uint32_t) cls : 0x100u + lane);
+    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    if (cls >= 0 && rank == 0) s_cnt[warp][cls] = (uint32_t) __popc(peers);
+    __syncthreads();
+    if (threadIdx.x < (uint32_t) kClasses) {
+        uint32_t off = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < kWarps; ++w) { const uint32_t v = s_cnt[w][threadIdx.x]; s_cnt[w][threadIdx.x] = off; off += v; }
+        if (off) s_base[threadIdx.x] = atomicAdd(st.counts + cnt_shade(0, threadIdx.x), off);
+    }
+    __syncthreads();
+    if (cls >= 0) st.shade_q[cls][s_base[cls] + s_cnt[warp][cls] + rank] = local;
     flush_counters(cnt, st.counters);
 }
 
@@ -236,27 +262,69 @@ __global__ void __launch_bounds__(128, Shadow ? PLTB_TRACE_MINB_SHADOW : PLTB_TR
 
 // Routes the results of k_trace: hits to the shade queue of their material class, misses finalised in place.  k_trace leaves the
 // class (or 0xFF for a miss) in hit_cls[position in the live list], so this pass reads two dense arrays (4 + 1 bytes per ray) and
-// only the misses touch per-path state; a warp takes 128 consecutive entries at a time and appends in list order.
+// only the misses touch per-path state.  Appending per warp (one atomicAdd per 32 entries and class) made this pass 15 % faster
+// than the block-wide form below, but left the queues as interleaved 10-30 entry pieces of unrelated warps: with one run per
+// block and class k_shade reads the state of consecutive paths (k_shade<other> 60.9 -> 54.2 ms per 2^30 samples on cbox, 3102 ->
+// 2944 ms per render on veach-mis; profiles/r02_ab_session17.txt).
 __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                   uint32_t bounce) {
+    // A block takes 1024 consecutive entries at a time (warp w the entries 128 w .. 128 w + 127, in four rounds of 32) and reserves
+    // ONE run per class in the shade queues for all of them: the 32 (warp, round) groups count their hits per class, warp 0 scans
+    // the groups, lanes 0..6 issue the (at most seven, concurrent) atomicAdds.  List order is kept within the block's entries.
     const uint32_t n = live_count(st, bounce);
-    const uint32_t lane = threadIdx.x & 31u, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    constexpr uint32_t kPerBlock = 8u * 128u;
+    __shared__ uint32_t s_cnt[32][kClasses + 1];   // [group = 4 * warp + round][class]: hits, then their offset in the block's run
+    __shared__ uint32_t s_base[kClasses];
     DevPush push;
-    for (uint32_t base = warp * 128u; base < n; base += n_warps * 128u) {
-        uint32_t local[4]; uint32_t cls[4];
+    for (uint32_t base = blockIdx.x * kPerBlock; base < n; base += gridDim.x * kPerBlock) {
+        for (uint32_t k = threadIdx.x; k < 32u * (kClasses + 1); k += blockDim.x) (&s_cnt[0][0])[k] = 0u;
+        __syncthreads();
+        uint32_t local[4], cls[4], rank[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t e = base + 32u * j + lane;
-            local[j] = e < n ? st.live[e] : 0u; cls[j] = e < n ? (uint32_t) st.hit_cls[e] : 0u;
+            const uint32_t e = base + 128u * warp + 32u * j + lane;
+            local[j] = e < n ? st.live[e] : kNoPath; cls[j] = e < n ? (uint32_t) st.hit_cls[e] : 0xFFu;
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            if (base + 32u * j + lane >= n || local[j] == kNoPath) continue;
-            Hit h; h.t = 0.f; h.u = h.v = 0.f; h.prim = 0; h.cls = cls[j] & 7u; h.shape = cls[j] == 0xFFu ? -1 : 0;
-            PCG32 rng; rng.state = 0; rng.inc = 0;
-            if (h.shape < 0) { rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]]; }
-            route_hit(sc, st, local[j], bounce, h, rng, false, push);   // any valid shape: only hit / miss and the class matter here
+            const bool hit = local[j] != kNoPath && cls[j] != 0xFFu;
+            const unsigned peers = __match_any_sync(0xffffffffu, hit ? cls[j] : 0x100u + lane);
+            rank[j] = __popc(peers & ((1u << lane) - 1u));
+            if (hit && rank[j] == 0) s_cnt[4 * warp + j][cls[j] & 7u] = (uint32_t) __popc(peers);
         }
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t mine = 0;   // lane c: hits of class c in the block's entries
+#pragma unroll
+            for (uint32_t c = 0; c < (uint32_t) kClasses; ++c) {
+                const uint32_t v = s_cnt[lane][c];
+                uint32_t incl = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if ((int) lane >= o) incl += t;
+                }
+                s_cnt[lane][c] = incl - v;
+                const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+                if (lane == c) mine = total;
+            }
+            if (lane < (uint32_t) kClasses && mine) s_base[lane] = atomicAdd(st.counts + cnt_shade(bounce, lane), mine);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (local[j] == kNoPath) continue;
+            if (cls[j] != 0xFFu) {
+                const uint32_t c = cls[j] & 7u;
+                st.shade_q[c][s_base[c] + s_cnt[4 * warp + j][c] + rank[j]] = local[j];
+            } else {
+                Hit h; h.t = 0.f; h.u = h.v = 0.f; h.prim = 0; h.cls = 0; h.shape = -1;
+                PCG32 rng; rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]];
+                route_hit(sc, st, local[j], bounce, h, rng, false, push);   // miss: finalised in place
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -629,7 +697,7 @@ thread_local LaunchHook g_launch_hook;
 #define PLTB_AFTER(k) do { if (g_launch_hook.fn) g_launch_hook.fn((k), g_launch_hook.user); } while (0)
 
 void launch_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, cudaStream_t s) {
-    k_raygen<<<(pp.count + 127) / 128, 128, 0, s>>>(sc, st, pp); PLTB_AFTER(PLTB_K_RAYGEN);
+    k_raygen<<<(pp.count + PLTB_RAYGEN_THREADS - 1) / PLTB_RAYGEN_THREADS, PLTB_RAYGEN_THREADS, 0, s>>>(sc, st, pp); PLTB_AFTER(PLTB_K_RAYGEN);
 }
 void launch_trace(const DeviceScene &sc, const PassState &st, uint32_t bounce, int grid, cudaStream_t s) {
     k_trace<false><<<grid, 128, 0, s>>>(sc, st, bounce); PLTB_AFTER(PLTB_K_TRACE);

@@ -97,8 +97,8 @@ PLTB_HD void route_hit(const DeviceScene &sc, const PassState &st, uint32_t loca
 
 // ADIntegrator.sample_rays (common.py:231-309) + the first iteration's scene.ray_intersect (plt.py:96)
 template <class Push>
-PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Push &push,
-                          uint32_t cnt[4]) {
+PLTB_HD int stage_raygen(const DeviceScene &sc, const PassState &st, const PassParams &pp, uint32_t local, Push &push,
+                         uint32_t cnt[4]) {   // returns the material class of what the primary ray hit, -1 for a miss
     uint32_t x, y, s, idx;
     decode_sample(pp, pp.first + local, x, y, s, idx);
     // PCG32Sampler::seed (src/render/sampler.cpp:125-145)
@@ -135,6 +135,7 @@ PLTB_HD void stage_raygen(const DeviceScene &sc, const PassState &st, const Pass
         st.p_ray_d[local] = mkf4(ray.d.x, ray.d.y, ray.d.z, 1.f);
     }
     route_hit(sc, st, local, 0, h, rng, true, push);
+    return h.shape >= 0 ? (int) h.cls : -1;
 }
 
 // One iteration of the sample-phase loop (plt.py:93-168) for a path that hit a surface of material class `Class`, fused with
