@@ -334,15 +334,17 @@ static int ensure_state(pltb_context *c, uint32_t chunk, uint32_t depth, bool po
     rc |= alloc((void **) &st.wl, chunk * sizeof(float4));
     rc |= alloc((void **) &st.sensor_w, chunk * sizeof(float4));
     rc |= alloc((void **) &st.film_pos, chunk * sizeof(float2));
-    rc |= alloc((void **) &st.rng_state, chunk * sizeof(uint64_t));
-    rc |= alloc((void **) &st.rng_inc, chunk * sizeof(uint64_t));
+    {   // interleaved per-path streams (Strided, pltb_integrator.cuh)
+        uint64_t *rec = nullptr; float4 *ray = nullptr, *thr = nullptr;
+        rc |= alloc((void **) &rec, 4 * (size_t) chunk * sizeof(uint64_t));
+        rc |= alloc((void **) &ray, 2 * (size_t) chunk * sizeof(float4));
+        rc |= alloc((void **) &thr, 2 * (size_t) chunk * sizeof(float4));
+        st.rng_state.base = rec; st.rng_inc.base = rec + 1; st.p_flags.base = rec + 2;
+        st.p_ray_o.base = ray; st.p_ray_d.base = ray + 1;
+        st.p_alpha.base = thr; st.p_prev.base = thr + 1;
+    }
     rc |= alloc((void **) &st.n_vertices, chunk * sizeof(uint32_t));
-    rc |= alloc((void **) &st.p_ray_o, chunk * sizeof(float4));
-    rc |= alloc((void **) &st.p_ray_d, chunk * sizeof(float4));
     rc |= alloc((void **) &st.p_hit, chunk * sizeof(float4));
-    rc |= alloc((void **) &st.p_alpha, chunk * sizeof(float4));
-    rc |= alloc((void **) &st.p_prev, chunk * sizeof(float4));
-    rc |= alloc((void **) &st.p_flags, chunk * sizeof(uint64_t));
     rc |= alloc((void **) &st.v_mask, chunk * sizeof(uint32_t));
     rc |= alloc((void **) &st.v_w, nv * sizeof(float4));
     rc |= alloc((void **) &st.live, chunk * sizeof(uint32_t));
@@ -444,6 +446,7 @@ int pltb_render(pltb_context *c, const pltb_scene *scene, const pltb_render_para
     if (!polarized) { st.pp_alpha = st.pv_w = st.pv_alpha = st.pv_em = nullptr; st.stokes_theta = nullptr; }
     else if (!stokes) st.stokes_theta = nullptr;
     st.nv = (size_t) c->st_chunk * c->st_depth;
+    for (int k = 0; k < 4; ++k) st.L_out[k] = polarized ? st.pv_em + (size_t) k * st.nv : (k == 0 ? st.v_em : nullptr);
     st.chunk = c->st_chunk; st.max_depth = prm->max_depth; st.rr_depth = prm->rr_depth;
     float *d_wl = nullptr, *d_L = nullptr, *d_stokes = nullptr; uint32_t *d_rays = nullptr; uint64_t dcap = 0;
     st.n_shadow = nullptr;

@@ -222,6 +222,13 @@ PLTB_HD float rfilter_eval(const pltb_film &f, float x) {  // gaussian.cpp:94-10
 // veach-mis and missed the instruction cache (profiles/r02_ncu_kernels_c{1,4}_2class.txt).
 constexpr int kClasses = 7;
 
+// Per-path streams that the list-driven kernels (k_shade, k_trace, the NEE steps) read together are INTERLEAVED so that a path's
+// values share 32-byte sectors: those kernels gather by path id, and a gathered 16-byte (8-byte) element uses half (a quarter) of
+// the sector it pulls from DRAM.  `Strided<T, N>` is stream k of N interleaved ones: element i sits at base[N i] (base = buffer + k).
+template <class T, int N> struct Strided {
+    T *base;
+    PLTB_HD T &operator[](size_t i) const { return base[(size_t) N * i]; }
+};
 struct PassState {
     uint32_t chunk;            // samples per pass (capacity of every per-sample array)
     uint32_t max_depth, rr_depth;
@@ -229,16 +236,17 @@ struct PassState {
     float4 *wl;                // sampled wavelengths
     float4 *sensor_w;          // sensor spectral weight
     float2 *film_pos;          // splat position
-    uint64_t *rng_state, *rng_inc;   // PCG32 state (advanced bounce by bounce; NEE draws continue from the final state)
+    Strided<uint64_t, 4> rng_state, rng_inc;   // PCG32 state (advanced bounce by bounce; NEE draws continue from the final state);
+                                               // one 32-byte record per sample with p_flags: {state, inc, flags, -}
     uint32_t *n_vertices;      // bounce records written (== closest-hit rays traced: one per loop iteration)
     uint32_t *n_shadow;        // shadow rays traced per sample; nullptr unless the caller asked for pltb_sample_dump.n_rays
     // per path, carried from bounce to bounce
-    float4 *p_ray_o;           // {ray.o, ray.maxt}
-    float4 *p_ray_d;           // {ray.d, eta}
+    Strided<float4, 2> p_ray_o;   // {ray.o, ray.maxt}   } one 32-byte record per path
+    Strided<float4, 2> p_ray_d;   // {ray.d, eta}        }
     float4 *p_hit;             // {t, u, v, prim id bits} of the closest hit found by k_trace
-    float4 *p_alpha;           // sample-phase throughput alpha
-    float4 *p_prev;            // {prev_si.p, last_nd_pdf}
-    uint64_t *p_flags;         // bit 0: prev_bsdf_delta; bits 1 + j: (polarized) the replay weight of vertex j is a scaled identity;
+    Strided<float4, 2> p_alpha;   // sample-phase throughput alpha   } one 32-byte record per path
+    Strided<float4, 2> p_prev;    // {prev_si.p, last_nd_pdf}        }
+    Strided<uint64_t, 4> p_flags;       // bit 0: prev_bsdf_delta; bits 1 + j: (polarized) the replay weight of vertex j is a scaled identity;
                                // bits 17 + j / 33 + j: vertex j has an emissive / an NEE term (kFlagEm / kFlagNee)
     uint32_t *v_mask;          // per sample, written when the path ends: bit j: vertex j has an emissive term (v_em / pv_em written),
                                // bit 16 + j: an NEE term (v_nee written).  Most terms are exact zeros (only emitter hits have an
@@ -257,6 +265,8 @@ struct PassState {
     float4 *v_alpha;           // [slot] replayed throughput alpha_i
     float4 *v_emw;             // [slot] emitter weight between the NEE steps (k_nee_light -> k_nee_post -> k_nee_eval)
     uint32_t *rec_entry;       // [slot] sample_local | depth << 27 of the vertex, or kNoRecord
+    float4 *L_out[4];          // where k_gather leaves a sample's sum for the splat (dense, [sample]): row 0 of v_em -- polarized:
+                               // of the four pv_em components -- which the gathering thread has consumed by then
     float4 *v_em;              // MIS-weighted emissive contribution alpha_i * Lem_i
     float4 *v_nee;             // NEE contribution (k_nee)
     float2 *v_wiz_shape;       // [slot] {wi.z, shape id bits}
@@ -303,6 +313,10 @@ constexpr int kCntEval = kCntPad * (kCountsNee + kClasses), kCntShadow = kCntPad
               kCntShadowCursor = kCntPad * (kCountsNee + kClasses + 2);
 constexpr int kFlagEm = 17, kFlagNee = 33;   // first bit of the two presence masks in PassState::p_flags
 PLTB_HD uint32_t pack_mask(uint64_t flags) { return (uint32_t) ((flags >> kFlagEm) & 0xFFFFull) | ((uint32_t) ((flags >> kFlagNee) & 0xFFFFull) << 16); }
+// index of the replay weight of vertex j of a path in v_w / pv_w during the sample phase: depth-major.  (Path-major -- a path's
+// weights consecutive, so that the replay product reads whole sectors -- measured slower: the per-vertex store becomes a strided
+// partial-sector write; veach-mis 1127 -> 1106, C2 2234 -> 2211, C2pol 746 -> 665 Msamples/s, profiles/r02_ab_session17.txt)
+PLTB_HD size_t w_index(const PassState &st, uint32_t local, uint32_t j) { return (size_t) j * st.chunk + local; }
 constexpr uint32_t kNoRecord = 0xFFFFFFFFu;   // rec_entry of a vertex without NEE item
 constexpr uint32_t kNoPath = 0xFFFFFFFFu;     // live-list position of a path that ended at the previous bounce
 // material classes whose samples can be smooth (diffuse, roughconductor, roughgrating, principled): only they run the NEE kernels

@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(128) k_nee_eval(const __grid_constant__ Device
 
 // plt_solve_phase accumulation (plt.py:191-216), one thread per sample at full occupancy: the records of a path sit one DRAM
 // round trip apart (depth-major arrays), so the loads are issued four vertices at a time before the ordered sum consumes them.
-// The sum L is left in p_ray_o (dead after the last k_trace) for the splat kernels; optional per-sample dump.
+// The sum L is left in L_out[0] (PassState) for the splat kernels; optional per-sample dump.
 __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassState st, const __grid_constant__ PassParams pp,
                                                 float *dump_wl, float *dump_L, uint32_t *dump_rays, uint64_t dump_cap) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(256) k_gather(const __grid_constant__ PassStat
                 if (m >> (16 + base + j) & 1u) L = L + f4_to_s4(ne[j]);
             }
     }
-    st.p_ray_o[local] = s4_to_f4(L);
+    st.L_out[0][local] = s4_to_f4(L);
     if (dump_cap) {
         uint32_t pix, s_rel;
         split_work(pp, pp.first + local, pix, s_rel);
@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceSce
     if (local >= pp.count) return;
     DevFilm film{ accum };
     float values[4];
-    splat_values(sc, st, local, f4_to_s4(st.p_ray_o[local]), values);
+    splat_values(sc, st, local, f4_to_s4(st.L_out[0][local]), values);
     splat_taps(sc, pp, values, st.film_pos[local], film);
 }
 
@@ -463,11 +463,11 @@ __global__ void __launch_bounds__(256) k_splat(const __grid_constant__ DeviceSce
 #endif
 constexpr int kSplatWarps = 4, kSplatS = PLTB_SPLAT_S;
 // G < 0: the RGBW film.  G = 0..3: float4 group G of the 16-channel Stokes film (k_gather_pol left the four Stokes components of L
-// in p_ray_o / p_ray_d / p_hit / p_prev): four launches of this kernel replace one thread per sample issuing 100 vector atomics
+// in L_out[0..3]): four launches of this kernel replace one thread per sample issuing 100 vector atomics
 // (k_splat_stokes: 61.6 of the 229 ms of a polarized cbox-grating render at 128 spp).
 template <int G> __device__ __forceinline__ void stokes_group_values(const DeviceScene &sc, const PassState &st, uint32_t local, const S4 &wl,
                                                                      const S4 &sw, float values[4]) {
-    const float4 *comp[4] = { st.p_ray_o, st.p_ray_d, st.p_hit, st.p_prev };
+    const float4 *comp[4] = { st.L_out[0], st.L_out[1], st.L_out[2], st.L_out[3] };
     if (G == 0) { splat_values(sc, f4_to_s4(comp[0][local]), wl, sw, values); return; }
     // AOV i = spectrum_to_srgb(S_i / pdf_rgb_spectrum(wavelengths)) (stokes.cpp:108-121), RGB variants: S_i itself; flattened channels
     // 3 i + c sit at film channel 4 + 3 i + c, i.e. group G holds flattened channels 4 (G - 1) .. 4 (G - 1) + 3
@@ -518,7 +518,7 @@ __global__ void __launch_bounds__(32 * kSplatWarps) k_splat_strip(const __grid_c
         if (f.in) {
             const uint32_t local = (uint32_t) (w - pp.first);
             f.local = local;
-            if (G < 0) f.L = st.p_ray_o[local];
+            if (G < 0) f.L = st.L_out[0][local];
             f.wl = st.wl[local]; f.sw = st.sensor_w[local]; f.pos = st.film_pos[local];
         }
         return f;
@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(128) k_nee_post_pol(const __grid_constant__ De
 }
 
 // plt_solve_phase accumulation for the first column of L, then StokesIntegrator::sample's rotation to the sensor frame
-// (stokes.cpp:97-106) when `stokes`.  The four components are left in p_ray_o / p_ray_d / p_hit / p_prev (dead by now).
+// (stokes.cpp:97-106) when `stokes`.  The four components are left in L_out[0..3] (PassState).
 __global__ void __launch_bounds__(256) k_gather_pol(const __grid_constant__ PassState st, const __grid_constant__ PassParams pp, int stokes,
                                                     float *dump_wl, float *dump_L, uint32_t *dump_rays, float *dump_stokes, uint64_t dump_cap) {
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(256) k_gather_pol(const __grid_constant__ Pass
             for (int c = 0; c < 4; ++c) L[c].v[k] = x.v[c];
         }
     }
-    st.p_ray_o[local] = s4_to_f4(L[0]); st.p_ray_d[local] = s4_to_f4(L[1]); st.p_hit[local] = s4_to_f4(L[2]); st.p_prev[local] = s4_to_f4(L[3]);
+    for (int c = 0; c < 4; ++c) st.L_out[c][local] = s4_to_f4(L[c]);
     if (dump_cap) {
         uint32_t pix, s_rel;
         split_work(pp, pp.first + local, pix, s_rel);
@@ -661,7 +661,7 @@ __global__ void __launch_bounds__(256) k_splat_stokes(const __grid_constant__ De
     const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= pp.count) return;
     const S4 wl = f4_to_s4(st.wl[local]);
-    const S4 comp[4] = { f4_to_s4(st.p_ray_o[local]), f4_to_s4(st.p_ray_d[local]), f4_to_s4(st.p_hit[local]), f4_to_s4(st.p_prev[local]) };
+    const S4 comp[4] = { f4_to_s4(st.L_out[0][local]), f4_to_s4(st.L_out[1][local]), f4_to_s4(st.L_out[2][local]), f4_to_s4(st.L_out[3][local]) };
     float values[16];
     splat_values(sc, comp[0], wl, f4_to_s4(st.sensor_w[local]), values);
     for (int i = 0; i < 4; ++i) {

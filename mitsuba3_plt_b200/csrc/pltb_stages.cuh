@@ -66,7 +66,7 @@ PLTB_NI S4 env_miss_lem(const DeviceScene &sc, const PassState &st, uint32_t loc
 }
 PLTB_NI S4 env_miss_emission(const DeviceScene &sc, const PassState &st, uint32_t local, uint32_t i) {
     S4 ai = s4(1.f);
-    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
+    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[w_index(st, local, (uint32_t) j)]) * ai;
     return ai * env_miss_lem(sc, st, local, i);
 }
 
@@ -174,7 +174,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
 
     // replay_path for this vertex: alpha_i = w_0 * (w_1 * (... * (w_{i-1} * 1)))
     S4 ai = s4(1.f);
-    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[(size_t) j * st.chunk + local]) * ai;
+    for (int j = (int) i - 1; j >= 0; --j) ai = f4_to_s4(st.v_w[w_index(st, local, (uint32_t) j)]) * ai;
     // solve_replay_emissive
     S4 em = s4(0.f);
     const int32_t em_id = sc.shapes[si.shape].emitter;
@@ -193,7 +193,7 @@ PLTB_HD void stage_shade(const DeviceScene &sc, const PassState &st, uint32_t lo
         em = ai * (Le * mis_bsdf);
     }
     const size_t r = (size_t) i * st.chunk + local;
-    if (active_next) st.v_w[r] = s4_to_f4(wbsdf_weight<Class>(sc, b, si.wi, si.uv, wl, so.wo));
+    if (active_next) st.v_w[w_index(st, local, i)] = s4_to_f4(wbsdf_weight<Class>(sc, b, si.wi, si.uv, wl, so.wo));
     cnt[2]++;
     if (Class == PLTB_BSDF_ROUGHGRATING) cnt[3]++;
 

@@ -41,7 +41,7 @@ PLTB_HD float stokes_rotation_angle(const pltb_sensor &sn, V3 ray_d, bool batch)
 PLTB_HD void pol_replay_column(const PassState &st, uint32_t local, uint32_t i, uint32_t flags, C4 ai[4]) {
     for (int k = 0; k < 4; ++k) { ai[k].v[0] = 1.f; ai[k].v[1] = ai[k].v[2] = ai[k].v[3] = 0.f; }
     for (int j = (int) i - 1; j >= 0; --j) {
-        const size_t rj = (size_t) j * st.chunk + local;
+        const size_t rj = w_index(st, local, (uint32_t) j);
         if (flags >> (1 + j) & 1u) {
             const float4 s = st.pv_w[rj];
             const float sv[4] = { s.x, s.y, s.z, s.w };
@@ -138,14 +138,15 @@ PLTB_HD void stage_shade_pol(const DeviceScene &sc, const PassState &st, uint32_
     }
     if (em_id >= 0) { pol_store_col(st.pv_em, st.nv, r, em); flags |= 1ull << (kFlagEm + i); }   // other vertices have no emissive term
     if (active_next) {
+        const size_t rw = w_index(st, local, i);
         if (pv.type == PLTB_BSDF_DIFFUSE) {   // diag(reflectance): the four factors, flagged in p_flags
-            st.pv_w[r] = s4_to_f4(pv.refl);
+            st.pv_w[rw] = s4_to_f4(pv.refl);
             flags |= 1ull << (1 + i);
         } else {
             for (int k = 0; k < 4; ++k) {
                 const F44 W = pol_replay_weight(pv, k);
                 for (int row = 0; row < 4; ++row)
-                    st.pv_w[(size_t) (4 * k + row) * st.nv + r] = mkf4(W.m[row][0], W.m[row][1], W.m[row][2], W.m[row][3]);
+                    st.pv_w[(size_t) (4 * k + row) * st.nv + rw] = mkf4(W.m[row][0], W.m[row][1], W.m[row][2], W.m[row][3]);
             }
         }
     }
