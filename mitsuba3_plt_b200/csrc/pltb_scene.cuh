@@ -203,7 +203,12 @@ template <bool AnyHit> PLTB_NI Hit bvh_intersect(const DeviceScene &sc, Ray ray)
     unsigned long long stack_mem[kBvhStack];
     Traversal tr;
     tr.begin(sc, ray, stack_mem);
-    while (!tr.done) tr.template step<AnyHit>(sc);
+    // while-while: all lanes walk inner nodes until each sits at a leaf (or is done), then the leaves are tested together
+    // (one inner-or-leaf step per iteration ran both bodies at partial occupancy: k_raygen 78.8 -> 73.3 ms per 2^30 samples)
+    while (!tr.done) {
+        while (!tr.done && tr.node >= 0) tr.inner_step(sc);
+        if (!tr.done) tr.template leaf_step<AnyHit>(sc);
+    }
     return tr.best;
 }
 
