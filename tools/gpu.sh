@@ -42,7 +42,7 @@ for step in "$@"; do
           python tools/ncu_target.py $a 1 > ${O}_ncu_f.log 2>&1
       ncu -i /tmp/${T}_full.ncu-rep --page details > ${O}_details.txt 2>/dev/null
       ncu -i /tmp/${T}_full.ncu-rep --page raw --csv > ${O}_raw.csv 2>/dev/null
-      ncu -i /tmp/${T}_full.ncu-rep --page source --csv --kernel-name regex:"k_shade|k_nee_post|k_trace" > ${O}_source.csv 2>/dev/null
+      ncu -i /tmp/${T}_full.ncu-rep --page source --csv --kernel-name regex:"k_shade|k_nee_post|k_trace|k_raygen|k_classify|k_nee_light" > ${O}_source.csv 2>/dev/null
       gzip -f ${O}_source.csv ${O}_raw.csv ${O}_details.txt
       tail -n 3 ${O}_ncu_f.log ;;
     configs*)
