@@ -128,36 +128,58 @@ __device__ __forceinline__ uint32_t block_class_runs(const PassState &st, uint32
 #endif
 // a list append that does nothing: k_raygen appends the hits of a whole block at once
 struct NoPush { __device__ __forceinline__ void operator()(uint32_t *, uint32_t *, uint32_t) const {} };
-// The block's hits go to the shade queues as ONE run per class (counted per warp in shared memory, one atomicAdd per class and
-// block): a k_shade warp then reads the path state of consecutive samples -- appended warp by warp, the 16 or so entries a warp
-// contributes to a class sat between those of unrelated warps.
+// The block's hits go to the shade queues as ONE run per class (one atomicAdd per class and block): a k_shade warp then reads the
+// path state of consecutive samples -- appended warp by warp, the 16 or so entries a warp contributes to a class sat between
+// those of unrelated warps.  No warp waits for another: each leaves the classes of its lanes in shared memory and the LAST one to
+// arrive appends for the whole block (with barriers, 17 % of the kernel's stall samples sat at the first one: a block waited for
+// its slowest traversal).
 __global__ void __launch_bounds__(PLTB_RAYGEN_THREADS, 1024 / PLTB_RAYGEN_THREADS) k_raygen(const __grid_constant__ DeviceScene sc, const __grid_constant__ PassState st,
                                                 const __grid_constant__ PassParams pp) {
     constexpr uint32_t kWarps = PLTB_RAYGEN_THREADS / 32;
     __shared__ uint32_t s_cnt[kWarps][kClasses + 1];
     __shared__ uint32_t s_base[kClasses];
-    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    __shared__ uint32_t s_arrived;
+    __shared__ uint8_t s_cls[PLTB_RAYGEN_THREADS];
+    const uint32_t block_first = blockIdx.x * blockDim.x, local = block_first + threadIdx.x, lane = threadIdx.x & 31u;
     uint32_t cnt[4] = { 0, 0, 0, 0 };
-    for (uint32_t k = threadIdx.x; k < kWarps * (kClasses + 1); k += blockDim.x) (&s_cnt[0][0])[k] = 0u;
+    if (threadIdx.x == 0) s_arrived = 0u;
+    __syncthreads();   // (all warps are still together here)
     int cls = -1;
     if (local < pp.count) {
         NoPush push;
         cls = stage_raygen(sc, st, pp, local, push, cnt);
     }
-    __syncthreads();
-    const unsigned peers = __match_any_sync(0xffffffffu, cls >= 0 ? (uint32_t) cls : 0x100u + lane);
-    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-    if (cls >= 0 && rank == 0) s_cnt[warp][cls] = (uint32_t) __popc(peers);
-    __syncthreads();
-    if (threadIdx.x < (uint32_t) kClasses) {
+    flush_counters(cnt, st.counters);
+    s_cls[threadIdx.x] = cls >= 0 ? (uint8_t) cls : (uint8_t) 0xFF;
+    __threadfence_block();
+    __syncwarp();
+    uint32_t order = 0;
+    if (lane == 0) order = atomicAdd(&s_arrived, 1u);
+    order = __shfl_sync(0xffffffffu, order, 0);
+    if (order != kWarps - 1) return;
+    __threadfence_block();
+    // the last warp of the block: group g = the lanes of warp g
+    for (uint32_t k = lane; k < kWarps * (kClasses + 1); k += 32u) (&s_cnt[0][0])[k] = 0u;
+    __syncwarp();
+    uint32_t rank[kWarps], c[kWarps];
+#pragma unroll
+    for (uint32_t g = 0; g < kWarps; ++g) {
+        c[g] = s_cls[32u * g + lane];
+        const unsigned peers = __match_any_sync(0xffffffffu, c[g] != 0xFFu ? c[g] : 0x100u + lane);
+        rank[g] = __popc(peers & ((1u << lane) - 1u));
+        if (c[g] != 0xFFu && rank[g] == 0) s_cnt[g][c[g]] = (uint32_t) __popc(peers);
+    }
+    __syncwarp();
+    if (lane < (uint32_t) kClasses) {
         uint32_t off = 0;
 #pragma unroll
-        for (uint32_t w = 0; w < kWarps; ++w) { const uint32_t v = s_cnt[w][threadIdx.x]; s_cnt[w][threadIdx.x] = off; off += v; }
-        if (off) s_base[threadIdx.x] = atomicAdd(st.counts + cnt_shade(0, threadIdx.x), off);
+        for (uint32_t g = 0; g < kWarps; ++g) { const uint32_t v = s_cnt[g][lane]; s_cnt[g][lane] = off; off += v; }
+        if (off) s_base[lane] = atomicAdd(st.counts + cnt_shade(0, lane), off);
     }
-    __syncthreads();
-    if (cls >= 0) st.shade_q[cls][s_base[cls] + s_cnt[warp][cls] + rank] = local;
-    flush_counters(cnt, st.counters);
+    __syncwarp();
+#pragma unroll
+    for (uint32_t g = 0; g < kWarps; ++g)
+        if (c[g] != 0xFFu) st.shade_q[c[g]][s_base[c[g]] + s_cnt[g][c[g]] + rank[g]] = block_first + 32u * g + lane;
 }
 
 // Closest hit for the live paths of bounce >= 1.  Secondary rays are incoherent and their traversal lengths differ by orders
