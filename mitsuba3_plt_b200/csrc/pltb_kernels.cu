@@ -333,6 +333,14 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
             }
             if (lane < (uint32_t) kClasses && mine) s_base[lane] = atomicAdd(st.counts + cnt_shade(bounce, lane), mine);
         }
+        // the per-path record of the misses (rng state, rng increment, flags: one sector), requested for all four rounds at once
+        // and before the barrier that waits for the block's atomics
+        uint64_t m_state[4], m_inc[4], m_flags[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (local[j] != kNoPath && cls[j] == 0xFFu) {
+                m_state[j] = st.rng_state[local[j]]; m_inc[j] = st.rng_inc[local[j]]; m_flags[j] = st.p_flags[local[j]];
+            }
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -340,9 +348,15 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ Device
             if (cls[j] != 0xFFu) {
                 const uint32_t c = cls[j] & 7u;
                 st.shade_q[c][s_base[c] + s_cnt[4 * warp + j][c] + rank[j]] = local[j];
+            } else if (sc.env < 0) {   // miss without environment: route_hit's miss branch on the values already loaded
+                uint64_t state = m_state[j];
+                for (int k = 0; k < 6; ++k) state = state * 0x5851f42d4c957f2dULL + m_inc[j];
+                st.rng_state[local[j]] = state;
+                st.v_mask[local[j]] = pack_mask(m_flags[j]);
+                st.n_vertices[local[j]] = bounce + 1;
             } else {
                 Hit h; h.t = 0.f; h.u = h.v = 0.f; h.prim = 0; h.cls = 0; h.shape = -1;
-                PCG32 rng; rng.state = st.rng_state[local[j]]; rng.inc = st.rng_inc[local[j]];
+                PCG32 rng; rng.state = m_state[j]; rng.inc = m_inc[j];
                 route_hit(sc, st, local[j], bounce, h, rng, false, push);   // miss: finalised in place
             }
         }
