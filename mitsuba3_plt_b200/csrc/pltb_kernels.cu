@@ -106,16 +106,23 @@ struct ClassRuns {
         return base[b] + (x - start[b]);
     }
 };
-__device__ __forceinline__ uint32_t block_class_runs(const PassState &st, uint32_t cls, ClassRuns &runs) {   // contains barriers; returns the list size
+__device__ __forceinline__ uint32_t block_class_runs(const PassState &st, uint32_t cls, ClassRuns &runs) {   // contains a barrier; returns the list size
     if (threadIdx.x < 32) {
+        const unsigned lane = threadIdx.x;
         warp_slot_prefix(st, st.max_depth, [&](uint32_t b, uint32_t c, uint32_t base, uint32_t count) {
             if (c == cls) { runs.base[b] = base; runs.start[b + 1] = count; }
         });
         __syncwarp();
-        if (threadIdx.x == 0) {
-            runs.start[0] = 0;
-            for (uint32_t b = 0; b < st.max_depth; ++b) runs.start[b + 1] += runs.start[b];
+        // start[] = prefix of the per-bounce counts: a warp scan (lane b holds bounce b; PLTB_MAX_DEPTH <= 32)
+        const uint32_t v = lane < st.max_depth ? runs.start[lane + 1] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int) lane >= o) incl += t;
         }
+        if (lane < st.max_depth) runs.start[lane + 1] = incl;
+        if (lane == 0) runs.start[0] = 0u;
     }
     __syncthreads();
     return runs.start[st.max_depth];
