@@ -54,7 +54,9 @@ for cid, name, rx, ry, spp, note in CONFIGS:
                       {"type": "plt", "max_depth": 7, "rr_depth": 50})
     sc = scenes.load(name, resx=rx, resy=ry)
     W, H = sc.film_size()
-    warm = min(spp, max(1, (1 << 24) // (W * H)))
+    # warm-up at the pass size of the timed render (2^25 samples): a smaller one makes the timed render re-allocate the wavefront
+    # state, and the first render on freshly allocated device memory was an intermittent 1.5-2.5x outlier (profiles/r02_configs_7a.jsonl)
+    warm = min(spp, max(1, -(-(1 << 25) // (W * H))))
     it.render(sc, spp=warm, seed=0, download=False)
     t0 = time.perf_counter()
     img = it.render(sc, spp=spp, seed=0)
