@@ -18,7 +18,7 @@
 
 // -DPLTB_DEBUG_CHECKS: device-side assertions on the invariants the kernels rely on (traversal stack bound, queue routing, record
 // indices).  compute-sanitizer is closed on the GPU pool this was developed on, so `tools/gpu.sh <tag> debugchecks` runs the GPU
-// test-suite against this build instead (profiles/r02_debugchecks.txt).
+// test-suite against this build instead (profiles/r02_debugchecks_7e.txt).
 #if defined(PLTB_DEBUG_CHECKS) && defined(__CUDA_ARCH__)
 #  include <assert.h>
 #  define PLTB_ASSERT(x) assert(x)
